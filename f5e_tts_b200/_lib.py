@@ -1,0 +1,75 @@
+"""ctypes binding of libf5e_b200.so (the C ABI declared in include/f5e_b200.h).
+
+There is deliberately no fallback: if the library is missing or a call fails, a RuntimeError is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+_HERE = Path(__file__).resolve().parent
+_LIB_PATH = _HERE / "libf5e_b200.so"
+_lib = None
+
+ACT_NONE, ACT_GELU_TANH, ACT_GELU_ERF, ACT_MISH, ACT_RELU, ACT_SILU = range(6)
+
+
+class Epilogue(C.Structure):
+    """Mirror of `f5e_epilogue` (include/f5e_b200.h)."""
+
+    _fields_ = [
+        ("out", C.c_void_p), ("ldo", C.c_int32), ("out_f32", C.c_int32),
+        ("bias", C.c_void_p), ("act", C.c_int32),
+        ("gate", C.c_void_p), ("gate_stride", C.c_int32),
+        ("residual", C.c_void_p), ("ldr", C.c_int32),
+        ("row_len", C.c_void_p), ("n_pad", C.c_int32),
+        ("rope_cos", C.c_void_p), ("rope_sin", C.c_void_p),
+        ("rope_inner", C.c_int32), ("rope_heads", C.c_int32),
+    ]
+
+
+def lib_path() -> Path:
+    return _LIB_PATH
+
+
+def load():
+    """Load (building first if the sources are newer and nvcc is present) the shared library."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if os.environ.get("F5E_NO_BUILD") != "1":
+        try:
+            from . import build as _build
+
+            _build.build()
+        except Exception as e:  # the prebuilt .so may still be usable (GPU box without nvcc)
+            if not _LIB_PATH.exists():
+                raise RuntimeError(f"libf5e_b200.so is missing and could not be built: {e}") from e
+    if not _LIB_PATH.exists():
+        raise RuntimeError(f"{_LIB_PATH} not found; run `python -m f5e_tts_b200.build`")
+    lib = C.CDLL(str(_LIB_PATH))
+    lib.f5e_last_error.restype = C.c_char_p
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        msg = load().f5e_last_error().decode(errors="replace")
+        raise RuntimeError(f"libf5e_b200 {what} failed ({rc}): {msg}")
+
+
+def ptr(t) -> C.c_void_p:
+    """Device pointer of a torch tensor (None -> NULL)."""
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def stream_ptr() -> C.c_void_p:
+    import torch
+
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def require_device() -> None:
+    check(load().f5e_check_device(), "f5e_check_device")

@@ -1,0 +1,57 @@
+// extern "C" surface of libf5e_b200.so (declared in include/f5e_b200.h).
+#include "../../include/f5e_b200.h"
+#include "host.h"
+
+using namespace f5e;
+
+static EpiParams to_epi(const f5e_epilogue* e, int M) {
+  EpiParams p{};
+  p.out = e->out; p.ldo = e->ldo; p.out_f32 = e->out_f32;
+  p.bias = e->bias; p.act = e->act;
+  p.gate = e->gate; p.gate_stride = e->gate_stride;
+  p.residual = reinterpret_cast<const __nv_bfloat16*>(e->residual); p.ldr = e->ldr;
+  p.row_len = e->row_len; p.n_pad = e->n_pad > 0 ? e->n_pad : M;
+  p.rope_cos = e->rope_cos; p.rope_sin = e->rope_sin;
+  p.rope_inner = e->rope_inner; p.rope_heads = e->rope_heads;
+  return p;
+}
+
+extern "C" {
+
+const char* f5e_last_error(void) { return last_error(); }
+int f5e_version(void) { return 100; }
+
+int f5e_check_device(void) {
+  int dev = 0;
+  F5E_CUDA_CHECK(cudaGetDevice(&dev));
+  cudaDeviceProp prop;
+  F5E_CUDA_CHECK(cudaGetDeviceProperties(&prop, dev));
+  F5E_REQUIRE(prop.major == 10, "device %d (%s) is sm_%d%d; libf5e_b200 needs sm_100a (B200)", dev, prop.name,
+              prop.major, prop.minor);
+  return 0;
+}
+
+int f5e_gemm_bf16(const void* A, int32_t lda, const void* W, int32_t ldw, int32_t M, int32_t N, int32_t K,
+                  const f5e_epilogue* ep, void* stream) {
+  F5E_REQUIRE(A && W && ep, "f5e_gemm_bf16: null argument");
+  F5E_REQUIRE(ep->out_f32 ? ep->ldo % 4 == 0 : ep->ldo % 8 == 0, "f5e_gemm_bf16: ldo=%d breaks 16-byte row alignment", ep->ldo);
+  F5E_REQUIRE(ep->residual == nullptr || ep->ldr % 8 == 0, "f5e_gemm_bf16: ldr=%d breaks 16-byte row alignment", ep->ldr);
+  return gemm_bf16((cudaStream_t)stream, (const __nv_bfloat16*)A, lda, (const __nv_bfloat16*)W, ldw, M, N, K,
+                   to_epi(ep, M));
+}
+
+int f5e_norm_mod(const void* x, void* out, int32_t M, int32_t D, const float* mul, const float* add,
+                 int32_t mod_stride, int32_t n_pad, float plus_one, float eps, void* stream) {
+  F5E_REQUIRE(x && out && mul && add, "f5e_norm_mod: null argument");
+  return norm_mod((cudaStream_t)stream, (const __nv_bfloat16*)x, (__nv_bfloat16*)out, M, D, mul, add, mod_stride,
+                  n_pad, plus_one, eps);
+}
+
+int f5e_cfg_euler(const float* pred, int32_t ld_pred, float* y, void* x_cat, int32_t ld_cat, float* traj,
+                  int32_t rows, int32_t C, float dt, float cfg_strength, int32_t round_bf16, void* stream) {
+  F5E_REQUIRE(pred && y, "f5e_cfg_euler: null argument");
+  return cfg_euler((cudaStream_t)stream, pred, ld_pred, y, (__nv_bfloat16*)x_cat, ld_cat, traj, rows, C, dt,
+                   cfg_strength, round_bf16);
+}
+
+}  // extern "C"

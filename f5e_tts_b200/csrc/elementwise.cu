@@ -1,0 +1,133 @@
+// Bandwidth-bound kernels of the DiT step: modulated LayerNorm and the fused CFG + Euler update.
+// All accesses are 16-byte vectorised and coalesced; reductions are warp shuffles (one warp per row).
+#include "host.h"
+
+namespace f5e {
+
+// ---------------------------------------------------------------------------------------------
+// norm_mod: out = LN(x) * (plus_one + mul) + add      (reference model/modules.py:301-336, :636)
+// One warp per row; each lane keeps CH chunks of 8 bf16 in registers (D = 256 * CH).
+// Algorithmic bytes: 2 * M * D * 2.
+// ---------------------------------------------------------------------------------------------
+template <int CH>
+__global__ void __launch_bounds__(256)
+norm_mod_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, int M,
+                const float* __restrict__ mul, const float* __restrict__ add, int mod_stride, int n_pad,
+                float plus_one, float eps) {
+  constexpr int D = CH * 256;
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= M) return;
+  const uint4* xr = reinterpret_cast<const uint4*>(x + (size_t)row * D);
+  float v[CH][8];
+  float sum = 0.f;
+#pragma unroll
+  for (int c = 0; c < CH; ++c) {
+    uint4 u = xr[c * 32 + lane];
+    float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+    v[c][0] = a.x; v[c][1] = a.y; v[c][2] = b.x; v[c][3] = b.y;
+    v[c][4] = cc.x; v[c][5] = cc.y; v[c][6] = d.x; v[c][7] = d.y;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) sum += v[c][i];
+  }
+  const float mean = warp_sum(sum) * (1.0f / D);
+  float sq = 0.f;
+#pragma unroll
+  for (int c = 0; c < CH; ++c)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float d = v[c][i] - mean;
+      sq += d * d;
+    }
+  const float rstd = rsqrtf(warp_sum(sq) * (1.0f / D) + eps);
+  const size_t moff = mod_stride ? (size_t)(row / n_pad) * mod_stride : 0;
+  const float4* mp = reinterpret_cast<const float4*>(mul + moff);
+  const float4* ap = reinterpret_cast<const float4*>(add + moff);
+  uint4* orow = reinterpret_cast<uint4*>(out + (size_t)row * D);
+#pragma unroll
+  for (int c = 0; c < CH; ++c) {
+    const int e4 = (c * 32 + lane) * 2;  // float4 index of the first of 8 elements
+    float4 m0 = __ldg(mp + e4), m1 = __ldg(mp + e4 + 1), a0 = __ldg(ap + e4), a1 = __ldg(ap + e4 + 1);
+    float m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+    float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+    float r[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r[i] = (v[c][i] - mean) * rstd * (plus_one + m[i]) + a[i];
+    uint4 u;
+    u.x = pack_bf16x2(r[0], r[1]); u.y = pack_bf16x2(r[2], r[3]);
+    u.z = pack_bf16x2(r[4], r[5]); u.w = pack_bf16x2(r[6], r[7]);
+    orow[c * 32 + lane] = u;
+  }
+}
+
+int norm_mod(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int M, int D, const float* mul,
+             const float* add, int mod_stride, int n_pad, float plus_one, float eps) {
+  F5E_REQUIRE(M > 0, "norm_mod: M must be positive");
+  F5E_REQUIRE(D % 256 == 0 && D >= 256 && D <= 2048, "norm_mod: D=%d must be a multiple of 256 in [256,2048]", D);
+  if (n_pad <= 0) n_pad = M;
+  const int grid = (M + 7) / 8;
+#define F5E_NM(CH)                                                                                             \
+  case CH:                                                                                                     \
+    norm_mod_kernel<CH><<<grid, 256, 0, st>>>(x, out, M, mul, add, mod_stride, n_pad, plus_one, eps);          \
+    break;
+  switch (D / 256) {
+    F5E_NM(1) F5E_NM(2) F5E_NM(3) F5E_NM(4) F5E_NM(5) F5E_NM(6) F5E_NM(7) F5E_NM(8)
+  }
+#undef F5E_NM
+  F5E_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// cfg_euler: v = pc + (pc - pu) * cfg ; y += dt * v     (reference model/cfm.py:431-447 + Euler)
+// Algorithmic bytes: rows*C*(2 pred reads + y read + y write)*4 (+ 2 bf16 writes into x_cat).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+cfg_euler_kernel(const float* __restrict__ pred, int ld_pred, float* __restrict__ y,
+                 __nv_bfloat16* __restrict__ x_cat, int ld_cat, float* __restrict__ traj, int rows, int C,
+                 float dt, float cfg, int round_bf16) {
+  const int quads = C >> 2;  // C % 4 == 0
+  const long long total = (long long)rows * quads;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)(idx / quads), q = (int)(idx - (long long)r * quads);
+    const float4 pc = *reinterpret_cast<const float4*>(pred + (size_t)r * ld_pred + q * 4);
+    float4 v = pc;
+    if (cfg >= 1e-5f) {
+      const float4 pu = *reinterpret_cast<const float4*>(pred + ((size_t)rows + r) * ld_pred + q * 4);
+      v.x = pc.x + (pc.x - pu.x) * cfg; v.y = pc.y + (pc.y - pu.y) * cfg;
+      v.z = pc.z + (pc.z - pu.z) * cfg; v.w = pc.w + (pc.w - pu.w) * cfg;
+    }
+    float4* yp = reinterpret_cast<float4*>(y + (size_t)r * C + q * 4);
+    float4 yy = *yp;
+    yy.x += dt * v.x; yy.y += dt * v.y; yy.z += dt * v.z; yy.w += dt * v.w;
+    if (round_bf16) {
+      yy.x = __bfloat162float(__float2bfloat16(yy.x)); yy.y = __bfloat162float(__float2bfloat16(yy.y));
+      yy.z = __bfloat162float(__float2bfloat16(yy.z)); yy.w = __bfloat162float(__float2bfloat16(yy.w));
+    }
+    *yp = yy;
+    if (traj) *reinterpret_cast<float4*>(traj + (size_t)r * C + q * 4) = yy;
+    if (x_cat) {
+      uint2 u;
+      u.x = pack_bf16x2(yy.x, yy.y);
+      u.y = pack_bf16x2(yy.z, yy.w);
+      *reinterpret_cast<uint2*>(x_cat + (size_t)r * ld_cat + q * 4) = u;
+      *reinterpret_cast<uint2*>(x_cat + ((size_t)rows + r) * ld_cat + q * 4) = u;
+    }
+  }
+}
+
+int cfg_euler(cudaStream_t st, const float* pred, int ld_pred, float* y, __nv_bfloat16* x_cat, int ld_cat,
+              float* traj, int rows, int C, float dt, float cfg, int round_bf16) {
+  F5E_REQUIRE(rows > 0 && C > 0 && C % 4 == 0, "cfg_euler: need rows>0 and C%%4==0 (rows=%d C=%d)", rows, C);
+  F5E_REQUIRE(ld_pred % 4 == 0 && (x_cat == nullptr || ld_cat % 4 == 0), "cfg_euler: leading dims must be multiples of 4");
+  const long long total = (long long)rows * (C / 4);
+  int grid = (int)((total + 255) / 256);
+  const int cap = num_sms() * 8;
+  if (grid > cap) grid = cap;
+  cfg_euler_kernel<<<grid, 256, 0, st>>>(pred, ld_pred, y, x_cat, ld_cat, traj, rows, C, dt, cfg, round_bf16);
+  F5E_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace f5e

@@ -1,0 +1,173 @@
+// Fused GEMM epilogue shared by the dense GEMM and the grouped-conv implicit GEMM.
+// One thread owns one output row and handles 32 consecutive fp32 accumulator columns at a time
+// (that is exactly what tcgen05.ld 32x32b.x32 hands it), so everything row-wise (RoPE pair
+// rotation, row masks) is register-local.
+#pragma once
+#include "common.cuh"
+
+namespace f5e {
+
+enum Act : int { ACT_NONE = 0, ACT_GELU_TANH = 1, ACT_GELU_ERF = 2, ACT_MISH = 3, ACT_RELU = 4, ACT_SILU = 5 };
+
+struct EpiParams {
+  void* out;                       // [M, ldo] bf16 (or fp32 when out_f32)
+  int ldo;
+  int out_f32;
+  const float* bias;               // [N] or null
+  int act;                         // Act
+  const float* gate;               // [N] or null : v *= gate[sample * gate_stride + col]
+  int gate_stride;                 // 0 = one gate vector shared by every sample
+  const __nv_bfloat16* residual;   // [M, ldr] or null : v += residual
+  int ldr;
+  const int* row_len;              // [M / n_pad] or null : rows with (row % n_pad) >= row_len[row / n_pad] -> 0
+  int n_pad;                       // frames per sample (row -> (sample, frame)); needed by row_len / rope
+  const float* rope_cos;           // [n_pad, 32] or null (interleaved-pair RoPE, dim_head 64)
+  const float* rope_sin;
+  int rope_inner;                  // heads*64 (columns [0, 2*rope_inner) hold Q then K)
+  int rope_heads;                  // heads [0, rope_heads) of Q and of K get rotated
+};
+
+// v: 32 accumulator values for (row, col0 .. col0+31).  M/N are the logical output extents.
+__device__ __forceinline__ void epilogue_chunk(float (&v)[32], int row, int col0, int M, int N,
+                                               const EpiParams& p) {
+  if (row >= M || col0 >= N) return;
+  const bool full = (col0 + 32 <= N);
+
+  if (p.bias) {
+    if (full) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) {
+        float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + i));
+        v[i] += b.x; v[i + 1] += b.y; v[i + 2] += b.z; v[i + 3] += b.w;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (col0 + i < N) v[i] += __ldg(p.bias + col0 + i);
+    }
+  }
+
+  if (p.rope_cos) {
+    const int inner = p.rope_inner;
+    if (col0 < 2 * inner) {
+      const int c = col0 % inner;
+      const int head = c >> 6;
+      if (head < p.rope_heads) {
+        const int n = row % p.n_pad;
+        const int j0 = (c & 63) >> 1;  // first frequency index of this chunk (0 or 16)
+        const float4* cp = reinterpret_cast<const float4*>(p.rope_cos + (size_t)n * 32 + j0);
+        const float4* sp = reinterpret_cast<const float4*>(p.rope_sin + (size_t)n * 32 + j0);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          float4 c4 = __ldg(cp + q), s4 = __ldg(sp + q);
+          float cs[4] = {c4.x, c4.y, c4.z, c4.w}, sn[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int i = (q * 4 + k) * 2;
+            const float a = v[i], b = v[i + 1];
+            v[i] = a * cs[k] - b * sn[k];
+            v[i + 1] = b * cs[k] + a * sn[k];
+          }
+        }
+      }
+    }
+  }
+
+  switch (p.act) {
+    case ACT_GELU_TANH:
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = gelu_tanh(v[i]);
+      break;
+    case ACT_GELU_ERF:
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+      break;
+    case ACT_MISH:
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = mish(v[i]);
+      break;
+    case ACT_RELU:
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.0f);
+      break;
+    case ACT_SILU:
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = silu(v[i]);
+      break;
+    default:
+      break;
+  }
+
+  if (p.row_len) {
+    const int s = row / p.n_pad, n = row - s * p.n_pad;
+    if (n >= __ldg(p.row_len + s)) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = 0.0f;
+    }
+  }
+
+  if (p.gate) {
+    const float* gate = p.gate + (p.gate_stride ? (size_t)(row / p.n_pad) * p.gate_stride : 0);
+    if (full) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) {
+        float4 g = __ldg(reinterpret_cast<const float4*>(gate + col0 + i));
+        v[i] *= g.x; v[i + 1] *= g.y; v[i + 2] *= g.z; v[i + 3] *= g.w;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (col0 + i < N) v[i] *= __ldg(gate + col0 + i);
+    }
+  }
+
+  if (p.residual) {
+    const __nv_bfloat16* r = p.residual + (size_t)row * p.ldr + col0;
+    if (full) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 8) {
+        uint4 u = *reinterpret_cast<const uint4*>(r + i);
+        float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z),
+               d = unpack_bf16x2(u.w);
+        v[i] += a.x; v[i + 1] += a.y; v[i + 2] += b.x; v[i + 3] += b.y;
+        v[i + 4] += c.x; v[i + 5] += c.y; v[i + 6] += d.x; v[i + 7] += d.y;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (col0 + i < N) v[i] += __bfloat162float(r[i]);
+    }
+  }
+
+  if (p.out_f32) {
+    float* o = reinterpret_cast<float*>(p.out) + (size_t)row * p.ldo + col0;
+    if (full) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 4)
+        *reinterpret_cast<float4*>(o + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (col0 + i < N) o[i] = v[i];
+    }
+  } else {
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.ldo + col0;
+    if (full) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 8) {
+        uint4 u;
+        u.x = pack_bf16x2(v[i], v[i + 1]);
+        u.y = pack_bf16x2(v[i + 2], v[i + 3]);
+        u.z = pack_bf16x2(v[i + 4], v[i + 5]);
+        u.w = pack_bf16x2(v[i + 6], v[i + 7]);
+        *reinterpret_cast<uint4*>(o + i) = u;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (col0 + i < N) o[i] = __float2bfloat16(v[i]);
+    }
+  }
+}
+
+}  // namespace f5e

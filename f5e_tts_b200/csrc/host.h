@@ -1,0 +1,33 @@
+// Host-side internal interfaces between the translation units of libf5e_b200.so.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include "epilogue.cuh"
+
+namespace f5e {
+
+int num_sms();
+
+// 2-D row-major tensor map with 128-byte swizzle; `elem_bytes` 2 (bf16) or 4 (fp32/tf32).
+// box_inner * elem_bytes must be 128.
+int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t inner, uint64_t outer,
+                 uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer);
+// 3-D map over [d2][d1][inner] (used for [sample][frame][channel] views where out-of-range frames
+// of ONE sample must read as zero instead of bleeding into the neighbouring sample).
+int make_tmap_3d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t inner, uint64_t d1,
+                 uint64_t d2, uint64_t stride1_bytes, uint64_t stride2_bytes, uint32_t box_inner,
+                 uint32_t box1, uint32_t box2);
+
+// C[M,N] = epilogue(A[M,K] @ W[N,K]^T)   (bf16 operands, fp32 accumulation in TMEM)
+int gemm_bf16(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloat16* W, int ldw, int M,
+              int N, int K, const EpiParams& ep);
+
+int norm_mod(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int M, int D, const float* mul,
+             const float* add, int mod_stride, int n_pad, float plus_one, float eps);
+int cfg_euler(cudaStream_t st, const float* pred, int ld_pred, float* y, __nv_bfloat16* x_cat, int ld_cat,
+              float* traj, int rows, int C, float dt, float cfg, int round_bf16);
+const char* last_error();
+
+}  // namespace f5e

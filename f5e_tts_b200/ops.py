@@ -1,0 +1,71 @@
+"""Thin tensor-level wrappers over the C ABI (test hooks and building blocks of the drop-in modules).
+
+torch is used only for device memory and the current stream; every op runs a hand-written sm_100a kernel.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import Epilogue, check, ptr, stream_ptr
+
+
+def _cuda_bf16(t: torch.Tensor, name: str) -> None:
+    if not (t.is_cuda and t.dtype == torch.bfloat16):
+        raise RuntimeError(f"{name} must be a CUDA bfloat16 tensor (got {t.device}, {t.dtype}); there is no CPU path")
+
+
+def gemm(a, w, *, bias=None, act=_lib.ACT_NONE, gate=None, gate_stride=0, residual=None, row_len=None, n_pad=0,
+         rope=None, rope_heads=0, rope_inner=0, out=None, out_f32=False, n=None):
+    """epilogue(a[M,K] @ w[N,K]^T).  `a`/`w` may be row-strided views (last dim contiguous)."""
+    _cuda_bf16(a, "a"), _cuda_bf16(w, "w")
+    assert a.dim() == 2 and w.dim() == 2 and a.stride(1) == 1 and w.stride(1) == 1
+    M, K = a.shape
+    N = w.shape[0] if n is None else n
+    assert w.shape[1] == K
+    if out is None:
+        out = torch.empty(M, N, device=a.device, dtype=torch.float32 if out_f32 else torch.bfloat16)
+    ep = Epilogue()
+    ep.out, ep.ldo, ep.out_f32 = out.data_ptr(), out.stride(0), int(out.dtype == torch.float32)
+    ep.bias = 0 if bias is None else bias.data_ptr()
+    ep.act = act
+    ep.gate = 0 if gate is None else gate.data_ptr()
+    ep.gate_stride = gate_stride
+    ep.residual = 0 if residual is None else residual.data_ptr()
+    ep.ldr = 0 if residual is None else residual.stride(0)
+    ep.row_len = 0 if row_len is None else row_len.data_ptr()
+    ep.n_pad = n_pad
+    if rope is not None:
+        ep.rope_cos, ep.rope_sin = rope[0].data_ptr(), rope[1].data_ptr()
+        ep.rope_inner, ep.rope_heads = rope_inner, rope_heads
+    for t in (bias, gate):
+        assert t is None or t.dtype == torch.float32
+    assert row_len is None or row_len.dtype == torch.int32
+    check(_lib.load().f5e_gemm_bf16(ptr(a), a.stride(0), ptr(w), w.stride(0), M, N, K, C.byref(ep), stream_ptr()),
+          "f5e_gemm_bf16")
+    return out
+
+
+def norm_mod(x, mul, add, *, plus_one=1.0, eps=1e-6, mod_stride=0, n_pad=0, out=None):
+    _cuda_bf16(x, "x")
+    assert x.is_contiguous() and mul.dtype == torch.float32 and add.dtype == torch.float32
+    D = x.shape[-1]
+    M = x.numel() // D
+    if out is None:
+        out = torch.empty_like(x)
+    check(_lib.load().f5e_norm_mod(ptr(x), ptr(out), M, D, ptr(mul), ptr(add), mod_stride, n_pad,
+                                   C.c_float(plus_one), C.c_float(eps), stream_ptr()), "f5e_norm_mod")
+    return out
+
+
+def cfg_euler(pred, y, dt, cfg, *, x_cat=None, traj=None, round_bf16=False):
+    """In-place y += dt * (pc + (pc - pu) * cfg); pred is fp32 [2, rows, ld]."""
+    assert pred.dtype == torch.float32 and y.dtype == torch.float32 and y.is_contiguous()
+    rows, Cc = y.numel() // y.shape[-1], y.shape[-1]
+    ld_pred = pred.stride(-2)
+    check(_lib.load().f5e_cfg_euler(ptr(pred), ld_pred, ptr(y), ptr(x_cat), 0 if x_cat is None else x_cat.stride(-2),
+                                    ptr(traj), rows, Cc, C.c_float(dt), C.c_float(cfg), int(round_bf16),
+                                    stream_ptr()), "f5e_cfg_euler")
+    return y

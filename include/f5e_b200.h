@@ -1,0 +1,75 @@
+/* libf5e_b200.so - C ABI of the B200-native (sm_100a) F5E-TTS inference hot path.
+ *
+ * The reference (kaleo996/F5E-TTS) has no FFI: its boundary is the Python object protocol
+ * (CFM.sample, DiT.sample, MelSpec.forward, GumbelVectorQuantizer.forward, vocoder.decode).  The
+ * Python mirror of those objects lives in f5e_tts_b200/ and reaches the GPU ONLY through the entry
+ * points below (ctypes).  Every entry point cites the reference code it replaces (paths relative to
+ * the reference's src/f5_tts/).
+ *
+ * Conventions
+ *  - all pointers are DEVICE pointers unless the name ends in _host; the caller owns every buffer;
+ *  - `stream` is a cudaStream_t passed as void*; no call synchronises unless documented;
+ *  - return 0 on success, negative on error; f5e_last_error() gives the message (thread local);
+ *  - there is NO CPU fallback: a missing/incompatible device is an error.
+ */
+#ifndef F5E_B200_H
+#define F5E_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* f5e_last_error(void);
+/* 0 when the current device is compute capability 10.x, else an error (message says what it is). */
+int f5e_check_device(void);
+int f5e_version(void);
+
+/* ---- activation ids for f5e_epilogue.act ---- */
+enum { F5E_ACT_NONE = 0, F5E_ACT_GELU_TANH = 1, F5E_ACT_GELU_ERF = 2, F5E_ACT_MISH = 3, F5E_ACT_RELU = 4,
+       F5E_ACT_SILU = 5 };
+
+/* Fused GEMM epilogue:  v = acc + bias ; RoPE(v) ; act(v) ; row-mask ; v *= gate ; v += residual ; store */
+typedef struct f5e_epilogue {
+  void* out;               /* [M, ldo] bf16, or fp32 when out_f32 != 0 */
+  int32_t ldo;
+  int32_t out_f32;
+  const float* bias;       /* [N] or NULL */
+  int32_t act;
+  const float* gate;       /* [N] (or [samples, gate_stride]) or NULL */
+  int32_t gate_stride;
+  const void* residual;    /* bf16 [M, ldr] or NULL */
+  int32_t ldr;
+  const int32_t* row_len;  /* [M / n_pad] valid frames per sample, or NULL (rows beyond are zeroed) */
+  int32_t n_pad;           /* frames per sample */
+  const float* rope_cos;   /* [n_pad, 32] or NULL */
+  const float* rope_sin;
+  int32_t rope_inner;      /* heads * 64 */
+  int32_t rope_heads;      /* rotate heads [0, rope_heads) of Q and K */
+} f5e_epilogue;
+
+/* C[M,N] = epilogue(A[M,K] @ W[N,K]^T); bf16 operands, tcgen05 / TMEM fp32 accumulation.
+ * Replaces F.linear at model/modules.py:442-449, :494, :342-353; backbones/dit.py:169-177, :470. */
+int f5e_gemm_bf16(const void* A, int32_t lda, const void* W, int32_t ldw, int32_t M, int32_t N, int32_t K,
+                  const f5e_epilogue* ep, void* stream);
+
+/* out[r,:] = LN(x[r,:]; eps, no affine) * (plus_one + mul[s,:]) + add[s,:], s = r / n_pad when
+ * mod_stride != 0 else shared.  bf16 in/out, fp32 statistics.  D must be a multiple of 256.
+ * Replaces AdaLayerNorm / AdaLayerNorm_Final / ff_norm modulate (model/modules.py:301-336, :636)
+ * and, with plus_one = 0, nn.LayerNorm with affine (modules.py:258). */
+int f5e_norm_mod(const void* x, void* out, int32_t M, int32_t D, const float* mul, const float* add,
+                 int32_t mod_stride, int32_t n_pad, float plus_one, float eps, void* stream);
+
+/* Fused classifier-free-guidance combine + Euler update (model/cfm.py:431-447 + torchdiffeq Euler):
+ *   v = pc + (pc - pu) * cfg ;  y += dt * v
+ * pred: fp32 [2, rows, ld_pred] (cond half, then uncond half; when cfg_strength < 1e-5 only the
+ * first half is read).  y: fp32 [rows, C] state, updated in place.  x_cat: bf16 [2*rows, ld_cat]
+ * concat buffer whose first C columns receive the new state for BOTH halves (NULL to skip).
+ * traj: optional fp32 [rows, C] snapshot.  round_bf16 != 0 reproduces a bf16-carried state. */
+int f5e_cfg_euler(const float* pred, int32_t ld_pred, float* y, void* x_cat, int32_t ld_cat, float* traj,
+                  int32_t rows, int32_t C, float dt, float cfg_strength, int32_t round_bf16, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* F5E_B200_H */

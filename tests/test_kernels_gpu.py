@@ -1,0 +1,103 @@
+"""Kernel-level parity on the GPU, through the C ABI, against plain torch fp32 math of the same op."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def rel_l2(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).norm() / b.norm().clamp_min(1e-12)).item()
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (300, 1024, 1024), (1000, 3072, 1024), (777, 100, 1024),
+                                   (2056, 2048, 712), (33, 512, 256)])
+def test_gemm_bias(cuda_dev, M, N, K):
+    from f5e_tts_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    a = torch.randn(M, K, device=cuda_dev, generator=g).bfloat16()
+    w = (torch.randn(N, K, device=cuda_dev, generator=g) / math.sqrt(K)).bfloat16()
+    b = torch.randn(N, device=cuda_dev, generator=g)
+    f32 = (N % 8 != 0)
+    out = ops.gemm(a, w, bias=b, out_f32=f32)
+    ref = a.float() @ w.float().t() + b
+    torch.cuda.synchronize()
+    assert rel_l2(out, ref) < (1e-5 if f32 else 4e-3), rel_l2(out, ref)
+    assert (out.float() - ref).abs().max().item() < (1e-3 if f32 else 0.06)
+
+
+def test_gemm_full_epilogue(cuda_dev):
+    from f5e_tts_b200 import ops, _lib
+    torch.manual_seed(1)
+    B, n_pad, D = 3, 200, 1024
+    M = B * n_pad
+    a = torch.randn(M, D, device=cuda_dev).bfloat16()
+    w = (torch.randn(D, D, device=cuda_dev) / 32).bfloat16()
+    bias = torch.randn(D, device=cuda_dev)
+    gate = torch.randn(D, device=cuda_dev)
+    res = torch.randn(M, D, device=cuda_dev).bfloat16()
+    lens = torch.tensor([200, 150, 7], device=cuda_dev, dtype=torch.int32)
+    out = ops.gemm(a, w, bias=bias, act=_lib.ACT_GELU_TANH, gate=gate, residual=res, row_len=lens, n_pad=n_pad)
+    v = torch.nn.functional.gelu(a.float() @ w.float().t() + bias, approximate="tanh")
+    valid = (torch.arange(n_pad, device=cuda_dev)[None] < lens[:, None]).reshape(M, 1)
+    ref = res.float() + gate * torch.where(valid, v, torch.zeros_like(v))
+    assert rel_l2(out, ref) < 4e-3
+
+
+def test_gemm_qkv_rope(cuda_dev):
+    from f5e_tts_b200 import ops
+    torch.manual_seed(2)
+    B, n_pad, D, H = 2, 333, 1024, 16
+    M = B * n_pad
+    a = torch.randn(M, D, device=cuda_dev).bfloat16()
+    w = (torch.randn(3 * D, D, device=cuda_dev) / 32).bfloat16()
+    bias = torch.randn(3 * D, device=cuda_dev)
+    inv = 1.0 / (10000 ** (torch.arange(0, 64, 2, device=cuda_dev).float() / 64))
+    ang = torch.arange(n_pad, device=cuda_dev).float()[:, None] * inv[None]
+    cos, sin = ang.cos().contiguous(), ang.sin().contiguous()
+    for heads in (16, 1):
+        out = ops.gemm(a, w, bias=bias, rope=(cos, sin), rope_heads=heads, rope_inner=D, n_pad=n_pad)
+        y = (a.float() @ w.float().t() + bias).view(B, n_pad, 3, H, 32, 2)
+        c, s = cos[None, :, None, :], sin[None, :, None, :]
+        ref = y.clone()
+        for part in (0, 1):
+            xa, xb = y[:, :, part, :heads, :, 0], y[:, :, part, :heads, :, 1]
+            ref[:, :, part, :heads, :, 0] = xa * c - xb * s
+            ref[:, :, part, :heads, :, 1] = xb * c + xa * s
+        assert rel_l2(out, ref.reshape(M, 3 * D)) < 4e-3
+
+
+@pytest.mark.parametrize("D", [512, 768, 1024])
+def test_norm_mod(cuda_dev, D):
+    from f5e_tts_b200 import ops
+    torch.manual_seed(3)
+    B, n_pad = 4, 123
+    x = (torch.randn(B, n_pad, D, device=cuda_dev) * 3 + 1).bfloat16()
+    mul = torch.randn(B, D, device=cuda_dev)
+    add = torch.randn(B, D, device=cuda_dev)
+    ln = torch.nn.functional.layer_norm(x.float(), (D,), eps=1e-6)
+    out = ops.norm_mod(x, mul[0], add[0])
+    assert rel_l2(out, ln * (1 + mul[0]) + add[0]) < 3e-3
+    out = ops.norm_mod(x, mul, add, mod_stride=D, n_pad=n_pad)
+    assert rel_l2(out, ln * (1 + mul[:, None]) + add[:, None]) < 3e-3
+    out = ops.norm_mod(x, mul[0], add[0], plus_one=0.0)
+    assert rel_l2(out, ln * mul[0] + add[0]) < 3e-3
+
+
+def test_cfg_euler(cuda_dev):
+    from f5e_tts_b200 import ops
+    torch.manual_seed(4)
+    rows, Cc = 1000, 100
+    pred = torch.randn(2, rows, Cc, device=cuda_dev)
+    y = torch.randn(rows, Cc, device=cuda_dev)
+    y0 = y.clone()
+    xcat = torch.zeros(2 * rows, 712, device=cuda_dev, dtype=torch.bfloat16)
+    traj = torch.empty(rows, Cc, device=cuda_dev)
+    ops.cfg_euler(pred, y, 0.03, 2.0, x_cat=xcat, traj=traj)
+    ref = y0 + 0.03 * (pred[0] + (pred[0] - pred[1]) * 2.0)
+    assert torch.allclose(y, ref, atol=1e-6, rtol=1e-6)
+    assert torch.equal(traj, y)
+    assert torch.equal(xcat[:rows, :100], y.bfloat16()) and torch.equal(xcat[rows:, :100], y.bfloat16())
+    assert xcat[:, 100:].abs().max().item() == 0
