@@ -54,4 +54,11 @@ int f5e_cfg_euler(const float* pred, int32_t ld_pred, float* y, void* x_cat, int
                    cfg_strength, round_bf16);
 }
 
+int f5e_attention(const void* qkv, int32_t ld_qkv, void* out, int32_t ldo, const int32_t* klen, int32_t samples,
+                  int32_t n_pad, int32_t heads, float scale, void* stream) {
+  F5E_REQUIRE(qkv && out, "f5e_attention: null argument");
+  return attention((cudaStream_t)stream, (const __nv_bfloat16*)qkv, ld_qkv, (__nv_bfloat16*)out, ldo, klen, samples,
+                   n_pad, heads, scale);
+}
+
 }  // extern "C"

@@ -28,6 +28,9 @@ int norm_mod(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int M,
              const float* add, int mod_stride, int n_pad, float plus_one, float eps);
 int cfg_euler(cudaStream_t st, const float* pred, int ld_pred, float* y, __nv_bfloat16* x_cat, int ld_cat,
               float* traj, int rows, int C, float dt, float cfg, int round_bf16);
+// o[rows, inner] = softmax(q k^T * scale, keys < klen[sample]) v over qkv[rows, 3*inner] (Q|K|V column blocks)
+int attention(cudaStream_t st, const __nv_bfloat16* qkv, int ld_qkv, __nv_bfloat16* out, int ldo, const int* klen,
+              int samples, int n_pad, int heads, float scale);
 const char* last_error();
 
 }  // namespace f5e

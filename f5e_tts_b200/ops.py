@@ -69,3 +69,19 @@ def cfg_euler(pred, y, dt, cfg, *, x_cat=None, traj=None, round_bf16=False):
                                     ptr(traj), rows, Cc, C.c_float(dt), C.c_float(cfg), int(round_bf16),
                                     stream_ptr()), "f5e_cfg_euler")
     return y
+
+
+def attention(qkv, heads, *, klen=None, n_pad=None, scale=None, out=None):
+    """qkv: bf16 [samples*n_pad, 3*heads*64] -> bf16 [samples*n_pad, heads*64]."""
+    _cuda_bf16(qkv, "qkv")
+    rows = qkv.shape[0]
+    inner = heads * 64
+    assert qkv.shape[1] == 3 * inner and qkv.stride(1) == 1
+    n_pad = rows if n_pad is None else n_pad
+    samples = rows // n_pad
+    if out is None:
+        out = torch.zeros(rows, inner, device=qkv.device, dtype=torch.bfloat16)
+    assert klen is None or (klen.dtype == torch.int32 and klen.numel() == samples)
+    check(_lib.load().f5e_attention(ptr(qkv), qkv.stride(0), ptr(out), out.stride(0), ptr(klen), samples, n_pad, heads,
+                                    C.c_float(scale if scale is not None else 0.125), stream_ptr()), "f5e_attention")
+    return out

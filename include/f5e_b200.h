@@ -69,6 +69,13 @@ int f5e_norm_mod(const void* x, void* out, int32_t M, int32_t D, const float* mu
 int f5e_cfg_euler(const float* pred, int32_t ld_pred, float* y, void* x_cat, int32_t ld_cat, float* traj,
                   int32_t rows, int32_t C, float dt, float cfg_strength, int32_t round_bf16, void* stream);
 
+/* Non-causal flash attention, dim_head 64, keys n >= klen[sample] masked (klen NULL = no mask).
+ * qkv: bf16 [samples*n_pad, ld_qkv] with column blocks Q | K | V of heads*64 each (RoPE already applied);
+ * out: bf16 [samples*n_pad, ldo] (heads merged).  Query tiles entirely beyond klen are not written.
+ * Replaces F.scaled_dot_product_attention + expanded bool mask at model/modules.py:483-492. */
+int f5e_attention(const void* qkv, int32_t ld_qkv, void* out, int32_t ldo, const int32_t* klen, int32_t samples,
+                  int32_t n_pad, int32_t heads, float scale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

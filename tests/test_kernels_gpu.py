@@ -101,3 +101,24 @@ def test_cfg_euler(cuda_dev):
     assert torch.equal(traj, y)
     assert torch.equal(xcat[:rows, :100], y.bfloat16()) and torch.equal(xcat[rows:, :100], y.bfloat16())
     assert xcat[:, 100:].abs().max().item() == 0
+
+
+@pytest.mark.parametrize("samples,n_pad,heads,lens", [(1, 128, 1, None), (2, 300, 4, [300, 129]),
+                                                       (3, 1031, 16, [1031, 850, 5]), (1, 940, 16, None)])
+def test_attention(cuda_dev, samples, n_pad, heads, lens):
+    from f5e_tts_b200 import ops
+    torch.manual_seed(5)
+    inner = heads * 64
+    qkv = torch.randn(samples * n_pad, 3 * inner, device=cuda_dev).bfloat16()
+    klen = None if lens is None else torch.tensor(lens, device=cuda_dev, dtype=torch.int32)
+    out = ops.attention(qkv, heads, klen=klen, n_pad=n_pad)
+    q, k, v = qkv.float().view(samples, n_pad, 3, heads, 64).permute(2, 0, 3, 1, 4)
+    s = (q @ k.transpose(-1, -2)) * 0.125
+    if lens is not None:
+        km = torch.arange(n_pad, device=cuda_dev)[None] < klen[:, None]
+        s = s.masked_fill(~km[:, None, None, :], float("-inf"))
+    ref = (s.softmax(-1) @ v).permute(0, 2, 1, 3).reshape(samples, n_pad, inner)
+    o = out.view(samples, n_pad, inner).float()
+    for i in range(samples):
+        L = n_pad if lens is None else lens[i]
+        assert rel_l2(o[i, :L], ref[i, :L]) < 1e-2, (i, rel_l2(o[i, :L], ref[i, :L]))
