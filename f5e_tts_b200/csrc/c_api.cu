@@ -61,4 +61,14 @@ int f5e_attention(const void* qkv, int32_t ld_qkv, void* out, int32_t ldo, const
                    n_pad, heads, scale);
 }
 
+int f5e_conv_pos(const void* x, const void* w_packed, int32_t samples, int32_t n_pad, int32_t dim, int32_t groups,
+                 const f5e_epilogue* ep, void* stream) {
+  F5E_REQUIRE(x && w_packed && ep && ep->out, "f5e_conv_pos: null argument");
+  F5E_REQUIRE(ep->ldo % 8 == 0 && (ep->residual == nullptr || ep->ldr % 8 == 0), "f5e_conv_pos: unaligned leading dim");
+  EpiParams p = to_epi(ep, samples * n_pad);
+  p.n_pad = n_pad;
+  return conv_pos((cudaStream_t)stream, (const __nv_bfloat16*)x, (const __nv_bfloat16*)w_packed, samples, n_pad, dim,
+                  groups, p);
+}
+
 }  // extern "C"

@@ -31,6 +31,9 @@ int cfg_euler(cudaStream_t st, const float* pred, int ld_pred, float* y, __nv_bf
 // o[rows, inner] = softmax(q k^T * scale, keys < klen[sample]) v over qkv[rows, 3*inner] (Q|K|V column blocks)
 int attention(cudaStream_t st, const __nv_bfloat16* qkv, int ld_qkv, __nv_bfloat16* out, int ldo, const int* klen,
               int samples, int n_pad, int heads, float scale);
+// grouped conv k=31 as implicit GEMM; wp = packed weights [31*dim, 64]
+int conv_pos(cudaStream_t st, const __nv_bfloat16* x, const __nv_bfloat16* wp, int samples, int n_pad, int dim,
+             int groups, const EpiParams& ep);
 const char* last_error();
 
 }  // namespace f5e

@@ -85,3 +85,28 @@ def attention(qkv, heads, *, klen=None, n_pad=None, scale=None, out=None):
     check(_lib.load().f5e_attention(ptr(qkv), qkv.stride(0), ptr(out), out.stride(0), ptr(klen), samples, n_pad, heads,
                                     C.c_float(scale if scale is not None else 0.125), stream_ptr()), "f5e_attention")
     return out
+
+
+def pack_conv_pos_weight(w: torch.Tensor) -> torch.Tensor:
+    """[dim, cpg, 31] conv weight -> bf16 [31*dim, 64] (tap-major, input channels zero-padded to 64)."""
+    dim, cpg, taps = w.shape
+    wp = torch.zeros(taps, dim, 64, device=w.device, dtype=torch.bfloat16)
+    wp[:, :, :cpg] = w.permute(2, 0, 1).to(torch.bfloat16)
+    return wp.reshape(taps * dim, 64).contiguous()
+
+
+def conv_pos(x, w_packed, bias, samples, n_pad, *, groups=16, act=_lib.ACT_MISH, residual=None, out=None):
+    _cuda_bf16(x, "x")
+    assert x.is_contiguous() and x.dim() == 2 and x.shape[0] == samples * n_pad
+    dim = x.shape[1]
+    if out is None:
+        out = torch.empty_like(x)
+    ep = Epilogue()
+    ep.out, ep.ldo = out.data_ptr(), out.stride(0)
+    ep.bias = bias.data_ptr()
+    ep.act = act
+    ep.residual = 0 if residual is None else residual.data_ptr()
+    ep.ldr = 0 if residual is None else residual.stride(0)
+    check(_lib.load().f5e_conv_pos(ptr(x), ptr(w_packed), samples, n_pad, dim, groups, C.byref(ep), stream_ptr()),
+          "f5e_conv_pos")
+    return out

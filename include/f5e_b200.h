@@ -76,6 +76,13 @@ int f5e_cfg_euler(const float* pred, int32_t ld_pred, float* y, void* x_cat, int
 int f5e_attention(const void* qkv, int32_t ld_qkv, void* out, int32_t ldo, const int32_t* klen, int32_t samples,
                   int32_t n_pad, int32_t heads, float scale, void* stream);
 
+/* Grouped Conv1d(dim, dim, k=31, groups, padding=15) over frames, per sample, as a tcgen05 implicit GEMM with the
+ * fused epilogue (bias, Mish, residual).  x: bf16 [samples*n_pad, dim] contiguous; w_packed: bf16 [31*dim, 64]
+ * with w_packed[tap*dim + co, ci] = weight[co, ci, tap] (ci >= dim/groups zero).  Frames outside [0, n_pad) of a
+ * sample read as zero.  Replaces ConvPositionEmbedding's Conv1d+Mish pairs (model/modules.py:167-190). */
+int f5e_conv_pos(const void* x, const void* w_packed, int32_t samples, int32_t n_pad, int32_t dim, int32_t groups,
+                 const f5e_epilogue* ep, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -122,3 +122,18 @@ def test_attention(cuda_dev, samples, n_pad, heads, lens):
     for i in range(samples):
         L = n_pad if lens is None else lens[i]
         assert rel_l2(o[i, :L], ref[i, :L]) < 1e-2, (i, rel_l2(o[i, :L], ref[i, :L]))
+
+
+@pytest.mark.parametrize("samples,n_pad,dim", [(1, 128, 1024), (3, 333, 1024), (2, 200, 768)])
+def test_conv_pos(cuda_dev, samples, n_pad, dim):
+    from f5e_tts_b200 import ops
+    torch.manual_seed(6)
+    cpg = dim // 16
+    x = torch.randn(samples, n_pad, dim, device=cuda_dev).bfloat16()
+    w = (torch.randn(dim, cpg, 31, device=cuda_dev) / math.sqrt(cpg * 31)).bfloat16()
+    b = torch.randn(dim, device=cuda_dev)
+    res = torch.randn(samples * n_pad, dim, device=cuda_dev).bfloat16()
+    out = ops.conv_pos(x.view(-1, dim), ops.pack_conv_pos_weight(w), b, samples, n_pad, residual=res)
+    ref = torch.nn.functional.conv1d(x.float().transpose(1, 2), w.float(), b, padding=15, groups=16).transpose(1, 2)
+    ref = torch.nn.functional.mish(ref).reshape(-1, dim) + res.float()
+    assert rel_l2(out, ref) < 4e-3, rel_l2(out, ref)
