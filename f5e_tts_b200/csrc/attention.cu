@@ -259,19 +259,20 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __res
   }
 }
 
+int attention_configure() {
+  F5E_CUDA_CHECK(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM_TOTAL));
+  return 0;
+}
+
 int attention(cudaStream_t st, const __nv_bfloat16* qkv, int ld_qkv, __nv_bfloat16* out, int ldo, const int* klen,
               int samples, int n_pad, int heads, float scale) {
+  { int rc0 = ensure_configured(); if (rc0) return rc0; }
   F5E_REQUIRE(samples > 0 && n_pad > 0 && heads > 0, "attention: empty problem");
   F5E_REQUIRE(ldo % 8 == 0, "attention: ldo must be a multiple of 8");
   const int inner = heads * ATT_DH;
   CUtensorMap tm;
   int rc = make_tmap_2d(&tm, qkv, 2, (uint64_t)3 * inner, (uint64_t)samples * n_pad, (uint64_t)ld_qkv * 2, ATT_DH, 128);
   if (rc) return rc;
-  static bool configured = false;
-  if (!configured) {
-    F5E_CUDA_CHECK(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM_TOTAL));
-    configured = true;
-  }
   dim3 grid((n_pad + ATT_BM - 1) / ATT_BM, heads, samples);
   attention_kernel<<<grid, ATT_THREADS, ATT_SMEM_TOTAL, st>>>(tm, out, ldo, klen, n_pad, inner,
                                                               scale * 1.4426950408889634f);

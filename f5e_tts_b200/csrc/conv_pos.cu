@@ -137,9 +137,15 @@ conv_pos_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
   }
 }
 
+int conv_pos_configure() {
+  F5E_CUDA_CHECK(cudaFuncSetAttribute(conv_pos_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CV_SMEM_TOTAL));
+  return 0;
+}
+
 // x: bf16 [samples*n_pad, dim] (contiguous); wp: bf16 [31*dim, 64] packed weights.
 int conv_pos(cudaStream_t st, const __nv_bfloat16* x, const __nv_bfloat16* wp, int samples, int n_pad, int dim,
              int groups, const EpiParams& ep) {
+  { int rc0 = ensure_configured(); if (rc0) return rc0; }
   F5E_REQUIRE(samples > 0 && n_pad > 0, "conv_pos: empty problem");
   F5E_REQUIRE(dim % groups == 0, "conv_pos: dim %d not divisible by groups %d", dim, groups);
   const int cpg = dim / groups;
@@ -150,11 +156,6 @@ int conv_pos(cudaStream_t st, const __nv_bfloat16* x, const __nv_bfloat16* wp, i
   if (rc) return rc;
   rc = make_tmap_2d(&tmW, wp, 2, 64, (uint64_t)CV_TAPS * dim, 128, 64, (uint32_t)cpg);
   if (rc) return rc;
-  static bool configured = false;
-  if (!configured) {
-    F5E_CUDA_CHECK(cudaFuncSetAttribute(conv_pos_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CV_SMEM_TOTAL));
-    configured = true;
-  }
   const int tiles = samples * ((n_pad + CV_BM - 1) / CV_BM) * groups;
   const int grid = tiles < num_sms() ? tiles : num_sms();
   conv_pos_kernel<<<grid, CV_THREADS, CV_SMEM_TOTAL, st>>>(tmX, tmW, samples, n_pad, dim, cpg, ep);

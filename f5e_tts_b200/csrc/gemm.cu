@@ -151,12 +151,6 @@ template <int BN, int STAGES>
 static int launch_gemm(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& tmB, int M, int N, int K,
                        const EpiParams& ep) {
   using S = GemmSmem<BN, STAGES>;
-  static bool configured = false;
-  if (!configured) {
-    F5E_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        S::TOTAL));
-    configured = true;
-  }
   const int tiles = ((M + GEMM_BM - 1) / GEMM_BM) * ((N + BN - 1) / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
   gemm_bf16_kernel<BN, STAGES><<<grid, GEMM_THREADS, S::TOTAL, st>>>(tmA, tmB, M, N, K, ep);
@@ -164,8 +158,17 @@ static int launch_gemm(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMa
   return 0;
 }
 
+int gemm_configure() {
+  F5E_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      GemmSmem<256, 4>::TOTAL));
+  F5E_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<128, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      GemmSmem<128, 6>::TOTAL));
+  return 0;
+}
+
 int gemm_bf16(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloat16* W, int ldw, int M, int N,
               int K, const EpiParams& ep) {
+  { int rc0 = ensure_configured(); if (rc0) return rc0; }
   F5E_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_bf16: empty problem (M=%d N=%d K=%d)", M, N, K);
   F5E_REQUIRE(ep.out != nullptr, "gemm_bf16: null output");
   const bool wide = N > 128;

@@ -34,6 +34,19 @@ int attention(cudaStream_t st, const __nv_bfloat16* qkv, int ld_qkv, __nv_bfloat
 // grouped conv k=31 as implicit GEMM; wp = packed weights [31*dim, 64]
 int conv_pos(cudaStream_t st, const __nv_bfloat16* x, const __nv_bfloat16* wp, int samples, int n_pad, int dim,
              int groups, const EpiParams& ep);
+int pack_cols(cudaStream_t st, __nv_bfloat16* dst, int ld_dst, int col0, const void* src, int src_is_f32, int ld_src,
+              int rows, int cols);
+int text_gather(cudaStream_t st, const int64_t* text, int samples, int nt, const __nv_bfloat16* table, const float* pos,
+                int max_pos, __nv_bfloat16* out, int n_pad, int dim, int drop, int mask_padding, int add_pos);
+int dwconv7(cudaStream_t st, const __nv_bfloat16* x, const float* w, const float* b, __nv_bfloat16* out, int samples,
+            int n_pad, int C);
+int grn(cudaStream_t st, const __nv_bfloat16* x, const float* gamma, const float* beta, __nv_bfloat16* out,
+        float* scratch, int samples, int n_pad, int C);
+// one-time per-device kernel attribute setup (opt-in shared memory sizes); idempotent
+int ensure_configured();
+int gemm_configure();
+int attention_configure();
+int conv_pos_configure();
 const char* last_error();
 
 }  // namespace f5e

@@ -28,6 +28,20 @@ int num_sms() {
   return n;
 }
 
+int ensure_configured() {
+  static std::mutex mu;
+  static bool done[64] = {};
+  int dev = 0;
+  F5E_CUDA_CHECK(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lk(mu);
+  if (dev >= 0 && dev < 64 && done[dev]) return 0;
+  int rc = gemm_configure();
+  if (!rc) rc = attention_configure();
+  if (!rc) rc = conv_pos_configure();
+  if (!rc && dev >= 0 && dev < 64) done[dev] = true;
+  return rc;
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
                                   CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,

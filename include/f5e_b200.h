@@ -83,6 +83,79 @@ int f5e_attention(const void* qkv, int32_t ld_qkv, void* out, int32_t ldo, const
 int f5e_conv_pos(const void* x, const void* w_packed, int32_t samples, int32_t n_pad, int32_t dim, int32_t groups,
                  const f5e_epilogue* ep, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * Conditioning kernels (run twice per ODE solve: cond / uncond)
+ * ------------------------------------------------------------------------------------------------- */
+/* dst[r, col0 + c] = bf16(src[r, c]) for c < cols; src NULL writes zeros.  Builds the InputEmbedding
+ * concat buffer [x | cond | text_embed | ppg_embed] (backbones/dit.py:169-175). */
+int f5e_pack_cols(void* dst, int32_t ld_dst, int32_t col0, const void* src, int32_t src_is_f32, int32_t ld_src,
+                  int32_t rows, int32_t cols, void* stream);
+/* TextEmbedding front (backbones/dit.py:54-80): ids+1, truncate/pad to n_pad with the filler 0, embedding
+ * gather, + sinusoid position table row min(n, max_pos-1), zero where (mask_padding && filler).  text: int64
+ * [samples, nt] padded with -1.  drop != 0 embeds the filler everywhere (the mask still comes from the text). */
+int f5e_text_gather(const int64_t* text, int32_t samples, int32_t nt, const void* table_bf16, const float* pos_table,
+                    int32_t max_pos, void* out_bf16, int32_t n_pad, int32_t dim, int32_t drop, int32_t mask_padding,
+                    int32_t add_pos, void* stream);
+/* Depthwise Conv1d(C, C, k=7, padding=3) + bias over frames per sample (model/modules.py:250-252). */
+int f5e_dwconv7(const void* x_bf16, const float* w, const float* b, void* out_bf16, int32_t samples, int32_t n_pad,
+                int32_t C, void* stream);
+/* GRN (model/modules.py:225-234) over all n_pad frames of each sample; scratch: fp32 [samples, C]. */
+int f5e_grn(const void* x_bf16, const float* gamma, const float* beta, void* out_bf16, float* scratch, int32_t samples,
+            int32_t n_pad, int32_t C, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * DiT evaluation and the Euler/CFG ODE loop
+ * ------------------------------------------------------------------------------------------------- */
+typedef struct f5e_dit_layer {     /* one DiTBlock (model/modules.py:610-641); weights bf16 [out, in], biases fp32 */
+  const void* w_qkv;  const float* b_qkv;   /* to_q | to_k | to_v stacked: [3*inner, dim] */
+  const void* w_out;  const float* b_out;   /* attn.to_out.0 : [dim, inner] */
+  const void* w_ff1;  const float* b_ff1;   /* ff.ff.0.0     : [ff_dim, dim] */
+  const void* w_ff2;  const float* b_ff2;   /* ff.ff.2       : [dim, ff_dim] */
+} f5e_dit_layer;
+
+typedef struct f5e_dit_model {
+  int32_t dim, depth, heads, ff_dim, in_dim, mel_dim, rope_heads, conv_groups;
+  const void* w_in;    const float* b_in;     /* input_embed.proj [dim, in_dim] */
+  const void* w_conv1; const float* b_conv1;  /* conv_pos_embed.conv1d.0, packed (see f5e_conv_pos) */
+  const void* w_conv2; const float* b_conv2;  /* conv_pos_embed.conv1d.2, packed */
+  const f5e_dit_layer* layers;                /* HOST array [depth] */
+  const void* w_proj;  const float* b_proj;   /* proj_out [mel_dim, dim] */
+} f5e_dit_model;
+
+typedef struct f5e_dit_buffers {   /* caller-allocated scratch, rows = samples * n_pad */
+  void* x_cat;    /* bf16 [rows, in_dim]  concat input (columns [0, mel_dim) = current state)      */
+  void* h0;       /* bf16 [rows, dim]                                                              */
+  void* h1;       /* bf16 [rows, dim]                                                              */
+  void* x;        /* bf16 [rows, dim]     residual stream                                          */
+  void* xn;       /* bf16 [rows, dim]                                                              */
+  void* qkv;      /* bf16 [rows, 3*heads*64]                                                       */
+  void* attn;     /* bf16 [rows, heads*64]                                                         */
+  void* ff;       /* bf16 [rows, ff_dim]                                                           */
+  float* pred;    /* fp32 [rows, mel_dim]                                                          */
+} f5e_dit_buffers;
+
+/* One flow evaluation over `samples` sequences of n_pad frames (DiT.sample after the embeddings:
+ * backbones/dit.py:450-470).  mod: fp32 modulation vectors for this time step, laid out
+ * [depth][shift_msa|scale_msa|gate_msa|shift_mlp|scale_mlp|gate_mlp][dim] then [scale|shift][dim] of norm_out
+ * (AdaLayerNorm / AdaLayerNorm_Final chunk order, model/modules.py:310-315, 331-336); mod_stride = 0 when every
+ * sample shares the time step, else the per-sample stride in floats.  klen: int32 [samples] valid frames
+ * (attention key mask + zeroing of the attention branch on padded rows), NULL = no mask (batch 1).
+ * rope_cos/sin: fp32 [n_pad, 32].  Result in buf->pred. */
+int f5e_dit_forward(const f5e_dit_model* model, const f5e_dit_buffers* buf, const float* mod, int32_t mod_stride,
+                    const int32_t* klen, const float* rope_cos, const float* rope_sin, int32_t samples, int32_t n_pad,
+                    void* stream);
+
+/* The whole sampler loop (model/cfm.py:431-447, 471 with torchdiffeq fixed-grid Euler): for i in [0, steps):
+ *   pred = DiT(x_cat; mod[i]) on the doubled batch (cond half then uncond half; a single half when
+ *   cfg_strength < 1e-5);  y += dt[i] * (pc + (pc - pu) * cfg);  state written back into x_cat for both halves.
+ * y: fp32 [batch*n_pad, mel_dim] state (y0 on entry, y(1) on exit).  mod: fp32 [steps, mod_size].  dt_host: HOST
+ * float [steps].  traj: optional fp32 [steps, batch*n_pad, mel_dim] (state after each step).  klen: int32
+ * [2*batch] (both halves) or NULL.  use_graph != 0 captures the loop into one CUDA graph launch. */
+int f5e_ode_solve(const f5e_dit_model* model, const f5e_dit_buffers* buf, float* y, const float* mod, int32_t mod_size,
+                  const float* dt_host, int32_t steps, float cfg_strength, const int32_t* klen, const float* rope_cos,
+                  const float* rope_sin, int32_t batch, int32_t n_pad, float* traj, int32_t round_bf16,
+                  int32_t use_graph, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -126,3 +126,296 @@ def make_state_dict(cfg: DiTConfig, seed: int = 1234, device="cpu", zero_init_st
     lin("norm_out.linear", 2 * D, D, std=zero_init_std)
     lin("proj_out", cfg.mel_dim, D, std=zero_init_std)
     return {k: v.to(device) for k, v in sd.items()}
+
+
+# -------------------------------------------------------------------------------------------------------
+# front end: MelSpec  (model/modules.py:75-143 == torchaudio MelSpectrogram, restated with torch.stft;
+# max-abs diff 0.0 against torchaudio)
+# -------------------------------------------------------------------------------------------------------
+def hz_to_mel_htk(f):
+    return 2595.0 * math.log10(1.0 + f / 700.0)
+
+
+def mel_filterbank(n_freqs=513, f_min=0.0, f_max=12000.0, n_mels=100, sample_rate=24000) -> torch.Tensor:
+    """HTK mel filterbank, norm=None, [n_freqs, n_mels] (torchaudio.functional.melscale_fbanks algorithm)."""
+    all_freqs = torch.linspace(0, sample_rate // 2, n_freqs)
+    m_pts = torch.linspace(hz_to_mel_htk(f_min), hz_to_mel_htk(f_max), n_mels + 2)
+    f_pts = 700.0 * (10.0 ** (m_pts / 2595.0) - 1.0)
+    f_diff = f_pts[1:] - f_pts[:-1]
+    slopes = f_pts.unsqueeze(0) - all_freqs.unsqueeze(1)
+    down = (-1.0 * slopes[:, :-2]) / f_diff[:-1]
+    up = slopes[:, 2:] / f_diff[1:]
+    return torch.clamp(torch.min(down, up), min=0.0)
+
+
+def mel_spectrogram(wav: torch.Tensor, n_fft=1024, hop=256, win=1024, n_mels=100, sr=24000) -> torch.Tensor:
+    """wav [B, nw] fp32 -> log-mel [B, n_mels, nw // hop + 1]."""
+    if wav.dim() == 3:
+        wav = wav.squeeze(1)
+    window = torch.hann_window(win, periodic=True, device=wav.device, dtype=wav.dtype)
+    spec = torch.stft(wav, n_fft, hop_length=hop, win_length=win, window=window, center=True, pad_mode="reflect",
+                      normalized=False, onesided=True, return_complex=True).abs()
+    fb = mel_filterbank(n_fft // 2 + 1, 0.0, sr / 2, n_mels, sr).to(wav.device, wav.dtype)
+    mel = torch.matmul(spec.transpose(-1, -2), fb).transpose(-1, -2)
+    return mel.clamp(min=1e-5).log()
+
+
+# -------------------------------------------------------------------------------------------------------
+# DiT evaluation  (backbones/dit.py:417-472)
+# -------------------------------------------------------------------------------------------------------
+def _lin(sd, p, x):
+    return F.linear(x, sd[p + ".weight"], sd[p + ".bias"])
+
+
+def sinus_time_embed(t: torch.Tensor, dim=256, scale=1000) -> torch.Tensor:
+    """model/modules.py:149-161, incl. its dtype behaviour: `scale * t` happens in t's dtype, the rest in fp32."""
+    half = dim // 2
+    e = math.log(10000) / (half - 1)
+    e = torch.exp(torch.arange(half, device=t.device).float() * -e)
+    e = scale * t.unsqueeze(1) * e.unsqueeze(0)
+    return torch.cat((e.sin(), e.cos()), dim=-1)
+
+
+def text_pos_table(dim: int, end: int = 4096, theta: float = 10000.0) -> torch.Tensor:
+    """model/modules.py:196-207 -> [end, dim] = [cos | sin]."""
+    freqs = 1.0 / (theta ** (torch.arange(0, dim, 2)[: dim // 2].float() / dim))
+    f = torch.outer(torch.arange(end), freqs).float()
+    return torch.cat([f.cos(), f.sin()], dim=-1)
+
+
+def rope_angles(n: int, dim_head=64, device="cpu") -> torch.Tensor:
+    """x_transformers RotaryEmbedding.forward_from_seq_len: interleaved pairs, [n, dim_head] fp32."""
+    inv = 1.0 / (10000 ** (torch.arange(0, dim_head, 2, device=device).float() / dim_head))
+    fr = torch.arange(n, device=device).float()[:, None] * inv[None]
+    return torch.stack((fr, fr), dim=-1).reshape(n, dim_head)
+
+
+def apply_rope(t: torch.Tensor, ang: torch.Tensor) -> torch.Tensor:
+    """x_transformers apply_rotary_pos_emb: fp32 math, cast back (modules.py:470-480 call site)."""
+    dt = t.dtype
+    x = t.float().reshape(*t.shape[:-1], -1, 2)
+    rot = torch.stack((-x[..., 1], x[..., 0]), dim=-1).reshape(t.shape)
+    return (t.float() * ang.cos() + rot * ang.sin()).to(dt)
+
+
+class OracleDiT:
+    """Functional restatement of DiT.sample over a reference-layout state dict."""
+
+    def __init__(self, cfg: DiTConfig, sd: dict, dtype=torch.float32, device="cpu"):
+        self.cfg = cfg
+        self.dtype = dtype
+        self.device = torch.device(device)
+        self.sd = {k: (v.to(self.device, dtype) if v.is_floating_point() else v.to(self.device)) for k, v in sd.items()}
+        # non-persistent buffer, cast with the module (model.to(dtype) casts float buffers)
+        self.pos = text_pos_table(cfg.text_dim).to(self.device, dtype)
+        self.text_cond = self.text_uncond = None
+
+    def clear_cache(self):
+        self.text_cond = self.text_uncond = None
+
+    # -- TextEmbedding (dit.py:54-87) + ConvNeXtV2Block (modules.py:241-269) + GRN (:225-234)
+    def text_embed(self, text, batch, seq_len, drop_text):
+        sd, cfg = self.sd, self.cfg
+        text = text + 1
+        text = text[:, :seq_len]
+        text = F.pad(text, (0, seq_len - text.shape[1]), value=0)
+        text_mask = text == 0
+        if drop_text:
+            text = torch.zeros_like(text)
+        x = F.embedding(text, sd["text_embed.text_embed.weight"])
+        if cfg.conv_layers > 0:
+            pos_idx = torch.arange(seq_len, device=x.device).clamp(max=4095)
+            x = x + self.pos[pos_idx][None]
+            mask = text_mask.unsqueeze(-1) if cfg.text_mask_padding else None
+            if mask is not None:
+                x = x.masked_fill(mask, 0.0)
+            for i in range(cfg.conv_layers):
+                p = f"text_embed.text_blocks.{i}"
+                r = x
+                h = F.conv1d(x.transpose(1, 2), sd[p + ".dwconv.weight"], sd[p + ".dwconv.bias"], padding=3,
+                             groups=cfg.text_dim).transpose(1, 2)
+                h = F.layer_norm(h, (cfg.text_dim,), sd[p + ".norm.weight"], sd[p + ".norm.bias"], eps=1e-6)
+                h = F.gelu(_lin(sd, p + ".pwconv1", h))
+                gx = torch.norm(h, p=2, dim=1, keepdim=True)
+                nx = gx / (gx.mean(dim=-1, keepdim=True) + 1e-6)
+                h = sd[p + ".grn.gamma"] * (h * nx) + sd[p + ".grn.beta"] + h
+                x = r + _lin(sd, p + ".pwconv2", h)
+                if mask is not None:
+                    x = x.masked_fill(mask, 0.0)
+        return x
+
+    # -- PPGEmbedding (dit.py:121-153), eval-mode BatchNorm
+    def ppg_embed(self, ppg, seq_len, drop_ppg, batch):
+        sd, cfg = self.sd, self.cfg
+        if ppg is None:
+            ppg = torch.zeros(batch, seq_len, cfg.ppg_dim, dtype=self.dtype, device=self.device)
+        else:
+            ppg = F.pad(ppg, (0, 0, 0, seq_len - ppg.shape[1]), value=0).to(self.dtype)
+            if drop_ppg:
+                ppg = torch.zeros_like(ppg)
+        h = _lin(sd, "ppg_embed.ppg_proj.0", ppg).transpose(1, 2)
+        for ci, bi in ((2, 3), (6, 7), (10, 11)):
+            h = F.conv1d(h, sd[f"ppg_embed.ppg_proj.{ci}.weight"], sd[f"ppg_embed.ppg_proj.{ci}.bias"], padding=2)
+            h = F.batch_norm(h, sd[f"ppg_embed.ppg_proj.{bi}.running_mean"], sd[f"ppg_embed.ppg_proj.{bi}.running_var"],
+                             sd[f"ppg_embed.ppg_proj.{bi}.weight"], sd[f"ppg_embed.ppg_proj.{bi}.bias"], False, 0.0, 1e-5)
+            h = F.relu(h)
+        return _lin(sd, "ppg_embed.ppg_proj.15", h.transpose(1, 2))
+
+    def sample(self, x, cond, text, ppg, time, drop_audio_cond, drop_text, drop_ppg, mask=None, taps=None):
+        sd, cfg = self.sd, self.cfg
+        B, N = x.shape[0], x.shape[1]
+        if time.ndim == 0:
+            time = time.repeat(B)
+        # TimestepEmbedding (modules.py:721-731)
+        th = sinus_time_embed(time).to(time.dtype)
+        t = _lin(sd, "time_embed.time_mlp.2", F.silu(_lin(sd, "time_embed.time_mlp.0", th)))
+        if drop_text:
+            if self.text_uncond is None:
+                self.text_uncond = self.text_embed(text, B, N, True)
+            te = self.text_uncond
+        else:
+            if self.text_cond is None:
+                self.text_cond = self.text_embed(text, B, N, False)
+            te = self.text_cond
+        if drop_audio_cond:
+            cond = torch.zeros_like(cond)
+        parts = [x, cond, te]
+        if cfg.use_ppg:
+            parts.append(self.ppg_embed(ppg, N, drop_ppg, B))
+        h = _lin(sd, "input_embed.proj", torch.cat(parts, dim=-1))
+        # ConvPositionEmbedding, unmasked (modules.py:167-190; dit.py:176)
+        c = h.transpose(1, 2)
+        for i in (0, 2):
+            c = F.mish(F.conv1d(c, sd[f"input_embed.conv_pos_embed.conv1d.{i}.weight"],
+                                sd[f"input_embed.conv_pos_embed.conv1d.{i}.bias"], padding=15, groups=16))
+        h = c.transpose(1, 2) + h
+        if taps is not None:
+            taps["embed"] = h
+        ang = rope_angles(N, cfg.dim_head, x.device)
+        H, dh = cfg.heads, cfg.dim_head
+        ts = F.silu(t)
+        for l in range(cfg.depth):
+            p = f"transformer_blocks.{l}"
+            emb = _lin(sd, p + ".attn_norm.linear", ts)
+            shift_msa, scale_msa, gate_msa, shift_mlp, scale_mlp, gate_mlp = torch.chunk(emb, 6, dim=1)
+            nrm = F.layer_norm(h, (cfg.dim,), eps=1e-6) * (1 + scale_msa[:, None]) + shift_msa[:, None]
+            q = _lin(sd, p + ".attn.to_q", nrm).view(B, N, H, dh).transpose(1, 2)
+            k = _lin(sd, p + ".attn.to_k", nrm).view(B, N, H, dh).transpose(1, 2)
+            v = _lin(sd, p + ".attn.to_v", nrm).view(B, N, H, dh).transpose(1, 2)
+            pn = H if cfg.pe_attn_head is None else cfg.pe_attn_head
+            q = torch.cat((apply_rope(q[:, :pn], ang), q[:, pn:]), dim=1)
+            k = torch.cat((apply_rope(k[:, :pn], ang), k[:, pn:]), dim=1)
+            am = None if mask is None else mask[:, None, None, :].expand(B, H, N, N)
+            a = F.scaled_dot_product_attention(q, k, v, attn_mask=am)
+            a = a.transpose(1, 2).reshape(B, N, H * dh)
+            a = _lin(sd, p + ".attn.to_out.0", a)
+            if mask is not None:
+                a = a.masked_fill(~mask.unsqueeze(-1), 0.0)
+            h = h + gate_msa.unsqueeze(1) * a
+            nrm = F.layer_norm(h, (cfg.dim,), eps=1e-6) * (1 + scale_mlp[:, None]) + shift_mlp[:, None]
+            ff = _lin(sd, p + ".ff.ff.2", F.gelu(_lin(sd, p + ".ff.ff.0.0", nrm), approximate="tanh"))
+            h = h + gate_mlp.unsqueeze(1) * ff
+            if taps is not None and l == 0:
+                taps["block0"] = h
+        emb = _lin(sd, "norm_out.linear", ts)
+        scale, shift = torch.chunk(emb, 2, dim=1)
+        h = F.layer_norm(h, (cfg.dim,), eps=1e-6) * (1 + scale)[:, None, :] + shift[:, None, :]
+        return _lin(sd, "proj_out", h)
+
+
+# -------------------------------------------------------------------------------------------------------
+# CFM.sample  (model/cfm.py:348-482) with torchdiffeq's fixed-grid Euler restated inline
+# -------------------------------------------------------------------------------------------------------
+def lens_to_mask(t: torch.Tensor, length=None) -> torch.Tensor:
+    """model/utils.py:41-46."""
+    if length is None:
+        length = int(t.amax())
+    return torch.arange(length, device=t.device)[None, :] < t[:, None]
+
+
+def sway_schedule(steps, sway, dtype, device, t_start=0.0):
+    """model/cfm.py:467-469, in the model dtype like the reference."""
+    t = torch.linspace(t_start, 1, steps + 1, device=device, dtype=dtype)
+    if sway is not None:
+        t = t + sway * (torch.cos(torch.pi / 2 * t) - 1 + t)
+    return t
+
+
+@torch.no_grad()
+def cfm_sample(dit: OracleDiT, cond, text, duration, *, ppg=None, lens=None, steps=32, cfg_strength=1.0,
+               sway_sampling_coef=None, seed=None, max_duration=4096, no_ref_audio=False, edit_mask=None,
+               y0=None, return_aux=False):
+    """cond: mel [B, T, 100] (or wave [B, nw]); text: int64 [B, nt] padded with -1.
+    Returns (out, trajectory) like the reference; with return_aux also the integer/bool side products."""
+    dtype, device = dit.dtype, dit.device
+    if cond.ndim == 2:
+        cond = mel_spectrogram(cond).permute(0, 2, 1)
+    cond = cond.to(dtype)
+    batch, cond_seq_len = cond.shape[:2]
+    if lens is None:
+        lens = torch.full((batch,), cond_seq_len, device=device, dtype=torch.long)
+    cond_mask = lens_to_mask(lens)
+    if edit_mask is not None:
+        cond_mask = cond_mask & edit_mask
+    if isinstance(duration, int):
+        duration = torch.full((batch,), duration, device=device, dtype=torch.long)
+    if text is not None:
+        duration = torch.maximum(torch.maximum((text != -1).sum(dim=-1), lens) + 1, duration)
+    else:
+        duration = torch.maximum(lens + 1, duration)
+    duration = duration.clamp(max=max_duration)
+    max_dur = int(duration.amax())
+    cond = F.pad(cond, (0, 0, 0, max_dur - cond_seq_len), value=0.0)
+    if no_ref_audio:
+        cond = torch.zeros_like(cond)
+    cond_mask = F.pad(cond_mask, (0, max_dur - cond_mask.shape[-1]), value=False).unsqueeze(-1)
+    step_cond = torch.where(cond_mask, cond, torch.zeros_like(cond))
+    mask = lens_to_mask(duration) if batch > 1 else None
+
+    def fn(t, x):
+        pred = dit.sample(x, step_cond, text, ppg, t, False, False, False, mask)
+        if cfg_strength < 1e-5:
+            return pred
+        null_pred = dit.sample(x, step_cond, text, ppg, t, True, True, True, mask)
+        return pred + (pred - null_pred) * cfg_strength
+
+    if y0 is None:
+        ys = []
+        for dur in duration:
+            if seed is not None:
+                torch.manual_seed(seed)
+            ys.append(torch.randn(int(dur), cond.shape[-1], device=device, dtype=dtype))
+        y0 = torch.nn.utils.rnn.pad_sequence(ys, padding_value=0, batch_first=True)
+    t = sway_schedule(steps, sway_sampling_coef, dtype, device)
+    traj = [y0]
+    y = y0
+    for i in range(steps):  # torchdiffeq fixed-grid Euler: y1 = y0 + (t1 - t0) * f(t0, y0)
+        dt = t[i + 1] - t[i]
+        y = y + dt * fn(t[i], y)
+        traj.append(y)
+    dit.clear_cache()
+    trajectory = torch.stack(traj)
+    out = torch.where(cond_mask, cond, trajectory[-1])
+    if return_aux:
+        return out, trajectory, dict(duration=duration, cond_mask=cond_mask, mask=mask, t=t, y0=y0, step_cond=step_cond)
+    return out, trajectory
+
+
+# -------------------------------------------------------------------------------------------------------
+# GumbelVectorQuantizer.forward in eval mode  (model/modules.py:881-950)
+# -------------------------------------------------------------------------------------------------------
+def vq_forward(sd: dict, x: torch.Tensor, groups=2, num_vars=100) -> dict:
+    bsz, tsz, fsz = x.shape
+    w, b, vars_ = sd["quantizer.weight_proj.weight"], sd["quantizer.weight_proj.bias"], sd["quantizer.vars"]
+    logits = F.linear(x.reshape(-1, fsz), w, b).view(bsz * tsz * groups, -1)
+    _, k = logits.max(-1)
+    hard_x = logits.new_zeros(*logits.shape).scatter_(-1, k.view(-1, 1), 1.0).view(bsz * tsz, groups, -1)
+    hard_probs = torch.mean(hard_x.float(), dim=0)
+    code_ppl = torch.exp(-torch.sum(hard_probs * torch.log(hard_probs + 1e-7), dim=-1)).sum()
+    avg_probs = torch.softmax(logits.view(bsz * tsz, groups, -1).float(), dim=-1).mean(dim=0)
+    prob_ppl = torch.exp(-torch.sum(avg_probs * torch.log(avg_probs + 1e-7), dim=-1)).sum()
+    targets = hard_x.view(bsz * tsz * groups, -1).argmax(dim=-1).view(bsz, tsz, groups)
+    xq = hard_x.view(bsz * tsz, -1).unsqueeze(-1) * vars_
+    xq = xq.view(bsz * tsz, groups, num_vars, -1).sum(-2).view(bsz, tsz, -1)
+    return {"x": xq, "targets": targets, "num_vars": num_vars * groups, "code_perplexity": code_ppl,
+            "prob_perplexity": prob_ppl}

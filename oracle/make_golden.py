@@ -1,0 +1,133 @@
+"""Generate tests/golden/*.pt by running the UNMODIFIED reference (imported from /root/reference through
+oracle/shims) on seeded inputs, and print how closely the oracle restatement reproduces it.
+TEST INFRASTRUCTURE.  Runs only in the build container (needs /root/reference); the fixtures travel.
+
+    python oracle/make_golden.py
+"""
+import os
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path[:0] = [os.path.join(HERE, "shims"), "/root/reference/src", os.path.dirname(HERE)]
+
+import torch  # noqa: E402
+
+from oracle import f5e_oracle as O  # noqa: E402
+from f5_tts.model import CFM, DiT  # noqa: E402
+from f5_tts.model.modules import GumbelVectorQuantizer, MelSpec  # noqa: E402
+
+OUT = os.path.join(os.path.dirname(HERE), "tests", "golden")
+os.makedirs(OUT, exist_ok=True)
+torch.set_num_threads(8)
+
+SMALL = O.DiTConfig(dim=256, depth=2, heads=4, text_dim=64, conv_layers=2, text_num_embeds=50)
+SMALL_PPG = O.DiTConfig(dim=256, depth=2, heads=4, text_dim=64, conv_layers=2, text_num_embeds=50,
+                        text_mask_padding=False, pe_attn_head=1, use_ppg=True, use_codebook=True, ppg_dim=32,
+                        cb_num_vars=10, cb_groups=2)
+
+
+def build_reference(cfg: O.DiTConfig, seed: int):
+    ppg_config = dict(use_ppg=cfg.use_ppg, ppg_dim=cfg.ppg_dim, use_transformer=False, transformer_config={},
+                      combined_cond_drop_prob=0.1)
+    cb_config = dict(use_codebook=cfg.use_codebook, num_vars=cfg.cb_num_vars, temp_start=2.0, temp_stop=0.5,
+                     temp_decay=0.999, groups=cfg.cb_groups, combine_groups=False, weight_proj_depth=1,
+                     weight_proj_factor=1)
+    dit = DiT(dim=cfg.dim, depth=cfg.depth, heads=cfg.heads, ff_mult=cfg.ff_mult, mel_dim=cfg.mel_dim,
+              text_num_embeds=cfg.text_num_embeds, text_dim=cfg.text_dim, text_mask_padding=cfg.text_mask_padding,
+              conv_layers=cfg.conv_layers, pe_attn_head=cfg.pe_attn_head, ppg_config=ppg_config, cb_config=cb_config)
+    sd = O.make_state_dict(cfg, seed)
+    missing, unexpected = dit.load_state_dict(sd, strict=False)
+    missing = [k for k in missing if "num_batches_tracked" not in k and "inv_freq" not in k]
+    assert not missing and not unexpected, (missing, unexpected)
+    model = CFM(transformer=dit, mel_spec_kwargs=dict(), ppg_config=ppg_config, cb_config=cb_config).eval()
+    return model, sd
+
+
+def rel(a, b):
+    return ((a.float() - b.float()).norm() / b.float().norm().clamp_min(1e-12)).item()
+
+
+def case_sample(name, cfg, batch, seed, with_ppg=False):
+    model, sd = build_reference(cfg, seed)
+    g = torch.Generator().manual_seed(seed + 1)
+    ref_len = torch.randint(12, 20, (batch,), generator=g)
+    dur = torch.randint(40, 64, (batch,), generator=g)
+    tlen = torch.randint(5, 15, (batch,), generator=g)
+    T = int(ref_len.max())
+    cond = torch.randn(batch, T, cfg.mel_dim, generator=g)
+    text = torch.full((batch, int(tlen.max())), -1, dtype=torch.long)
+    for i in range(batch):
+        text[i, : tlen[i]] = torch.randint(0, cfg.text_num_embeds, (int(tlen[i]),), generator=g)
+    ppg = torch.randn(batch, 30, cfg.ppg_dim, generator=g) if with_ppg else None
+    kw = dict(steps=4, cfg_strength=2.0, sway_sampling_coef=-1.0, seed=7)
+    with torch.no_grad():
+        out, traj = model.sample(cond=cond, text=text, ppg=ppg, duration=dur, lens=ref_len, **kw)
+    dit = O.OracleDiT(cfg, sd)
+    o_out, o_traj, aux = O.cfm_sample(dit, cond, text, dur, ppg=ppg, lens=ref_len, return_aux=True, **kw)
+    print(f"[{name}] oracle vs reference: out rel-L2 {rel(o_out, out):.2e}  max-abs {(o_out - out).abs().max():.2e}; "
+          f"traj rel-L2 {rel(o_traj, traj):.2e}")
+    torch.save(dict(cfg=cfg.__dict__, seed=seed, cond=cond, text=text, ppg=ppg, duration_in=dur, lens=ref_len, kw=kw,
+                    out=out, traj_last=traj[-1], traj_1=traj[1], duration=aux["duration"], mask=aux["mask"],
+                    cond_mask=aux["cond_mask"]), os.path.join(OUT, name + ".pt"))
+    return model, sd
+
+
+def case_single_eval(name, cfg, seed):
+    """One DiT.sample call (cond and uncond) with a per-sample mask."""
+    model, sd = build_reference(cfg, seed)
+    g = torch.Generator().manual_seed(seed + 2)
+    B, N = 2, 48
+    x = torch.randn(B, N, cfg.mel_dim, generator=g)
+    cond = torch.randn(B, N, cfg.mel_dim, generator=g)
+    text = torch.randint(0, cfg.text_num_embeds, (B, 11), generator=g)
+    text[1, 7:] = -1
+    ppg = torch.randn(B, 25, cfg.ppg_dim, generator=g) if cfg.use_ppg else None
+    mask = O.lens_to_mask(torch.tensor([48, 31]))
+    t = torch.tensor(0.37)
+    dit = O.OracleDiT(cfg, sd)
+    res = {}
+    with torch.no_grad():
+        for drop in (False, True):
+            r = model.transformer.sample(x=x, cond=cond, text=text, ppg=ppg, time=t, mask=mask, drop_audio_cond=drop,
+                                         drop_text=drop, drop_ppg=drop)
+            o = dit.sample(x, cond, text, ppg, t, drop, drop, drop, mask)
+            print(f"[{name}] drop={drop}: oracle vs reference rel-L2 {rel(o, r):.2e} max-abs {(o - r).abs().max():.2e}")
+            res["pred_drop" if drop else "pred"] = r
+        model.transformer.clear_cache()
+    torch.save(dict(cfg=cfg.__dict__, seed=seed, x=x, cond=cond, text=text, ppg=ppg, mask=mask, t=t, **res),
+               os.path.join(OUT, name + ".pt"))
+
+
+def case_mel(name):
+    g = torch.Generator().manual_seed(11)
+    wav = 0.1 * torch.randn(2, 5000, generator=g)
+    ref = MelSpec()(wav)
+    mine = O.mel_spectrogram(wav)
+    print(f"[{name}] oracle vs reference MelSpec: max-abs {(ref - mine).abs().max():.2e}")
+    torch.save(dict(wav=wav, mel=ref), os.path.join(OUT, name + ".pt"))
+
+
+def case_vq(name):
+    torch.manual_seed(5)
+    q = GumbelVectorQuantizer(dim=64, num_vars=10, temp=(2.0, 0.5, 0.999), groups=2, combine_groups=False, vq_dim=64,
+                              time_first=True).eval()
+    x = torch.randn(3, 17, 64)
+    with torch.no_grad():
+        r = q(x, produce_targets=True)
+    sd = {"quantizer.vars": q.vars.data, "quantizer.weight_proj.weight": q.weight_proj.weight.data,
+          "quantizer.weight_proj.bias": q.weight_proj.bias.data}
+    o = O.vq_forward(sd, x, groups=2, num_vars=10)
+    print(f"[{name}] targets equal: {torch.equal(o['targets'], r['targets'])}; x max-abs {(o['x'] - r['x']).abs().max():.2e}; "
+          f"ppl {float(o['code_perplexity'] - r['code_perplexity']):.1e} {float(o['prob_perplexity'] - r['prob_perplexity']):.1e}")
+    torch.save(dict(sd=sd, x=x, xq=r["x"], targets=r["targets"], code_perplexity=r["code_perplexity"],
+                    prob_perplexity=r["prob_perplexity"]), os.path.join(OUT, name + ".pt"))
+
+
+if __name__ == "__main__":
+    case_mel("melspec")
+    case_vq("vq")
+    case_single_eval("dit_eval_small", SMALL, 100)
+    case_single_eval("dit_eval_small_ppg", SMALL_PPG, 101)
+    case_sample("sample_b1", SMALL, 1, 200)
+    case_sample("sample_b3", SMALL, 3, 201)
+    case_sample("sample_b2_ppg", SMALL_PPG, 2, 202, with_ppg=True)
