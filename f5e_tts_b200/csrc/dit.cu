@@ -102,34 +102,44 @@ int f5e_ode_solve(const f5e_dit_model* model, const f5e_dit_buffers* buf, float*
   F5E_TRY(check_model(model, buf));
   F5E_REQUIRE(y && mod && dt_host && steps > 0 && batch > 0 && n_pad > 0, "f5e_ode_solve: bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
+  F5E_TRY(ensure_configured());  // attribute setup must not happen inside a stream capture
   const bool cfg = cfg_strength >= 1e-5f;
   const int samples = cfg ? 2 * batch : batch;
   const int rows_half = batch * n_pad;
-  auto enqueue = [&]() -> int {
+  auto enqueue = [&](cudaStream_t es) -> int {
     for (int i = 0; i < steps; ++i) {
-      F5E_TRY(dit_forward_impl(st, model, buf, mod + (size_t)i * mod_size, 0, klen, rope_cos, rope_sin, samples, n_pad));
+      F5E_TRY(dit_forward_impl(es, model, buf, mod + (size_t)i * mod_size, 0, klen, rope_cos, rope_sin, samples, n_pad));
       // when cfg is off only the first half of x_cat exists: cfg_euler's second x_cat write would be out of
       // bounds, so the state is written back by pack_cols instead
       float* tr = traj ? traj + (size_t)i * rows_half * model->mel_dim : nullptr;
       if (cfg) {
-        F5E_TRY(cfg_euler(st, buf->pred, model->mel_dim, y, (__nv_bfloat16*)buf->x_cat, model->in_dim, tr, rows_half,
+        F5E_TRY(cfg_euler(es, buf->pred, model->mel_dim, y, (__nv_bfloat16*)buf->x_cat, model->in_dim, tr, rows_half,
                           model->mel_dim, dt_host[i], cfg_strength, round_bf16));
       } else {
-        F5E_TRY(cfg_euler(st, buf->pred, model->mel_dim, y, nullptr, 0, tr, rows_half, model->mel_dim, dt_host[i], 0.0f,
+        F5E_TRY(cfg_euler(es, buf->pred, model->mel_dim, y, nullptr, 0, tr, rows_half, model->mel_dim, dt_host[i], 0.0f,
                           round_bf16));
-        F5E_TRY(pack_cols(st, (__nv_bfloat16*)buf->x_cat, model->in_dim, 0, y, 1, model->mel_dim, rows_half,
+        F5E_TRY(pack_cols(es, (__nv_bfloat16*)buf->x_cat, model->in_dim, 0, y, 1, model->mel_dim, rows_half,
                           model->mel_dim));
       }
     }
     return 0;
   };
-  if (!use_graph) return enqueue();
+  if (!use_graph) return enqueue(st);
 
+  // Capture on a private stream (the caller's may be the legacy default stream, which cannot be captured);
+  // nothing executes during capture.  The instantiated graph is then launched on the caller's stream.
+  cudaStream_t cap = nullptr;
+  F5E_CUDA_CHECK(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t exec = nullptr;
-  F5E_CUDA_CHECK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-  int rc = enqueue();
-  cudaError_t ce = cudaStreamEndCapture(st, &graph);
+  cudaError_t ce = cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal);
+  if (ce != cudaSuccess) {
+    cudaStreamDestroy(cap);
+    F5E_CUDA_CHECK(ce);
+  }
+  int rc = enqueue(cap);
+  ce = cudaStreamEndCapture(cap, &graph);
+  cudaStreamDestroy(cap);
   if (rc) {
     if (graph) cudaGraphDestroy(graph);
     return rc;
@@ -141,8 +151,7 @@ int f5e_ode_solve(const f5e_dit_model* model, const f5e_dit_buffers* buf, float*
     F5E_CUDA_CHECK(ce);
   }
   ce = cudaGraphLaunch(exec, st);
-  // the exec must outlive the launch: destroy after the stream drains (the caller's next sync covers it, but the
-  // handle itself has to be released here, so synchronise this stream once per solve)
+  // the executable graph must outlive its launch, so this path drains the stream once per solve before releasing it
   cudaError_t cs = cudaStreamSynchronize(st);
   cudaGraphExecDestroy(exec);
   cudaGraphDestroy(graph);
@@ -173,6 +182,12 @@ int f5e_grn(const void* x_bf16, const float* gamma, const float* beta, void* out
   F5E_REQUIRE(x_bf16 && gamma && beta && out_bf16 && scratch, "f5e_grn: null argument");
   return grn((cudaStream_t)stream, (const __nv_bfloat16*)x_bf16, gamma, beta, (__nv_bfloat16*)out_bf16, scratch, samples,
              n_pad, C);
+}
+
+int f5e_unfold_frames(const void* x_bf16, void* out_bf16, int32_t samples, int32_t n_pad, int32_t C, int32_t taps,
+                      void* stream) {
+  F5E_REQUIRE(x_bf16 && out_bf16, "f5e_unfold_frames: null argument");
+  return unfold_frames((cudaStream_t)stream, (const __nv_bfloat16*)x_bf16, (__nv_bfloat16*)out_bf16, samples, n_pad, C, taps);
 }
 
 }  // extern "C"

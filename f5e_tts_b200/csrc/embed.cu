@@ -196,4 +196,30 @@ int grn(cudaStream_t st, const __nv_bfloat16* x, const float* gamma, const float
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// unfold_frames: out[s, n, tap*C + c] = x[s, n + tap - taps/2, c] (zero outside the sample), so that a dense
+// Conv1d(C, C', k=taps, padding="same") becomes ONE GEMM with K = taps*C (PPGEmbedding's k=5 convs,
+// backbones/dit.py:124-135; runs twice per solve).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+unfold_frames_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, int n_pad, int C, int taps) {
+  const int n = blockIdx.x, s = blockIdx.y;
+  const int half = taps / 2, vec = C / 8;
+  for (int i = threadIdx.x; i < taps * vec; i += blockDim.x) {
+    const int tap = i / vec, c8 = i - tap * vec;
+    const int src = n + tap - half;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (src >= 0 && src < n_pad) v = *reinterpret_cast<const uint4*>(x + ((size_t)s * n_pad + src) * C + c8 * 8);
+    *reinterpret_cast<uint4*>(out + ((size_t)s * n_pad + n) * taps * C + (size_t)tap * C + c8 * 8) = v;
+  }
+}
+
+int unfold_frames(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int samples, int n_pad, int C, int taps) {
+  F5E_REQUIRE(samples > 0 && n_pad > 0 && C % 8 == 0 && taps % 2 == 1, "unfold_frames: bad shape");
+  dim3 grid(n_pad, samples);
+  unfold_frames_kernel<<<grid, 256, 0, st>>>(x, out, n_pad, C, taps);
+  F5E_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
 }  // namespace f5e

@@ -42,6 +42,7 @@ int dwconv7(cudaStream_t st, const __nv_bfloat16* x, const float* w, const float
             int n_pad, int C);
 int grn(cudaStream_t st, const __nv_bfloat16* x, const float* gamma, const float* beta, __nv_bfloat16* out,
         float* scratch, int samples, int n_pad, int C);
+int unfold_frames(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int samples, int n_pad, int C, int taps);
 // one-time per-device kernel attribute setup (opt-in shared memory sizes); idempotent
 int ensure_configured();
 int gemm_configure();

@@ -1,0 +1,509 @@
+"""Drop-in mirrors of the reference's inference objects, backed by libf5e_b200.so.
+
+    DiT      <-> f5_tts.model.backbones.dit.DiT        (constructor kwargs, .sample, .clear_cache, state-dict keys)
+    CFM      <-> f5_tts.model.cfm.CFM                  (.sample -> (out, trajectory))
+    MelSpec  <-> f5_tts.model.modules.MelSpec          (see frontend.py)
+
+torch supplies parameter storage (so `load_state_dict` / `load_checkpoint` of the reference work unchanged),
+device memory and the current stream.  All arithmetic on the hot path runs in the hand-written sm_100a
+kernels reached through ctypes; there is no eager fallback - on a CPU tensor or without the library the
+calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+from . import _lib, ops
+from ._lib import check, ptr, stream_ptr
+
+
+# ---- ctypes mirrors of include/f5e_b200.h ------------------------------------------------------------
+class _Layer(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("w_qkv", "b_qkv", "w_out", "b_out", "w_ff1", "b_ff1", "w_ff2", "b_ff2")]
+
+
+class _Model(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("dim", "depth", "heads", "ff_dim", "in_dim", "mel_dim", "rope_heads",
+                                         "conv_groups")] + [
+        ("w_in", C.c_void_p), ("b_in", C.c_void_p), ("w_conv1", C.c_void_p), ("b_conv1", C.c_void_p),
+        ("w_conv2", C.c_void_p), ("b_conv2", C.c_void_p), ("layers", C.POINTER(_Layer)),
+        ("w_proj", C.c_void_p), ("b_proj", C.c_void_p)]
+
+
+class _Buffers(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("x_cat", "h0", "h1", "x", "xn", "qkv", "attn", "ff", "pred")]
+
+
+# ---- parameter containers with the reference's state-dict names ---------------------------------------
+def _seq(mods: dict) -> nn.ModuleDict:
+    """nn.Sequential-compatible naming with gaps ("0", "2", ...)."""
+    return nn.ModuleDict({str(k): v for k, v in mods.items()})
+
+
+class _GRN(nn.Module):
+    def __init__(self, dim):
+        super().__init__()
+        self.gamma = nn.Parameter(torch.zeros(1, 1, dim))
+        self.beta = nn.Parameter(torch.zeros(1, 1, dim))
+
+
+class _ConvNeXtV2Block(nn.Module):  # parameters of model/modules.py:241-259
+    def __init__(self, dim, inter):
+        super().__init__()
+        self.dwconv = nn.Conv1d(dim, dim, 7, padding=3, groups=dim)
+        self.norm = nn.LayerNorm(dim, eps=1e-6)
+        self.pwconv1 = nn.Linear(dim, inter)
+        self.grn = _GRN(inter)
+        self.pwconv2 = nn.Linear(inter, dim)
+
+
+class _TextEmbedding(nn.Module):  # backbones/dit.py:37-52
+    def __init__(self, n, dim, conv_layers):
+        super().__init__()
+        self.text_embed = nn.Embedding(n + 1, dim)
+        if conv_layers > 0:
+            self.text_blocks = nn.ModuleList([_ConvNeXtV2Block(dim, dim * 2) for _ in range(conv_layers)])
+
+
+class _Holder(nn.Module):
+    def __init__(self, **mods):
+        super().__init__()
+        for k, v in mods.items():
+            setattr(self, k, v)
+
+
+class _Block(nn.Module):  # model/modules.py:610-625
+    def __init__(self, dim, heads, dim_head, ff_mult):
+        super().__init__()
+        inner = heads * dim_head
+        self.attn_norm = _Holder(linear=nn.Linear(dim, dim * 6))
+        self.attn = _Holder(to_q=nn.Linear(dim, inner), to_k=nn.Linear(dim, inner), to_v=nn.Linear(dim, inner),
+                            to_out=_seq({0: nn.Linear(inner, dim)}))
+        self.ff = _Holder(ff=_seq({0: _seq({0: nn.Linear(dim, dim * ff_mult)}), 2: nn.Linear(dim * ff_mult, dim)}))
+
+
+def _sinus_time_embed(t: torch.Tensor, dim=256, scale=1000) -> torch.Tensor:
+    """model/modules.py:149-161 with the same dtype promotion (`scale * t` in t's dtype, then fp32).  33 scalars of
+    host-side schedule glue; kept in torch so the rounding matches the reference op for op."""
+    half = dim // 2
+    e = math.log(10000) / (half - 1)
+    e = torch.exp(torch.arange(half, device=t.device).float() * -e)
+    e = scale * t.unsqueeze(1) * e.unsqueeze(0)
+    return torch.cat((e.sin(), e.cos()), dim=-1)
+
+
+class DiT(nn.Module):
+    """Mirror of reference backbones/dit.py:183-271 (constructor) and :417-472 (`sample`)."""
+
+    def __init__(self, *, dim, depth=8, heads=8, dim_head=64, dropout=0.1, ff_mult=4, mel_dim=100, text_num_embeds=256,
+                 text_dim=None, text_mask_padding=True, qk_norm=None, conv_layers=0, pe_attn_head=None,
+                 long_skip_connection=False, checkpoint_activations=False, ppg_config=dict(use_ppg=False),
+                 cb_config=dict(use_codebook=False)):
+        super().__init__()
+        if dim_head != 64:
+            raise NotImplementedError("f5e_tts_b200: the attention kernel is specialised for dim_head=64")
+        if qk_norm is not None or long_skip_connection:
+            raise NotImplementedError("f5e_tts_b200: qk_norm / long_skip_connection are not on the F5E inference path")
+        if dim % 256 or (dim // 16) % 16 or dim // 16 > 64:
+            raise NotImplementedError(f"f5e_tts_b200: dim={dim} unsupported (need dim % 256 == 0 and dim/16 in 16..64)")
+        text_dim = mel_dim if text_dim is None else text_dim
+        self.dim, self.depth, self.heads, self.dim_head, self.ff_mult = dim, depth, heads, dim_head, ff_mult
+        self.mel_dim, self.text_dim, self.text_num_embeds = mel_dim, text_dim, text_num_embeds
+        self.text_mask_padding, self.conv_layers, self.pe_attn_head = text_mask_padding, conv_layers, pe_attn_head
+        self.use_ppg = ppg_config["use_ppg"]
+        self.use_codebook = cb_config["use_codebook"]
+
+        self.time_embed = _Holder(time_mlp=_seq({0: nn.Linear(256, dim), 2: nn.Linear(dim, dim)}))
+        self.text_embed = _TextEmbedding(text_num_embeds, text_dim, conv_layers)
+        in_dim = mel_dim * 2 + text_dim * (2 if self.use_ppg else 1)
+        if self.use_ppg:
+            if ppg_config.get("use_transformer", False):
+                raise NotImplementedError("f5e_tts_b200: PPGEmbedding(use_transformer=True) is not implemented")
+            P = self.ppg_dim = ppg_config["ppg_dim"]
+            self.ppg_embed = _Holder(ppg_proj=_seq({0: nn.Linear(P, P), 2: nn.Conv1d(P, P, 5, padding="same"),
+                                                    3: nn.BatchNorm1d(P), 6: nn.Conv1d(P, P, 5, padding="same"),
+                                                    7: nn.BatchNorm1d(P), 10: nn.Conv1d(P, P, 5, padding="same"),
+                                                    11: nn.BatchNorm1d(P), 15: nn.Linear(P, text_dim)}))
+        if self.use_codebook:
+            from .quantizer import GumbelVectorQuantizer
+            self.quantizer = GumbelVectorQuantizer(
+                dim=text_dim, num_vars=cb_config["num_vars"],
+                temp=(cb_config["temp_start"], cb_config["temp_stop"], cb_config["temp_decay"]),
+                groups=cb_config["groups"], combine_groups=cb_config["combine_groups"], vq_dim=text_dim,
+                time_first=True, weight_proj_depth=cb_config["weight_proj_depth"],
+                weight_proj_factor=cb_config["weight_proj_factor"])
+        self.in_dim = in_dim
+        self.input_embed = _Holder(proj=nn.Linear(in_dim, dim), conv_pos_embed=_Holder(conv1d=_seq({
+            0: nn.Conv1d(dim, dim, 31, groups=16, padding=15), 2: nn.Conv1d(dim, dim, 31, groups=16, padding=15)})))
+        self.rotary_embed = _Holder()
+        self.rotary_embed.register_buffer("inv_freq", 1.0 / (10000 ** (torch.arange(0, dim_head, 2).float() / dim_head)))
+        self.transformer_blocks = nn.ModuleList([_Block(dim, heads, dim_head, ff_mult) for _ in range(depth)])
+        self.norm_out = _Holder(linear=nn.Linear(dim, dim * 2))
+        self.proj_out = nn.Linear(dim, mel_dim)
+        self.text_cond = self.text_uncond = None
+        self._plan = None
+        self._ws = {}
+        self.initialize_weights()
+
+    def initialize_weights(self):  # backbones/dit.py:273-283
+        for blk in self.transformer_blocks:
+            nn.init.constant_(blk.attn_norm.linear.weight, 0)
+            nn.init.constant_(blk.attn_norm.linear.bias, 0)
+        for m in (self.norm_out.linear, self.proj_out):
+            nn.init.constant_(m.weight, 0)
+            nn.init.constant_(m.bias, 0)
+
+    def clear_cache(self):  # backbones/dit.py:293-294
+        self.text_cond = self.text_uncond = None
+
+    # any parameter change invalidates the packed plan
+    def _apply(self, fn, *a, **k):
+        self._plan, self._ws = None, {}
+        return super()._apply(fn, *a, **k)
+
+    def load_state_dict(self, *a, **k):
+        self._plan, self._ws = None, {}
+        return super().load_state_dict(*a, **k)
+
+    def forward(self, *a, **k):
+        raise NotImplementedError("f5e_tts_b200.DiT is inference-only: use .sample (training stays with the reference)")
+
+    # ---- packed weights ("plan") ------------------------------------------------------------------
+    def _get_plan(self):
+        if self._plan is not None:
+            return self._plan
+        dev = self.proj_out.weight.device
+        if dev.type != "cuda":
+            raise RuntimeError("f5e_tts_b200.DiT has no CPU path: move the module to a B200 (cuda) device")
+        _lib.require_device()
+        bf = lambda t: t.detach().to(dev, torch.bfloat16).contiguous()  # noqa: E731
+        f32 = lambda t: t.detach().to(dev, torch.float32).contiguous()  # noqa: E731
+        P = type("Plan", (), {})()
+        keep = P.keep = []
+
+        def K(t):
+            keep.append(t)
+            return t.data_ptr()
+
+        D = self.dim
+        layers = (_Layer * self.depth)()
+        mod_w, mod_b = [], []
+        for l, blk in enumerate(self.transformer_blocks):
+            a = blk.attn
+            layers[l].w_qkv = K(bf(torch.cat([a.to_q.weight, a.to_k.weight, a.to_v.weight], 0)))
+            layers[l].b_qkv = K(f32(torch.cat([a.to_q.bias, a.to_k.bias, a.to_v.bias], 0)))
+            layers[l].w_out, layers[l].b_out = K(bf(a.to_out["0"].weight)), K(f32(a.to_out["0"].bias))
+            layers[l].w_ff1, layers[l].b_ff1 = K(bf(blk.ff.ff["0"]["0"].weight)), K(f32(blk.ff.ff["0"]["0"].bias))
+            layers[l].w_ff2, layers[l].b_ff2 = K(bf(blk.ff.ff["2"].weight)), K(f32(blk.ff.ff["2"].bias))
+            mod_w.append(blk.attn_norm.linear.weight)
+            mod_b.append(blk.attn_norm.linear.bias)
+        mod_w.append(self.norm_out.linear.weight)
+        mod_b.append(self.norm_out.linear.bias)
+        P.w_mod, P.b_mod = bf(torch.cat(mod_w, 0)), f32(torch.cat(mod_b, 0))
+        P.mod_size = P.w_mod.shape[0]
+        tm = self.time_embed.time_mlp
+        P.w_t0, P.b_t0, P.w_t2, P.b_t2 = bf(tm["0"].weight), f32(tm["0"].bias), bf(tm["2"].weight), f32(tm["2"].bias)
+        m = _Model()
+        m.dim, m.depth, m.heads, m.ff_dim, m.in_dim, m.mel_dim = D, self.depth, self.heads, D * self.ff_mult, self.in_dim, self.mel_dim
+        m.rope_heads = self.heads if self.pe_attn_head is None else self.pe_attn_head
+        m.conv_groups = 16
+        ie = self.input_embed
+        m.w_in, m.b_in = K(bf(ie.proj.weight)), K(f32(ie.proj.bias))
+        c = ie.conv_pos_embed.conv1d
+        m.w_conv1, m.b_conv1 = K(ops.pack_conv_pos_weight(c["0"].weight.detach().to(dev))), K(f32(c["0"].bias))
+        m.w_conv2, m.b_conv2 = K(ops.pack_conv_pos_weight(c["2"].weight.detach().to(dev))), K(f32(c["2"].bias))
+        m.layers = C.cast(layers, C.POINTER(_Layer))
+        m.w_proj, m.b_proj = K(bf(self.proj_out.weight)), K(f32(self.proj_out.bias))
+        P.layers, P.model = layers, m
+        # text embedder
+        te = self.text_embed
+        P.table = bf(te.text_embed.weight)
+        P.text_blocks = []
+        if self.conv_layers > 0:
+            from .tables import text_pos_table
+            P.pos = text_pos_table(self.text_dim).to(dev)
+            for b in te.text_blocks:
+                P.text_blocks.append(dict(dw_w=f32(b.dwconv.weight.reshape(self.text_dim, 7)), dw_b=f32(b.dwconv.bias),
+                                          ln_w=f32(b.norm.weight), ln_b=f32(b.norm.bias),
+                                          w1=bf(b.pwconv1.weight), b1=f32(b.pwconv1.bias),
+                                          gamma=f32(b.grn.gamma.reshape(-1)), beta=f32(b.grn.beta.reshape(-1)),
+                                          w2=bf(b.pwconv2.weight), b2=f32(b.pwconv2.bias)))
+        else:
+            P.pos = None
+        if self.use_ppg:
+            pp = self.ppg_embed.ppg_proj
+            P.ppg = dict(w0=bf(pp["0"].weight), b0=f32(pp["0"].bias), w15=bf(pp["15"].weight), b15=f32(pp["15"].bias), convs=[])
+            for ci, bi in (("2", "3"), ("6", "7"), ("10", "11")):
+                conv, bn = pp[ci], pp[bi]
+                s = (bn.weight.detach().float() / torch.sqrt(bn.running_var.detach().float() + bn.eps)).to(dev)
+                w = conv.weight.detach().float().to(dev) * s[:, None, None]                # fold eval-mode BatchNorm
+                b = (conv.bias.detach().float().to(dev) - bn.running_mean.detach().float().to(dev)) * s + bn.bias.detach().float().to(dev)
+                P.ppg["convs"].append((bf(w.permute(0, 2, 1).reshape(w.shape[0], -1)), f32(b)))  # [co, tap*C + ci]
+        P.rope = {}
+        self._plan = P
+        return P
+
+    def _rope(self, n_pad):
+        P = self._get_plan()
+        if n_pad not in P.rope:
+            from .tables import rope_tables
+            P.rope = {n_pad: rope_tables(n_pad, self.dim_head, P.w_mod.device)}
+        return P.rope[n_pad]
+
+    def _workspace(self, samples, n_pad):
+        key = (samples, n_pad)
+        if key not in self._ws:
+            dev, rows, D, inner = self._get_plan().w_mod.device, samples * n_pad, self.dim, self.heads * 64
+            mk = lambda c, dt=torch.bfloat16: torch.empty(rows, c, device=dev, dtype=dt)  # noqa: E731
+            t = dict(x_cat=torch.zeros(rows, self.in_dim, device=dev, dtype=torch.bfloat16), h0=mk(D), h1=mk(D), x=mk(D),
+                     xn=mk(D), qkv=mk(3 * inner), attn=torch.zeros(rows, inner, device=dev, dtype=torch.bfloat16),
+                     ff=mk(D * self.ff_mult), pred=mk(self.mel_dim, torch.float32))
+            b = _Buffers(**{k: v.data_ptr() for k, v in t.items()})
+            self._ws = {key: (t, b)}  # keep only the latest shape
+        return self._ws[key]
+
+    # ---- once-per-solve conditioning ----------------------------------------------------------------
+    def _text_embed(self, text, batch, seq_len, drop_text):
+        """TextEmbedding.forward (backbones/dit.py:54-87) -> bf16 [B, N, text_dim]."""
+        P = self._get_plan()
+        if text is None:
+            text = torch.full((batch, 1), -1, dtype=torch.long, device=P.table.device)
+            mask_padding = False  # reference: no mask is built when text is None
+        else:
+            mask_padding = self.text_mask_padding
+        text = text.to(P.table.device)
+        x = ops.text_gather(text, P.table, P.pos, seq_len, drop=drop_text, mask_padding=mask_padding and self.conv_layers > 0,
+                            add_pos=self.conv_layers > 0)
+        if self.conv_layers == 0:
+            return x
+        row_len = None
+        if mask_padding:
+            valid = (text[:, :seq_len] != -1)
+            tl = valid.sum(-1)
+            if not bool((valid == (torch.arange(valid.shape[1], device=valid.device)[None] < tl[:, None])).all()):
+                raise NotImplementedError("f5e_tts_b200: text padding (-1) must be trailing")
+            row_len = tl.to(torch.int32)
+        B, N, TD = x.shape
+        for blk in P.text_blocks:  # ConvNeXtV2Block (model/modules.py:261-269)
+            h = ops.dwconv7(x, blk["dw_w"], blk["dw_b"])
+            h = ops.norm_mod(h, blk["ln_w"], blk["ln_b"], plus_one=0.0, eps=1e-6)
+            h = ops.gemm(h.view(B * N, TD), blk["w1"], bias=blk["b1"], act=_lib.ACT_GELU_ERF)
+            h = ops.grn(h.view(B, N, -1), blk["gamma"], blk["beta"])
+            # residual + pwconv2; rows beyond the text are zero in `x` and zeroed in the branch -> masked_fill(0)
+            x = ops.gemm(h.view(B * N, -1), blk["w2"], bias=blk["b2"], residual=x.view(B * N, TD), row_len=row_len,
+                         n_pad=N).view(B, N, TD)
+        return x
+
+    def _ppg_embed(self, ppg, seq_len, drop_ppg, batch):
+        """PPGEmbedding.forward (backbones/dit.py:140-153), BatchNorm folded into the k=5 convs."""
+        P = self._get_plan()
+        dev, Pd = P.table.device, self.ppg_dim
+        x = torch.zeros(batch, seq_len, Pd, device=dev, dtype=torch.bfloat16)
+        if ppg is not None and not drop_ppg:
+            n = min(ppg.shape[1], seq_len)
+            ops.pack_cols(x.view(batch * seq_len, Pd).view(batch, seq_len * Pd)[:, : n * Pd], 0,
+                          ppg[:, :n].reshape(batch, n * Pd).to(dev))
+        rows = batch * seq_len
+        h = ops.gemm(x.view(rows, Pd), P.ppg["w0"], bias=P.ppg["b0"])
+        for w, b in P.ppg["convs"]:
+            u = ops.unfold_frames(h.view(batch, seq_len, Pd), 5)
+            h = ops.gemm(u.view(rows, 5 * Pd), w, bias=b, act=_lib.ACT_RELU)
+        return ops.gemm(h, P.ppg["w15"], bias=P.ppg["b15"]).view(batch, seq_len, self.text_dim)
+
+    def _modulation(self, times: torch.Tensor) -> torch.Tensor:
+        """All time-dependent vectors for the given time values: TimestepEmbedding (model/modules.py:721-731),
+        then every AdaLayerNorm / AdaLayerNorm_Final linear on SiLU(t) (:310, :332) in ONE GEMM -> fp32 [S, mod_size]."""
+        P = self._get_plan()
+        th = _sinus_time_embed(times.to(P.w_mod.device)).to(times.dtype).to(torch.bfloat16).contiguous()
+        h = ops.gemm(th, P.w_t0, bias=P.b_t0, act=_lib.ACT_SILU)
+        st = ops.gemm(h, P.w_t2, bias=P.b_t2, act=_lib.ACT_SILU)  # SiLU(t_emb): the only way t_emb is consumed
+        return ops.gemm(st, P.w_mod, bias=P.b_mod, out_f32=True)
+
+    # ---- one flow evaluation ----------------------------------------------------------------------
+    @torch.no_grad()
+    def sample(self, x, cond, text, ppg, time, drop_audio_cond, drop_text, drop_ppg, mask=None):
+        """backbones/dit.py:417-472."""
+        P = self._get_plan()
+        B, N = x.shape[0], x.shape[1]
+        dev = P.table.device
+        if time.ndim == 0:
+            time = time.repeat(B)
+        mod = self._modulation(time)
+        if drop_text:
+            if self.text_uncond is None:
+                self.text_uncond = self._text_embed(text, B, N, True)
+            te = self.text_uncond
+        else:
+            if self.text_cond is None:
+                self.text_cond = self._text_embed(text, B, N, False)
+            te = self.text_cond
+        tens, buf = self._workspace(B, N)
+        xc, md, td = tens["x_cat"], self.mel_dim, self.text_dim
+        ops.pack_cols(xc, 0, x.reshape(B * N, md).to(dev))
+        ops.pack_cols(xc, md, None if drop_audio_cond else cond.reshape(B * N, md).to(dev), md)
+        ops.pack_cols(xc, 2 * md, te.view(B * N, td))
+        if self.use_ppg:
+            ops.pack_cols(xc, 2 * md + td, self._ppg_embed(ppg, N, drop_ppg, B).view(B * N, td))
+        klen = None
+        if mask is not None:
+            klen = mask.sum(-1).to(torch.int32).to(dev)
+        cos, sin = self._rope(N)
+        check(_lib.load().f5e_dit_forward(C.byref(P.model), C.byref(buf), ptr(mod), P.mod_size, ptr(klen), ptr(cos), ptr(sin),
+                                          B, N, stream_ptr()), "f5e_dit_forward")
+        return tens["pred"].view(B, N, md).to(x.dtype)
+
+
+# =======================================================================================================
+# CFM: the sampler
+# =======================================================================================================
+def lens_to_mask(t, length=None):  # model/utils.py:41-46
+    if length is None:
+        length = int(t.amax())
+    return torch.arange(length, device=t.device)[None, :] < t[:, None]
+
+
+def list_str_to_idx(text, vocab_char_map, padding_value=-1):  # model/utils.py:87-100
+    toks = [torch.tensor([vocab_char_map.get(c, 0) for c in t]) for t in text]
+    return torch.nn.utils.rnn.pad_sequence(toks, padding_value=padding_value, batch_first=True)
+
+
+def list_str_to_tensor(text, padding_value=-1):  # model/utils.py:80-84
+    toks = [torch.tensor([*bytes(t, "UTF-8")]) for t in text]
+    return torch.nn.utils.rnn.pad_sequence(toks, padding_value=padding_value, batch_first=True)
+
+
+class CFM(nn.Module):
+    """Mirror of reference model/cfm.py:34-91 (constructor / attributes) and :348-482 (`sample`)."""
+
+    def __init__(self, transformer, sigma=0.0, odeint_kwargs=dict(method="euler"), audio_drop_prob=0.3,
+                 cond_drop_prob=0.2, num_channels=None, mel_spec_module=None, mel_spec_kwargs=dict(),
+                 frac_lengths_mask=(0.7, 1.0), vocab_char_map=None, ppg_config=dict(use_ppg=False),
+                 cb_config=dict(use_codebook=False)):
+        super().__init__()
+        from .frontend import MelSpec
+        self.frac_lengths_mask = frac_lengths_mask
+        self.mel_spec = mel_spec_module if mel_spec_module is not None else MelSpec(**mel_spec_kwargs)
+        self.num_channels = num_channels if num_channels is not None else self.mel_spec.n_mel_channels
+        self.audio_drop_prob, self.cond_drop_prob = audio_drop_prob, cond_drop_prob
+        self.transformer = transformer
+        self.dim = transformer.dim
+        self.sigma = sigma
+        self.odeint_kwargs = odeint_kwargs
+        self.vocab_char_map = vocab_char_map
+        self.use_ppg = ppg_config["use_ppg"]
+        self.use_cross_mask = ppg_config.get("use_cross_mask", False)
+        self.use_codebook = cb_config["use_codebook"]
+        self.use_align_loss = cb_config.get("use_align_loss", False)
+        # knobs of the B200 path (not in the reference)
+        self.use_cuda_graph = False       # capture the whole Euler loop in one CUDA graph launch
+        self.store_trajectory = True      # False: return only [y0, y1] instead of steps+1 states
+        self.emulate_lowp_state = False   # True: round the ODE state to bf16 every step like a bf16 reference run
+
+    @property
+    def device(self):
+        return next(self.parameters()).device
+
+    def forward(self, *a, **k):
+        raise NotImplementedError("f5e_tts_b200.CFM is inference-only: use .sample")
+
+    @torch.no_grad()
+    def sample(self, cond, text, ppg=None, duration=None, *, lens=None, steps=32, cfg_strength=1.0,
+               sway_sampling_coef=None, seed=None, max_duration=4096, vocoder=None, no_ref_audio=False,
+               duplicate_test=False, t_inter=0.1, edit_mask=None):
+        """Same contract as reference model/cfm.py:348-482; the Euler/CFG loop runs in libf5e_b200 on a doubled batch."""
+        self.eval()
+        dit = self.transformer
+        if self.odeint_kwargs.get("method", "euler") != "euler":
+            raise NotImplementedError("f5e_tts_b200.CFM: only the fixed-grid Euler solver is implemented")
+        dtype = next(self.parameters()).dtype
+        if cond.ndim == 2:  # raw wave
+            cond = self.mel_spec(cond).permute(0, 2, 1)
+            assert cond.shape[-1] == self.num_channels
+        cond = cond.to(dtype)
+        batch, cond_seq_len, device = *cond.shape[:2], cond.device
+        if lens is None:
+            lens = torch.full((batch,), cond_seq_len, device=device, dtype=torch.long)
+        if isinstance(text, list):
+            if self.vocab_char_map is not None:
+                if self.use_align_loss or self.use_cross_mask:
+                    text = [[x for pair in zip(["_"] * len(t), t) for x in pair] + ["_"] for t in text]  # durpred.intersperse
+                text = list_str_to_idx(text, self.vocab_char_map).to(device)
+            else:
+                text = list_str_to_tensor(text).to(device)
+            assert text.shape[0] == batch
+        # ---- integer / mask logic: identical ops to cfm.py:393-428 ----
+        cond_mask = lens_to_mask(lens)
+        if edit_mask is not None:
+            cond_mask = cond_mask & edit_mask
+        if isinstance(duration, int):
+            duration = torch.full((batch,), duration, device=device, dtype=torch.long)
+        if text is not None:
+            duration = torch.maximum(torch.maximum((text != -1).sum(dim=-1), lens) + 1, duration)
+        else:
+            duration = torch.maximum(lens + 1, duration)
+        duration = duration.clamp(max=max_duration)
+        max_duration = int(duration.amax())
+        if duplicate_test:
+            test_cond = F.pad(cond, (0, 0, cond_seq_len, max_duration - 2 * cond_seq_len), value=0.0)
+        cond = F.pad(cond, (0, 0, 0, max_duration - cond_seq_len), value=0.0)
+        if no_ref_audio:
+            cond = torch.zeros_like(cond)
+        cond_mask = F.pad(cond_mask, (0, max_duration - cond_mask.shape[-1]), value=False).unsqueeze(-1)
+        step_cond = torch.where(cond_mask, cond, torch.zeros_like(cond))
+        # ---- noise: torch's RNG so that y0 is bit-identical to the reference (cfm.py:449-457) ----
+        y0 = []
+        for dur in duration:
+            if seed is not None:
+                torch.manual_seed(seed)
+            y0.append(torch.randn(int(dur), self.num_channels, device=self.device, dtype=step_cond.dtype))
+        y0 = torch.nn.utils.rnn.pad_sequence(y0, padding_value=0, batch_first=True)
+        t_start = 0
+        if duplicate_test:
+            t_start = t_inter
+            y0 = (1 - t_start) * y0 + t_start * test_cond
+            steps = int(steps * (1 - t_start))
+        t = torch.linspace(t_start, 1, steps + 1, device=self.device, dtype=step_cond.dtype)
+        if sway_sampling_coef is not None:
+            t = t + sway_sampling_coef * (torch.cos(torch.pi / 2 * t) - 1 + t)
+        dts = (t[1:] - t[:-1]).float().tolist()  # torchdiffeq: dt = t1 - t0 in the model dtype
+
+        # ---- device loop ----
+        P = dit._get_plan()
+        B, N, md, td = batch, max_duration, self.num_channels, dit.text_dim
+        use_cfg = cfg_strength >= 1e-5
+        S = 2 * B if use_cfg else B
+        tens, buf = dit._workspace(S, N)
+        xc = tens["x_cat"]
+        rows = B * N
+        halves = [(False, xc[:rows])] + ([(True, xc[rows:])] if use_cfg else [])
+        for drop, xh in halves:
+            ops.pack_cols(xh, 0, y0.reshape(rows, md))
+            ops.pack_cols(xh, md, None if drop else step_cond.reshape(rows, md), md)
+            ops.pack_cols(xh, 2 * md, dit._text_embed(text, B, N, drop).view(rows, td))
+            if dit.use_ppg:
+                ops.pack_cols(xh, 2 * md + td, dit._ppg_embed(ppg, N, drop, B).view(rows, td))
+        mod = dit._modulation(t[:-1])
+        klen = duration.to(torch.int32).repeat(2 if use_cfg else 1).contiguous() if batch > 1 else None
+        cos, sin = dit._rope(N)
+        y = y0.float().contiguous()
+        traj = torch.empty(steps, B, N, md, device=y.device, dtype=torch.float32) if self.store_trajectory else None
+        dt_arr = (C.c_float * steps)(*dts)
+        check(_lib.load().f5e_ode_solve(C.byref(P.model), C.byref(buf), ptr(y), ptr(mod), P.mod_size, dt_arr, steps,
+                                        C.c_float(cfg_strength), ptr(klen), ptr(cos), ptr(sin), B, N, ptr(traj),
+                                        int(self.emulate_lowp_state and dtype != torch.float32), int(self.use_cuda_graph),
+                                        stream_ptr()), "f5e_ode_solve")
+        dit.clear_cache()
+        sampled = y.to(dtype)
+        if traj is not None:
+            trajectory = torch.cat([y0.unsqueeze(0), traj.to(dtype)], dim=0)
+        else:
+            trajectory = torch.stack([y0, sampled])
+        out = torch.where(cond_mask, cond, sampled)
+        if vocoder is not None:
+            out = vocoder(out.permute(0, 2, 1))
+        return out, trajectory

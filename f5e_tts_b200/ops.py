@@ -110,3 +110,56 @@ def conv_pos(x, w_packed, bias, samples, n_pad, *, groups=16, act=_lib.ACT_MISH,
     check(_lib.load().f5e_conv_pos(ptr(x), ptr(w_packed), samples, n_pad, dim, groups, C.byref(ep), stream_ptr()),
           "f5e_conv_pos")
     return out
+
+
+def pack_cols(dst, col0, src, cols=None):
+    """dst[:, col0:col0+cols] = bf16(src) (src fp32/bf16 2-D, row-strided ok; None writes zeros)."""
+    _cuda_bf16(dst, "dst")
+    assert dst.dim() == 2 and dst.stride(1) == 1
+    rows = dst.shape[0]
+    if src is not None:
+        if src.dtype not in (torch.float32, torch.bfloat16):
+            src = src.float()
+        assert src.dim() == 2 and src.shape[0] == rows and src.stride(1) == 1
+        cols = src.shape[1] if cols is None else cols
+    check(_lib.load().f5e_pack_cols(ptr(dst), dst.stride(0), col0, ptr(src), int(src is not None and src.dtype == torch.float32),
+                                    0 if src is None else src.stride(0), rows, cols, stream_ptr()), "f5e_pack_cols")
+    return dst
+
+
+def text_gather(text, table, pos, n_pad, *, drop=False, mask_padding=True, add_pos=True):
+    """text int64 [B, nt] (pad -1) -> bf16 [B, n_pad, dim]."""
+    _cuda_bf16(table, "table")
+    B, nt = text.shape
+    text = text.to(torch.int64).contiguous()
+    dim = table.shape[1]
+    out = torch.empty(B, n_pad, dim, device=table.device, dtype=torch.bfloat16)
+    check(_lib.load().f5e_text_gather(ptr(text), B, nt, ptr(table), ptr(pos), 0 if pos is None else pos.shape[0], ptr(out),
+                                      n_pad, dim, int(drop), int(mask_padding), int(add_pos and pos is not None),
+                                      stream_ptr()), "f5e_text_gather")
+    return out
+
+
+def dwconv7(x, w, b):
+    _cuda_bf16(x, "x")
+    B, N, Cc = x.shape
+    out = torch.empty_like(x)
+    check(_lib.load().f5e_dwconv7(ptr(x), ptr(w), ptr(b), ptr(out), B, N, Cc, stream_ptr()), "f5e_dwconv7")
+    return out
+
+
+def grn(x, gamma, beta):
+    _cuda_bf16(x, "x")
+    B, N, Cc = x.shape
+    out = torch.empty_like(x)
+    scratch = torch.empty(B, Cc, device=x.device, dtype=torch.float32)
+    check(_lib.load().f5e_grn(ptr(x), ptr(gamma), ptr(beta), ptr(out), ptr(scratch), B, N, Cc, stream_ptr()), "f5e_grn")
+    return out
+
+
+def unfold_frames(x, taps):
+    _cuda_bf16(x, "x")
+    B, N, Cc = x.shape
+    out = torch.empty(B, N, taps * Cc, device=x.device, dtype=torch.bfloat16)
+    check(_lib.load().f5e_unfold_frames(ptr(x), ptr(out), B, N, Cc, taps, stream_ptr()), "f5e_unfold_frames")
+    return out

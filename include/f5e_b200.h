@@ -103,6 +103,11 @@ int f5e_dwconv7(const void* x_bf16, const float* w, const float* b, void* out_bf
 int f5e_grn(const void* x_bf16, const float* gamma, const float* beta, void* out_bf16, float* scratch, int32_t samples,
             int32_t n_pad, int32_t C, void* stream);
 
+/* out[s, n, tap*C + c] = x[s, n + tap - taps/2, c] (zero outside the sample): turns the dense k=5 Conv1d of
+ * PPGEmbedding (backbones/dit.py:124-135) into one GEMM with K = taps*C. */
+int f5e_unfold_frames(const void* x_bf16, void* out_bf16, int32_t samples, int32_t n_pad, int32_t C, int32_t taps,
+                      void* stream);
+
 /* ---------------------------------------------------------------------------------------------------
  * DiT evaluation and the Euler/CFG ODE loop
  * ------------------------------------------------------------------------------------------------- */

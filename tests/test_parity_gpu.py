@@ -1,0 +1,109 @@
+"""GPU parity of the product path (through the C ABI) against the oracle on the same seeded weights / inputs.
+
+Bar (north_star): integer/bool side products bit exact; floating point within a stated bf16 tolerance.  The
+tolerance is anchored on the oracle itself: the product (bf16 operands, fp32 accumulation, fused epilogues) must
+be no further from the fp32 oracle than K_TOL x the distance of the SAME oracle run in bf16 (what the reference
+does on a GPU in bf16), plus an absolute floor.
+"""
+import pytest
+import torch
+
+from oracle import f5e_oracle as O
+
+pytestmark = pytest.mark.gpu
+K_TOL = 2.0
+
+
+def rel_l2(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).norm() / b.norm().clamp_min(1e-12)).item()
+
+
+def build(cfg, seed, dev):
+    from f5e_tts_b200.model import CFM, DiT
+    sd = O.make_state_dict(cfg, seed)
+    sd = {k: v.to(torch.bfloat16).float() for k, v in sd.items()}  # bf16-representable weights on both sides
+    ppg_config = dict(use_ppg=cfg.use_ppg, ppg_dim=cfg.ppg_dim, use_transformer=False, transformer_config={})
+    cb_config = dict(use_codebook=cfg.use_codebook, num_vars=cfg.cb_num_vars, temp_start=2.0, temp_stop=0.5,
+                     temp_decay=0.999, groups=cfg.cb_groups, combine_groups=False, weight_proj_depth=1, weight_proj_factor=1)
+    dit = DiT(dim=cfg.dim, depth=cfg.depth, heads=cfg.heads, ff_mult=cfg.ff_mult, mel_dim=cfg.mel_dim,
+              text_num_embeds=cfg.text_num_embeds, text_dim=cfg.text_dim, text_mask_padding=cfg.text_mask_padding,
+              conv_layers=cfg.conv_layers, pe_attn_head=cfg.pe_attn_head, ppg_config=ppg_config, cb_config=cb_config)
+    missing, unexpected = dit.load_state_dict(sd, strict=False)
+    assert not unexpected and all("num_batches_tracked" in k or "inv_freq" in k for k in missing), (missing, unexpected)
+    model = CFM(dit, ppg_config=ppg_config, cb_config=cb_config).to(dev).to(torch.bfloat16)
+    return model, sd
+
+
+def inputs(cfg, B, N, seed, dev, ppg=False):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(B, N, cfg.mel_dim, generator=g)
+    cond = torch.randn(B, N, cfg.mel_dim, generator=g)
+    text = torch.randint(0, cfg.text_num_embeds, (B, 23), generator=g)
+    if B > 1:
+        text[1, 15:] = -1
+    p = torch.randn(B, N // 2, cfg.ppg_dim, generator=g) if ppg else None
+    return x.to(dev), cond.to(dev), text.to(dev), (p.to(dev) if ppg else None)
+
+
+SMALL = O.DiTConfig(dim=256, depth=2, heads=4, text_dim=256, conv_layers=2, text_num_embeds=50)
+SMALL_PPG = O.DiTConfig(dim=768, depth=2, heads=12, text_dim=256, conv_layers=2, text_num_embeds=50, text_mask_padding=False,
+                        pe_attn_head=1, use_ppg=True, ppg_dim=64)
+BASE2 = O.DiTConfig(depth=2)  # F5TTS_v1_Base widths, 2 layers
+
+
+@pytest.mark.parametrize("cfg,B,N,lens", [(SMALL, 1, 200, None), (SMALL, 3, 333, [333, 150, 290]),
+                                           (SMALL_PPG, 2, 260, [260, 131]), (BASE2, 2, 300, [300, 177])])
+def test_dit_eval_vs_oracle(cuda_dev, cfg, B, N, lens):
+    model, sd = build(cfg, 7, cuda_dev)
+    x, cond, text, ppg = inputs(cfg, B, N, 8, cuda_dev, cfg.use_ppg)
+    mask = None if lens is None else O.lens_to_mask(torch.tensor(lens, device=cuda_dev), N)
+    t = torch.tensor(0.37, device=cuda_dev)
+    o32 = O.OracleDiT(cfg, sd, torch.float32, cuda_dev)
+    o16 = O.OracleDiT(cfg, sd, torch.bfloat16, cuda_dev)
+    for drop in (False, True):
+        ref = o32.sample(x, cond, text, ppg, t, drop, drop, drop, mask)
+        ref16 = o16.sample(x.bfloat16(), cond.bfloat16(), text, ppg if ppg is None else ppg.bfloat16(), t.bfloat16(), drop, drop, drop, mask)
+        got = model.transformer.sample(x.bfloat16(), cond.bfloat16(), text, ppg, t.bfloat16(), drop, drop, drop, mask)
+        model.transformer.clear_cache()
+        for i in range(B):
+            L = N if lens is None else lens[i]
+            e_got, e_ref = rel_l2(got[i, :L], ref[i, :L]), rel_l2(ref16[i, :L], ref[i, :L])
+            print(f"cfg dim={cfg.dim} B={B} drop={drop} sample {i}: product-vs-fp32 {e_got:.3e}  oracle-bf16-vs-fp32 {e_ref:.3e}")
+            assert e_got <= K_TOL * e_ref + 5e-3, (i, e_got, e_ref)
+
+
+@pytest.mark.parametrize("cfg,B", [(SMALL, 1), (SMALL, 3), (SMALL_PPG, 2)])
+def test_cfm_sample_vs_oracle(cuda_dev, cfg, B):
+    model, sd = build(cfg, 17, cuda_dev)
+    g = torch.Generator().manual_seed(18)
+    ref_len = torch.randint(40, 80, (B,), generator=g).to(cuda_dev)
+    dur = torch.randint(150, 300, (B,), generator=g).to(cuda_dev)
+    cond = torch.randn(B, int(ref_len.max()), cfg.mel_dim, generator=g).to(cuda_dev)
+    text = torch.randint(0, cfg.text_num_embeds, (B, 30), generator=g).to(cuda_dev)
+    if B > 1:
+        text[1, 20:] = -1
+    ppg = torch.randn(B, 100, cfg.ppg_dim, generator=g).to(cuda_dev) if cfg.use_ppg else None
+    kw = dict(steps=8, cfg_strength=2.0, sway_sampling_coef=-1.0)
+    # same y0 on every side: draw it once the way CFM.sample does (seeded torch RNG on the device)
+    o32 = O.OracleDiT(cfg, sd, torch.float32, cuda_dev)
+    o16 = O.OracleDiT(cfg, sd, torch.bfloat16, cuda_dev)
+    out16, traj16, aux16 = O.cfm_sample(o16, cond, text, dur, ppg=ppg, lens=ref_len, seed=3, return_aux=True, **kw)
+    out32, traj32, aux32 = O.cfm_sample(o32, cond.bfloat16().float(), text, dur, ppg=ppg, lens=ref_len, y0=aux16["y0"].float(),
+                                        return_aux=True, **kw)
+    got, traj = model.sample(cond, text, ppg, dur, lens=ref_len, seed=3, **kw)
+    assert traj.shape == traj16.shape and got.dtype == torch.bfloat16
+    assert torch.equal(traj[0], aux16["y0"])  # identical noise by construction
+    # paste-back region is bit exact (cond copied through)
+    cm = aux16["cond_mask"].expand_as(got)
+    assert torch.equal(got[cm], out16[cm])
+    for step in (1, kw["steps"]):
+        for i in range(B):
+            L = int(aux16["duration"][i])
+            e_got, e_ref = rel_l2(traj[step][i, :L], traj32[step][i, :L]), rel_l2(traj16[step][i, :L], traj32[step][i, :L])
+            print(f"dim={cfg.dim} B={B} step {step} sample {i}: product-vs-fp32 {e_got:.3e}  oracle-bf16-vs-fp32 {e_ref:.3e}")
+            assert e_got <= K_TOL * e_ref + 5e-3, (step, i, e_got, e_ref)
+    # CUDA-graph path gives the same bits as the stream path
+    model.use_cuda_graph = True
+    got2, _ = model.sample(cond, text, ppg, dur, lens=ref_len, seed=3, **kw)
+    assert torch.equal(got2, got)
