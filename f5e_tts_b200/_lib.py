@@ -33,6 +33,18 @@ def lib_path() -> Path:
     return _LIB_PATH
 
 
+def header_path() -> Path:
+    return _HERE.parent / "include" / "f5e_b200.h"
+
+
+def exported_symbols() -> list[str]:
+    """Names of every function include/f5e_b200.h declares (the C ABI the library must export)."""
+    import re
+
+    src = re.sub(r"/\*.*?\*/", "", header_path().read_text(), flags=re.S)
+    return sorted(set(re.findall(r"\b(f5e_[a-z0-9_]+)\s*\(", src)))
+
+
 def load():
     """Load (building first if the sources are newer and nvcc is present) the shared library."""
     global _lib
@@ -50,6 +62,8 @@ def load():
         raise RuntimeError(f"{_LIB_PATH} not found; run `python -m f5e_tts_b200.build`")
     lib = C.CDLL(str(_LIB_PATH))
     lib.f5e_last_error.restype = C.c_char_p
+    lib.f5e_launch_count.restype = C.c_int64
+    lib.f5e_prof_end.restype = C.c_int64
     _lib = lib
     return lib
 

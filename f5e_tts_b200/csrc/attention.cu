@@ -274,6 +274,7 @@ int attention(cudaStream_t st, const __nv_bfloat16* qkv, int ld_qkv, __nv_bfloat
   int rc = make_tmap_2d(&tm, qkv, 2, (uint64_t)3 * inner, (uint64_t)samples * n_pad, (uint64_t)ld_qkv * 2, ATT_DH, 128);
   if (rc) return rc;
   dim3 grid((n_pad + ATT_BM - 1) / ATT_BM, heads, samples);
+  LaunchScope ls(st, PROF_ATTN, samples, n_pad, heads);
   attention_kernel<<<grid, ATT_THREADS, ATT_SMEM_TOTAL, st>>>(tm, out, ldo, klen, n_pad, inner,
                                                               scale * 1.4426950408889634f);
   F5E_CUDA_CHECK(cudaGetLastError());

@@ -158,6 +158,7 @@ int conv_pos(cudaStream_t st, const __nv_bfloat16* x, const __nv_bfloat16* wp, i
   if (rc) return rc;
   const int tiles = samples * ((n_pad + CV_BM - 1) / CV_BM) * groups;
   const int grid = tiles < num_sms() ? tiles : num_sms();
+  LaunchScope ls(st, PROF_CONV, samples, n_pad, dim);
   conv_pos_kernel<<<grid, CV_THREADS, CV_SMEM_TOTAL, st>>>(tmX, tmW, samples, n_pad, dim, cpg, ep);
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;

@@ -66,6 +66,7 @@ int norm_mod(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int M,
   F5E_REQUIRE(D % 256 == 0 && D >= 256 && D <= 2048, "norm_mod: D=%d must be a multiple of 256 in [256,2048]", D);
   if (n_pad <= 0) n_pad = M;
   const int grid = (M + 7) / 8;
+  LaunchScope ls(st, PROF_NORM, M, D, 0);
 #define F5E_NM(CH)                                                                                             \
   case CH:                                                                                                     \
     norm_mod_kernel<CH><<<grid, 256, 0, st>>>(x, out, M, mul, add, mod_stride, n_pad, plus_one, eps);          \
@@ -125,6 +126,7 @@ int cfg_euler(cudaStream_t st, const float* pred, int ld_pred, float* y, __nv_bf
   int grid = (int)((total + 255) / 256);
   const int cap = num_sms() * 8;
   if (grid > cap) grid = cap;
+  LaunchScope ls(st, PROF_ELEM, rows, C, 0);
   cfg_euler_kernel<<<grid, 256, 0, st>>>(pred, ld_pred, y, x_cat, ld_cat, traj, rows, C, dt, cfg, round_bf16);
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;

@@ -34,6 +34,7 @@ int pack_cols(cudaStream_t st, __nv_bfloat16* dst, int ld_dst, int col0, const v
   const long long total = (long long)rows * (cols / 2);
   int grid = (int)((total + 255) / 256);
   if (grid > num_sms() * 16) grid = num_sms() * 16;
+  LaunchScope ls(st, PROF_ELEM, rows, cols, 1);
   if (src_is_f32)
     pack_cols_kernel<float><<<grid, 256, 0, st>>>(dst, ld_dst, col0, (const float*)src, ld_src, rows, cols);
   else
@@ -79,6 +80,7 @@ int text_gather(cudaStream_t st, const int64_t* text, int samples, int nt, const
                 int max_pos, __nv_bfloat16* out, int n_pad, int dim, int drop, int mask_padding, int add_pos) {
   F5E_REQUIRE(samples > 0 && n_pad > 0 && dim % 2 == 0, "text_gather: bad shape");
   dim3 grid(n_pad, samples);
+  LaunchScope ls(st, PROF_ELEM, samples, n_pad, 2);
   text_gather_kernel<<<grid, 128, 0, st>>>(text, nt, table, pos, max_pos, out, n_pad, dim, drop, mask_padding, add_pos);
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;
@@ -124,6 +126,7 @@ int dwconv7(cudaStream_t st, const __nv_bfloat16* x, const float* w, const float
             int n_pad, int C) {
   F5E_REQUIRE(samples > 0 && n_pad > 0 && C % 2 == 0, "dwconv7: bad shape");
   dim3 grid((C / 2 + 255) / 256, (n_pad + DW_FRAMES - 1) / DW_FRAMES, samples);
+  LaunchScope ls(st, PROF_ELEM, samples, n_pad, 3);
   dwconv7_kernel<<<grid, 256, 0, st>>>(x, w, b, out, n_pad, C);
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;
@@ -189,8 +192,12 @@ int grn(cudaStream_t st, const __nv_bfloat16* x, const float* gamma, const float
   F5E_REQUIRE(samples > 0 && n_pad > 0 && C % 2 == 0 && C <= 8192, "grn: bad shape");
   F5E_CUDA_CHECK(cudaMemsetAsync(scratch, 0, (size_t)samples * C * sizeof(float), st));
   dim3 g1((C / 2 + 255) / 256, (n_pad + GRN_SLAB - 1) / GRN_SLAB, samples);
-  grn_sumsq_kernel<<<g1, 256, 0, st>>>(x, scratch, n_pad, C);
+  {
+    LaunchScope ls(st, PROF_ELEM, samples, n_pad, 4);
+    grn_sumsq_kernel<<<g1, 256, 0, st>>>(x, scratch, n_pad, C);
+  }
   dim3 g2(1, (n_pad + GRN_SLAB - 1) / GRN_SLAB, samples);
+  LaunchScope ls(st, PROF_ELEM, samples, n_pad, 5);
   grn_apply_kernel<<<g2, 256, (C + 8) * sizeof(float), st>>>(x, scratch, gamma, beta, out, n_pad, C);
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;
@@ -217,6 +224,7 @@ unfold_frames_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restr
 int unfold_frames(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int samples, int n_pad, int C, int taps) {
   F5E_REQUIRE(samples > 0 && n_pad > 0 && C % 8 == 0 && taps % 2 == 1, "unfold_frames: bad shape");
   dim3 grid(n_pad, samples);
+  LaunchScope ls(st, PROF_ELEM, samples, n_pad, 6);
   unfold_frames_kernel<<<grid, 256, 0, st>>>(x, out, n_pad, C, taps);
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;

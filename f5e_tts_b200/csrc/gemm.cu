@@ -153,6 +153,7 @@ static int launch_gemm(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMa
   using S = GemmSmem<BN, STAGES>;
   const int tiles = ((M + GEMM_BM - 1) / GEMM_BM) * ((N + BN - 1) / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
+  LaunchScope ls(st, PROF_GEMM, M, N, K);
   gemm_bf16_kernel<BN, STAGES><<<grid, GEMM_THREADS, S::TOTAL, st>>>(tmA, tmB, M, N, K, ep);
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;

@@ -50,4 +50,16 @@ int attention_configure();
 int conv_pos_configure();
 const char* last_error();
 
+// ---- launch accounting / in-stream kernel timing (bench.py's roofline leg) --------------------------
+// Every launcher opens a LaunchScope: it bumps the library's launch counter and, when profiling of its
+// class is enabled (f5e_prof_begin), brackets the launch with a CUDA event pair on the launching stream.
+enum ProfClass : int { PROF_GEMM = 1, PROF_ATTN = 2, PROF_CONV = 4, PROF_NORM = 8, PROF_ELEM = 16, PROF_DSP = 32,
+                       PROF_VQ = 64 };
+struct LaunchScope {
+  LaunchScope(cudaStream_t st, int cls, long long a = 0, long long b = 0, long long c = 0);
+  ~LaunchScope();
+  cudaStream_t st;
+  int rec;
+};
+
 }  // namespace f5e

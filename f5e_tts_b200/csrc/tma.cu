@@ -2,7 +2,10 @@
 // (resolved at run time so the library does not link against libcuda directly).
 #include <cstdarg>
 #include <cstdio>
+#include <atomic>
 #include <mutex>
+#include <vector>
+#include "../../include/f5e_b200.h"
 #include "host.h"
 
 namespace f5e {
@@ -97,3 +100,73 @@ int make_tmap_3d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t in
 }
 
 }  // namespace f5e
+
+// ---------------------------------------------------------------------------------------------
+// launch accounting and in-stream timing
+// ---------------------------------------------------------------------------------------------
+namespace f5e {
+namespace {
+struct ProfRec { cudaEvent_t a, b; int cls; long long d[3]; };
+std::mutex g_prof_mu;
+std::vector<ProfRec> g_prof;
+std::vector<cudaEvent_t> g_event_pool;
+std::atomic<int> g_prof_mask{0};
+std::atomic<long long> g_launches{0};
+
+cudaEvent_t take_event() {
+  if (!g_event_pool.empty()) { cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
+}  // namespace
+
+LaunchScope::LaunchScope(cudaStream_t s, int cls, long long a, long long b, long long c) : st(s), rec(-1) {
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  if (!(g_prof_mask.load(std::memory_order_relaxed) & cls)) return;
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(s, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) return;  // not inside a graph capture
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  ProfRec r{take_event(), take_event(), cls, {a, b, c}};
+  if (!r.a || !r.b) return;
+  cudaEventRecord(r.a, s);
+  g_prof.push_back(r);
+  rec = (int)g_prof.size() - 1;
+}
+LaunchScope::~LaunchScope() {
+  if (rec < 0) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (rec < (int)g_prof.size()) cudaEventRecord(g_prof[rec].b, st);
+}
+}  // namespace f5e
+
+extern "C" {
+int64_t f5e_launch_count(void) { return f5e::g_launches.load(); }
+
+int f5e_prof_begin(int32_t class_mask) {
+  std::lock_guard<std::mutex> lk(f5e::g_prof_mu);
+  for (auto& r : f5e::g_prof) { f5e::g_event_pool.push_back(r.a); f5e::g_event_pool.push_back(r.b); }
+  f5e::g_prof.clear();
+  f5e::g_prof_mask.store(class_mask);
+  return 0;
+}
+
+int64_t f5e_prof_end(void) {
+  f5e::g_prof_mask.store(0);
+  std::lock_guard<std::mutex> lk(f5e::g_prof_mu);
+  for (auto& r : f5e::g_prof) cudaEventSynchronize(r.b);
+  return (int64_t)f5e::g_prof.size();
+}
+
+int f5e_prof_read(int64_t index, int32_t* cls, float* ms, int64_t* dims3) {
+  std::lock_guard<std::mutex> lk(f5e::g_prof_mu);
+  F5E_REQUIRE(index >= 0 && index < (int64_t)f5e::g_prof.size(), "f5e_prof_read: index %lld out of range", (long long)index);
+  const auto& r = f5e::g_prof[index];
+  float t = 0.f;
+  F5E_CUDA_CHECK(cudaEventElapsedTime(&t, r.a, r.b));
+  if (cls) *cls = r.cls;
+  if (ms) *ms = t;
+  if (dims3) { dims3[0] = r.d[0]; dims3[1] = r.d[1]; dims3[2] = r.d[2]; }
+  return 0;
+}
+}  // extern "C"

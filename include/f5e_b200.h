@@ -25,6 +25,18 @@ const char* f5e_last_error(void);
 int f5e_check_device(void);
 int f5e_version(void);
 
+/* ---- launch accounting and in-stream kernel timing (used by bench.py; nothing here is on the data path) ----
+ * Every kernel launch of the library bumps a counter.  f5e_prof_begin(mask) additionally brackets each launch whose
+ * class is in `mask` with a CUDA event pair on the launching stream (skipped inside a graph capture);
+ * f5e_prof_end() synchronises those events and returns the number of records; f5e_prof_read() returns one record:
+ * class, elapsed ms and three launch dimensions (GEMM: M,N,K; attention: samples,n_pad,heads; ...). */
+enum { F5E_PROF_GEMM = 1, F5E_PROF_ATTN = 2, F5E_PROF_CONV = 4, F5E_PROF_NORM = 8, F5E_PROF_ELEM = 16, F5E_PROF_DSP = 32,
+       F5E_PROF_VQ = 64 };
+int64_t f5e_launch_count(void);
+int f5e_prof_begin(int32_t class_mask);
+int64_t f5e_prof_end(void);
+int f5e_prof_read(int64_t index, int32_t* cls, float* ms, int64_t* dims3);
+
 /* ---- activation ids for f5e_epilogue.act ---- */
 enum { F5E_ACT_NONE = 0, F5E_ACT_GELU_TANH = 1, F5E_ACT_GELU_ERF = 2, F5E_ACT_MISH = 3, F5E_ACT_RELU = 4,
        F5E_ACT_SILU = 5 };
