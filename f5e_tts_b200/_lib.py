@@ -5,7 +5,7 @@ There is deliberately no fallback: if the library is missing or a call fails, a 
 from __future__ import annotations
 
 import ctypes as C
-import os
+import os  # noqa: F401
 from pathlib import Path
 
 _HERE = Path(__file__).resolve().parent
@@ -26,6 +26,7 @@ class Epilogue(C.Structure):
         ("row_len", C.c_void_p), ("n_pad", C.c_int32),
         ("rope_cos", C.c_void_p), ("rope_sin", C.c_void_p),
         ("rope_inner", C.c_int32), ("rope_heads", C.c_int32),
+        ("residual_f32", C.c_int32), ("out_split3", C.c_int32),
     ]
 
 

@@ -13,6 +13,7 @@ static EpiParams to_epi(const f5e_epilogue* e, int M) {
   p.row_len = e->row_len; p.n_pad = e->n_pad > 0 ? e->n_pad : M;
   p.rope_cos = e->rope_cos; p.rope_sin = e->rope_sin;
   p.rope_inner = e->rope_inner; p.rope_heads = e->rope_heads;
+  p.res_f32 = e->residual_f32; p.split3 = e->out_split3;
   return p;
 }
 
@@ -35,7 +36,10 @@ int f5e_gemm_bf16(const void* A, int32_t lda, const void* W, int32_t ldw, int32_
                   const f5e_epilogue* ep, void* stream) {
   F5E_REQUIRE(A && W && ep, "f5e_gemm_bf16: null argument");
   F5E_REQUIRE(ep->out_f32 ? ep->ldo % 4 == 0 : ep->ldo % 8 == 0, "f5e_gemm_bf16: ldo=%d breaks 16-byte row alignment", ep->ldo);
-  F5E_REQUIRE(ep->residual == nullptr || ep->ldr % 8 == 0, "f5e_gemm_bf16: ldr=%d breaks 16-byte row alignment", ep->ldr);
+  F5E_REQUIRE(ep->residual == nullptr || ep->ldr % (ep->residual_f32 ? 4 : 8) == 0,
+              "f5e_gemm_bf16: ldr=%d breaks 16-byte row alignment", ep->ldr);
+  F5E_REQUIRE(ep->out_split3 == 0 || (N % 32 == 0 && ep->out_split3 % 8 == 0 && !ep->out_f32),
+              "f5e_gemm_bf16: out_split3 needs N %% 32 == 0, a bf16 output and an 8-aligned split stride");
   return gemm_bf16((cudaStream_t)stream, (const __nv_bfloat16*)A, lda, (const __nv_bfloat16*)W, ldw, M, N, K,
                    to_epi(ep, M));
 }

@@ -25,6 +25,9 @@ struct EpiParams {
   const float* rope_sin;
   int rope_inner;                  // heads*64 (columns [0, 2*rope_inner) hold Q then K)
   int rope_heads;                  // heads [0, rope_heads) of Q and of K get rotated
+  int res_f32;                     // residual is fp32 [M, ldr] instead of bf16
+  int split3;                      // > 0: bf16 output written as the 3-term split [hi | hi | lo] at columns
+                                   // c, c + split3, c + 2*split3 (A operand of a following fp32-accurate bf16x3 GEMM)
 };
 
 // v: 32 accumulator values for (row, col0 .. col0+31).  M/N are the logical output extents.
@@ -121,7 +124,20 @@ __device__ __forceinline__ void epilogue_chunk(float (&v)[32], int row, int col0
     }
   }
 
-  if (p.residual) {
+  if (p.residual && p.res_f32) {
+    const float* r = reinterpret_cast<const float*>(p.residual) + (size_t)row * p.ldr + col0;
+    if (full) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) {
+        float4 u = *reinterpret_cast<const float4*>(r + i);
+        v[i] += u.x; v[i + 1] += u.y; v[i + 2] += u.z; v[i + 3] += u.w;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (col0 + i < N) v[i] += r[i];
+    }
+  } else if (p.residual) {
     const __nv_bfloat16* r = p.residual + (size_t)row * p.ldr + col0;
     if (full) {
 #pragma unroll
@@ -139,7 +155,25 @@ __device__ __forceinline__ void epilogue_chunk(float (&v)[32], int row, int col0
     }
   }
 
-  if (p.out_f32) {
+  if (p.split3 > 0) {  // requires full chunks (N % 32 == 0, checked by the launcher)
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.ldo + col0;
+#pragma unroll
+    for (int i = 0; i < 32; i += 8) {
+      uint4 hi, lo;
+      uint32_t* h = &hi.x;
+      uint32_t* l = &lo.x;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float a = v[i + 2 * q], b = v[i + 2 * q + 1];
+        const __nv_bfloat16 ah = __float2bfloat16(a), bh = __float2bfloat16(b);
+        h[q] = pack_bf16x2(__bfloat162float(ah), __bfloat162float(bh));
+        l[q] = pack_bf16x2(a - __bfloat162float(ah), b - __bfloat162float(bh));
+      }
+      *reinterpret_cast<uint4*>(o + i) = hi;
+      *reinterpret_cast<uint4*>(o + p.split3 + i) = hi;
+      *reinterpret_cast<uint4*>(o + 2 * p.split3 + i) = lo;
+    }
+  } else if (p.out_f32) {
     float* o = reinterpret_cast<float*>(p.out) + (size_t)row * p.ldo + col0;
     if (full) {
 #pragma unroll

@@ -43,6 +43,20 @@ int dwconv7(cudaStream_t st, const __nv_bfloat16* x, const float* w, const float
 int grn(cudaStream_t st, const __nv_bfloat16* x, const float* gamma, const float* beta, __nv_bfloat16* out,
         float* scratch, int samples, int n_pad, int C);
 int unfold_frames(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int samples, int n_pad, int C, int taps);
+// ---- fp32 DSP front/back end and the Vocos / VQ helpers (dsp.cu, vq.cu) ----
+int melspec(cudaStream_t st, const float* wav, long long ld_wav, int batch, int nw, const float* window, const float* tw,
+            const float* fbT, const int* fb_lo, const int* fb_hi, int n_mels, float* out);
+int istft_head(cudaStream_t st, const float* spec, long long ld_spec, int batch, int t_pad, const int* n_frames,
+               const float* window, const float* tw, float* out, long long ld_out, int out_len);
+int layernorm_f32(cudaStream_t st, const float* x, int M, int D, const float* w, const float* b, float eps,
+                  const int* row_len, int n_pad, float* out_f32, __nv_bfloat16* out_split);
+int dwconv7_f32(cudaStream_t st, const float* x, const float* w, const float* b, float* out, int samples, int n_pad, int C);
+int unfold_mel_split3(cudaStream_t st, const float* mel, long long ld_b, long long ld_c, long long ld_t, const int* t_off,
+                      const int* n_frames, int batch, int t_pad, int C, int taps, int kpad, __nv_bfloat16* out);
+int split3(cudaStream_t st, const float* x, long long ld, int M, int K, __nv_bfloat16* out);
+int vq_select(cudaStream_t st, const float* logits, int ld_logits, const float* x, int ld_x, int dim, const float* W,
+              const float* bias, const float* vars, int M, int G, int V, int vd, int combine_groups, float refine_tol,
+              long long* targets, void* xq, int xq_bf16, float* sums, int* hist, int* refined, float* perplexity);
 // one-time per-device kernel attribute setup (opt-in shared memory sizes); idempotent
 int ensure_configured();
 int gemm_configure();

@@ -1,0 +1,133 @@
+"""Per-utterance sharding of batched evaluation across the GPUs of one box, and the one exchange the path has.
+
+The reference shards `eval_infer_batch.py` by `accelerator.split_between_processes(prompts_all)` - contiguous slices of a
+shuffled list, no tensor exchange, every rank writing its own wav files (eval/eval_infer_batch.py:184-220).  Here:
+  * `plan_shards` forms length-bucketed padded batches under a frame budget and assigns them to ranks by LPT on a cost
+    model a*N + b*N^2 (attention is 18-40 % of the work between 10 s and 30 s utterances), identically on every rank;
+  * the solves themselves share nothing (weights are replicated) - there is NO collective inside the data path;
+  * `gather_varlen` / `gather_padded` bring mels / waveforms to one rank with a single NCCL gather over NVLink
+    (lengths first, then one padded payload), replacing the file-system rendezvous.
+One process per GPU (torchrun); `torch.distributed` is plumbing only.  The same code runs on gloo for the CPU tests.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import torch
+import torch.distributed as dist
+
+# FLOPs of one DiT evaluation of a sample with N valid frames: N * (A + B * N)
+COST_A, COST_B = 378.89e6, 90112.0
+
+
+def utterance_cost(n_frames) -> float:
+    n = float(n_frames)
+    return n * (COST_A + COST_B * n)
+
+
+@dataclass
+class Batch:
+    indices: list          # utterance ids (positions in the caller's list)
+    n_pad: int             # frames every member is padded to
+    cost: float            # modelled FLOPs of one DiT evaluation of the padded batch
+
+
+def make_batches(durations, frame_budget: int, max_batch: int = 64) -> list:
+    """Sort by duration (longest first) and cut padded batches of at most `frame_budget` padded frames."""
+    order = sorted(range(len(durations)), key=lambda i: (-int(durations[i]), i))
+    batches, cur = [], []
+    for i in order:
+        n_pad = int(durations[cur[0]]) if cur else int(durations[i])
+        if cur and ((len(cur) + 1) * n_pad > frame_budget or len(cur) >= max_batch):
+            batches.append(Batch(cur, n_pad, len(cur) * utterance_cost(n_pad)))
+            cur = []
+        cur.append(i)
+    if cur:
+        n_pad = int(durations[cur[0]])
+        batches.append(Batch(cur, n_pad, len(cur) * utterance_cost(n_pad)))
+    return batches
+
+
+def _lpt(batches, world):
+    loads = [0.0] * world
+    shards = [[] for _ in range(world)]
+    for b in sorted(batches, key=lambda b: (-b.cost, b.indices[0])):
+        r = min(range(world), key=lambda r: (loads[r], r))
+        shards[r].append(b)
+        loads[r] += b.cost
+    return shards
+
+
+def plan_shards(durations, world: int, frame_budget: int = 16 * 1031, max_batch: int = 64, balance_tol: float = 1.03) -> list:
+    """-> per rank, the list of `Batch`es it runs.  Longest-processing-time-first on the modelled cost; deterministic.
+    When the batches are too coarse to balance `world` ranks within `balance_tol`, the frame budget is halved (down to a
+    quarter: a batch must still fill the GPU) and the plan rebuilt."""
+    shards = None
+    for div in (1, 2, 4):
+        shards = _lpt(make_batches(durations, max(frame_budget // div, 1), max_batch), world)
+        if imbalance(shards) <= balance_tol:
+            break
+    return shards
+
+
+def imbalance(shards) -> float:
+    """max rank load / mean rank load (1.0 = perfect)."""
+    loads = [sum(b.cost for b in s) for s in shards]
+    mean = sum(loads) / len(loads)
+    return max(loads) / mean if mean > 0 else 1.0
+
+
+def _world():
+    return dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+
+
+def gather_padded(t: torch.Tensor, dst: int = 0):
+    """t [B, L] (L may differ between ranks) -> on `dst`: [world * B, Lmax] zero padded; elsewhere None.
+    One max-reduction of the length, one gather of the payload."""
+    world = _world()
+    if world == 1:
+        return t
+    L = torch.tensor([t.shape[1]], device=t.device, dtype=torch.int64)
+    dist.all_reduce(L, op=dist.ReduceOp.MAX)
+    Lmax = int(L)
+    if t.shape[1] != Lmax:
+        t = torch.nn.functional.pad(t, (0, Lmax - t.shape[1]))
+    t = t.contiguous()
+    rank = dist.get_rank()
+    if rank == dst:
+        out = torch.empty(world * t.shape[0], Lmax, device=t.device, dtype=t.dtype)
+        dist.gather(t, list(out.view(world, t.shape[0], Lmax).unbind(0)), dst=dst)
+        return out
+    dist.gather(t, None, dst=dst)
+    return None
+
+
+def gather_varlen(lens: torch.Tensor, payload: torch.Tensor, dst: int = 0):
+    """Ragged gather: `payload` is the concatenation along dim 0 of this rank's items (item i has lens[i] rows, any trailing
+    shape).  On `dst` returns (all_lens [sum items], all_payload [sum rows, ...]) in rank order; elsewhere (None, None).
+    Lengths travel first (all_gather of the item counts and row totals), then ONE padded gather of the payload."""
+    world = _world()
+    if world == 1:
+        return lens, payload
+    rank = dist.get_rank()
+    dev = payload.device
+    meta = torch.tensor([lens.numel(), payload.shape[0]], device=dev, dtype=torch.int64)
+    metas = torch.empty(world * 2, device=dev, dtype=torch.int64)
+    dist.all_gather_into_tensor(metas, meta)
+    metas_h = metas.view(world, 2).cpu()
+    max_items, max_rows = int(metas_h[:, 0].max()), int(metas_h[:, 1].max())
+    lens_p = torch.zeros(max_items, device=dev, dtype=torch.int64)
+    lens_p[: lens.numel()] = lens.to(dev)
+    pay_p = torch.zeros((max_rows,) + tuple(payload.shape[1:]), device=dev, dtype=payload.dtype)
+    pay_p[: payload.shape[0]] = payload
+    if rank == dst:
+        all_lens = torch.empty(world, max_items, device=dev, dtype=torch.int64)
+        all_pay = torch.empty((world,) + tuple(pay_p.shape), device=dev, dtype=payload.dtype)
+        dist.gather(lens_p, list(all_lens.unbind(0)), dst=dst)
+        dist.gather(pay_p, list(all_pay.unbind(0)), dst=dst)
+        out_l = torch.cat([all_lens[r, : int(metas_h[r, 0])] for r in range(world)])
+        out_p = torch.cat([all_pay[r, : int(metas_h[r, 1])] for r in range(world)])
+        return out_l, out_p
+    dist.gather(lens_p, None, dst=dst)
+    dist.gather(pay_p, None, dst=dst)
+    return None, None

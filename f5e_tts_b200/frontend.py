@@ -1,5 +1,5 @@
-"""MelSpec front end (mirror of reference model/modules.py:104-143).  The CUDA STFT/mel kernel is bound in
-`MelSpec.forward`; see csrc/melspec.cu."""
+"""MelSpec front end (mirror of reference model/modules.py:104-143).  The CUDA STFT/mel kernel (csrc/dsp.cu) is bound
+in `MelSpec.forward` through dsp.mel_spectrogram."""
 from __future__ import annotations
 
 import torch
@@ -15,8 +15,9 @@ class MelSpec(nn.Module):
         self.n_fft, self.hop_length, self.win_length = n_fft, hop_length, win_length
         self.n_mel_channels, self.target_sample_rate = n_mel_channels, target_sample_rate
         self.register_buffer("dummy", torch.tensor(0), persistent=False)
-        self._tables = None
 
     def forward(self, wav):
         from . import dsp
+        if self.dummy.device != wav.device:  # the reference moves itself to the input's device (modules.py:131-132)
+            self.to(wav.device)
         return dsp.mel_spectrogram(self, wav)

@@ -18,7 +18,7 @@ def _cuda_bf16(t: torch.Tensor, name: str) -> None:
 
 
 def gemm(a, w, *, bias=None, act=_lib.ACT_NONE, gate=None, gate_stride=0, residual=None, row_len=None, n_pad=0,
-         rope=None, rope_heads=0, rope_inner=0, out=None, out_f32=False, n=None):
+         rope=None, rope_heads=0, rope_inner=0, out=None, out_f32=False, n=None, split3=0):
     """epilogue(a[M,K] @ w[N,K]^T).  `a`/`w` may be row-strided views (last dim contiguous)."""
     _cuda_bf16(a, "a"), _cuda_bf16(w, "w")
     assert a.dim() == 2 and w.dim() == 2 and a.stride(1) == 1 and w.stride(1) == 1
@@ -26,8 +26,10 @@ def gemm(a, w, *, bias=None, act=_lib.ACT_NONE, gate=None, gate_stride=0, residu
     N = w.shape[0] if n is None else n
     assert w.shape[1] == K
     if out is None:
-        out = torch.empty(M, N, device=a.device, dtype=torch.float32 if out_f32 else torch.bfloat16)
+        out = torch.empty(M, 3 * split3 if split3 else N, device=a.device, dtype=torch.float32 if out_f32 else torch.bfloat16)
     ep = Epilogue()
+    ep.out_split3 = split3
+    ep.residual_f32 = int(residual is not None and residual.dtype == torch.float32)
     ep.out, ep.ldo, ep.out_f32 = out.data_ptr(), out.stride(0), int(out.dtype == torch.float32)
     ep.bias = 0 if bias is None else bias.data_ptr()
     ep.act = act

@@ -58,6 +58,10 @@ typedef struct f5e_epilogue {
   const float* rope_sin;
   int32_t rope_inner;      /* heads * 64 */
   int32_t rope_heads;      /* rotate heads [0, rope_heads) of Q and K */
+  int32_t residual_f32;    /* residual is fp32 [M, ldr] */
+  int32_t out_split3;      /* > 0: bf16 output as the 3-term split [hi | hi | lo] at columns c, c+out_split3,
+                              c+2*out_split3: the A operand of a following fp32-accurate "bf16x3" GEMM whose weight
+                              is packed [W_hi | W_lo | W_hi] along K (used by the fp32 Vocos / VQ paths) */
 } f5e_epilogue;
 
 /* C[M,N] = epilogue(A[M,K] @ W[N,K]^T); bf16 operands, tcgen05 / TMEM fp32 accumulation.
@@ -172,6 +176,77 @@ int f5e_ode_solve(const f5e_dit_model* model, const f5e_dit_buffers* buf, float*
                   const float* dt_host, int32_t steps, float cfg_strength, const int32_t* klen, const float* rope_cos,
                   const float* rope_sin, int32_t batch, int32_t n_pad, float* traj, int32_t round_bf16,
                   int32_t use_graph, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * fp32 front end / back end / codebook
+ * ------------------------------------------------------------------------------------------------- */
+/* MelSpec.forward (model/modules.py:104-143 -> get_vocos_mel_spectrogram :75-101): reflect pad 512, periodic Hann 1024,
+ * hop 256, |rFFT|, HTK mel filterbank, log(clamp(1e-5)).  wav: fp32 [batch, n_samples] (row stride ld_wav);
+ * out: fp32 [batch, n_mels, n_samples / 256 + 1].  Tables (built by the caller once): window [1024]; twiddles
+ * float2[512] = exp(-2 pi i j / 1024); fb_t [n_mels, 513] transposed filterbank with its non-zero bin range
+ * [fb_lo[m], fb_hi[m]) per filter. */
+int f5e_melspec(const float* wav, int64_t ld_wav, int32_t batch, int32_t n_samples, const float* window,
+                const float* twiddles, const float* fb_t, const int32_t* fb_lo, const int32_t* fb_hi, int32_t n_mels,
+                float* out, void* stream);
+
+/* Vocos ISTFTHead after its Linear (published vocos architecture; in-tree corroboration
+ * runtime/triton_trtllm/scripts/export_vocoder_to_onnx.py:45-59, scripts/conv_stft.py:193-234):
+ * spec fp32 [batch, t_pad, ld_spec] rows = (log-magnitude[513] | phase[513]); frames >= n_frames[b] ignored (NULL: all).
+ * out fp32 [batch, ld_out]: samples [0, (n_frames[b]-1)*256) = torch.istft(center=True) of exp/clip/cos/sin, rest of
+ * [0, out_len) zero. */
+int f5e_istft_head(const float* spec, int64_t ld_spec, int32_t batch, int32_t t_pad, const int32_t* n_frames,
+                   const float* window, const float* twiddles, float* out, int64_t ld_out, int32_t out_len, void* stream);
+
+typedef struct f5e_vocos_block {   /* ConvNeXtBlock; w1 / w2 are bf16 3-term splits [W_hi | W_lo | W_hi] along K */
+  const float* dw_w; const float* dw_b;   /* dwconv [dim, 7], [dim] */
+  const float* ln_w; const float* ln_b;
+  const void* w1; const float* b1;        /* pwconv1 [inter, 3*dim] */
+  const void* w2; const float* b2;        /* pwconv2 [dim, 3*inter] */
+  const float* gamma;                     /* layer scale [dim] */
+} f5e_vocos_block;
+
+typedef struct f5e_vocos_model {
+  int32_t dim, inter, n_layers, in_ch, k_embed, n_fft, hop;
+  const void* w_embed; const float* b_embed;   /* backbone.embed as [dim, 3*k_embed], column tap*in_ch + c, zero padded */
+  const float* ln0_w; const float* ln0_b;      /* backbone.norm */
+  const f5e_vocos_block* blocks;               /* HOST array [n_layers] */
+  const float* lnf_w; const float* lnf_b;      /* backbone.final_layer_norm */
+  const void* w_head; const float* b_head;     /* head.out [n_fft + 2, 3*dim] */
+  const float* window; const float* twiddles;
+} f5e_vocos_model;
+
+typedef struct f5e_vocos_buffers {   /* rows = batch * t_pad */
+  void* a_embed;   /* bf16 [rows, 3*k_embed] */
+  float* x;        /* fp32 [rows, dim] */
+  float* h;        /* fp32 [rows, dim] */
+  void* a1;        /* bf16 [rows, 3*dim] */
+  void* a2;        /* bf16 [rows, 3*inter] */
+  float* spec;     /* fp32 [rows, round_up(n_fft + 2, 4)] */
+} f5e_vocos_buffers;
+
+/* vocoder.decode (call sites infer/utils_infer.py:488-489, eval/eval_infer_batch.py:211-212) for a whole batch of
+ * variable-length spans in one go: sample b decodes mel frames [t_off[b], t_off[b] + n_frames[b]) of
+ * mel[b, c, t] = mel[b*ld_b + c*ld_c + t*ld_t] (so both [B,100,T] and [B,T,100] layouts work without a copy);
+ * every span is decoded exactly as if it were alone (zero "same" padding at ITS ends).  out as in f5e_istft_head. */
+int f5e_vocos_decode(const f5e_vocos_model* model, const f5e_vocos_buffers* buf, const float* mel, int64_t ld_b,
+                     int64_t ld_c, int64_t ld_t, const int32_t* t_off, const int32_t* n_frames, int32_t batch,
+                     int32_t t_pad, float* out, int64_t ld_out, int32_t out_len, void* stream);
+
+/* GumbelVectorQuantizer.forward / .forward_idx in eval mode (model/modules.py:877-950): logits = x W^T + b on tcgen05
+ * (bf16x3 split, fp32 accumulate), per-group first-max argmax (near ties re-decided with sequential fp32 FMAs so indices
+ * are those of an fp32 implementation), code-vector gather, histogram / mean-softmax perplexities.
+ * x fp32 [M, dim]; w_split3 bf16 [groups*num_vars, 3*dim]; w_f32 [groups*num_vars, dim]; vars fp32 [(combine ? 1 : groups)
+ * * num_vars, var_dim]; scratch a_split3 bf16 [M, 3*dim], logits fp32 [M, ld_logits], prob_sums fp32 / hist int32
+ * [groups*num_vars]; outputs targets int64 [M, groups], xq [M, groups*var_dim] (fp32 or bf16), perplexity[2] =
+ * (code_perplexity, prob_perplexity), n_refined = number of near-tie re-decisions. */
+int f5e_vq_quantize(const float* x, int32_t ld_x, int32_t M, int32_t dim, const void* w_split3, const float* w_f32,
+                    const float* bias, const float* vars, int32_t groups, int32_t num_vars, int32_t var_dim,
+                    int32_t combine_groups, float refine_tol, void* a_split3, float* logits, int32_t ld_logits,
+                    int64_t* targets, void* xq, int32_t xq_bf16, float* prob_sums, int32_t* hist, int32_t* n_refined,
+                    float* perplexity, void* stream);
+
+/* fp32 [M, K] -> bf16 [M, 3K] = [hi | hi | lo]: the A operand of a bf16x3 GEMM (test hook / building block). */
+int f5e_split3(const float* x, int64_t ld, int32_t M, int32_t K, void* out_bf16, void* stream);
 
 #ifdef __cplusplus
 }

@@ -419,3 +419,67 @@ def vq_forward(sd: dict, x: torch.Tensor, groups=2, num_vars=100) -> dict:
     xq = xq.view(bsz * tsz, groups, num_vars, -1).sum(-2).view(bsz, tsz, -1)
     return {"x": xq, "targets": targets, "num_vars": num_vars * groups, "code_perplexity": code_ppl,
             "prob_perplexity": prob_ppl}
+
+
+# -------------------------------------------------------------------------------------------------------
+# Vocos mel-24khz decode.  PARITY UNPINNED for the backbone: the `vocos` package is an unpinned third-party dependency
+# (pyproject.toml:41) that is neither vendored nor installed, and no reference test touches it; the backbone below is
+# restated from the package's published architecture (VocosBackbone + ConvNeXtBlock + ISTFTHead, config of
+# charactr/vocos-mel-24khz).  The head is corroborated in-tree: runtime/triton_trtllm/scripts/export_vocoder_to_onnx.py:45-59
+# (exp / clip 1e2 / cos / sin) and scripts/conv_stft.py:193-234 (window, overlap-add, envelope); SURVEY appendix A pins
+# ISTFT(padding="center") == torch.istft(center=True) numerically.
+# -------------------------------------------------------------------------------------------------------
+def make_vocos_state_dict(seed: int = 4321, in_ch=100, dim=512, inter=1536, n_layers=8, n_fft=1024) -> dict:
+    """Random weights in the package's state-dict layout with its init (trunc_normal std 0.02, zero bias,
+    gamma = 1 / n_layers); norm affine parameters are perturbed so that they are exercised."""
+    g = torch.Generator().manual_seed(seed)
+    sd = {}
+
+    def tn(*shape):
+        return torch.nn.init.trunc_normal_(torch.empty(*shape), std=0.02, generator=g)
+
+    sd["backbone.embed.weight"], sd["backbone.embed.bias"] = tn(dim, in_ch, 7), 0.02 * torch.randn(dim, generator=g)
+    sd["backbone.norm.weight"], sd["backbone.norm.bias"] = 1 + 0.1 * torch.randn(dim, generator=g), 0.1 * torch.randn(dim, generator=g)
+    for i in range(n_layers):
+        p = f"backbone.convnext.{i}"
+        sd[p + ".dwconv.weight"], sd[p + ".dwconv.bias"] = tn(dim, 1, 7) * 10, 0.02 * torch.randn(dim, generator=g)
+        sd[p + ".norm.weight"], sd[p + ".norm.bias"] = 1 + 0.1 * torch.randn(dim, generator=g), 0.1 * torch.randn(dim, generator=g)
+        sd[p + ".pwconv1.weight"], sd[p + ".pwconv1.bias"] = tn(inter, dim) * 3, 0.02 * torch.randn(inter, generator=g)
+        sd[p + ".pwconv2.weight"], sd[p + ".pwconv2.bias"] = tn(dim, inter) * 3, 0.02 * torch.randn(dim, generator=g)
+        sd[p + ".gamma"] = torch.full((dim,), 1.0 / n_layers) * (1 + 0.1 * torch.randn(dim, generator=g))
+    sd["backbone.final_layer_norm.weight"] = 1 + 0.1 * torch.randn(dim, generator=g)
+    sd["backbone.final_layer_norm.bias"] = 0.1 * torch.randn(dim, generator=g)
+    sd["head.out.weight"], sd["head.out.bias"] = tn(n_fft + 2, dim) * 3, 0.1 * torch.randn(n_fft + 2, generator=g)
+    sd["head.istft.window"] = torch.hann_window(n_fft)
+    return sd
+
+
+@torch.no_grad()
+def vocos_decode(sd: dict, mel: torch.Tensor, n_fft=1024, hop=256) -> torch.Tensor:
+    """mel [B, 100, T] fp32 -> wav [B, (T-1)*hop]   (Vocos.decode = ISTFTHead(VocosBackbone(mel)))."""
+    sd = {k: v.to(mel.device, torch.float32) for k, v in sd.items()}
+    dim = sd["backbone.embed.weight"].shape[0]
+    x = F.conv1d(mel.float(), sd["backbone.embed.weight"], sd["backbone.embed.bias"], padding=3)
+    x = F.layer_norm(x.transpose(1, 2), (dim,), sd["backbone.norm.weight"], sd["backbone.norm.bias"], eps=1e-6).transpose(1, 2)
+    i = 0
+    while f"backbone.convnext.{i}.gamma" in sd:
+        p = f"backbone.convnext.{i}"
+        r = x
+        h = F.conv1d(x, sd[p + ".dwconv.weight"], sd[p + ".dwconv.bias"], padding=3, groups=dim).transpose(1, 2)
+        h = F.layer_norm(h, (dim,), sd[p + ".norm.weight"], sd[p + ".norm.bias"], eps=1e-6)
+        h = F.linear(F.gelu(F.linear(h, sd[p + ".pwconv1.weight"], sd[p + ".pwconv1.bias"])), sd[p + ".pwconv2.weight"],
+                     sd[p + ".pwconv2.bias"])
+        x = r + (sd[p + ".gamma"] * h).transpose(1, 2)
+        i += 1
+    x = F.layer_norm(x.transpose(1, 2), (dim,), sd["backbone.final_layer_norm.weight"], sd["backbone.final_layer_norm.bias"], eps=1e-6)
+    x = F.linear(x, sd["head.out.weight"], sd["head.out.bias"]).transpose(1, 2)
+    return istft_head(x, n_fft, hop)
+
+
+def istft_head(x: torch.Tensor, n_fft=1024, hop=256) -> torch.Tensor:
+    """x [B, n_fft + 2, T] = (log-magnitude | phase) -> wav; vocos ISTFTHead after its Linear."""
+    mag, p = x.chunk(2, dim=1)
+    mag = torch.clip(torch.exp(mag), max=1e2)
+    S = mag * (torch.cos(p) + 1j * torch.sin(p))
+    window = torch.hann_window(n_fft, device=x.device, dtype=x.dtype)
+    return torch.istft(S, n_fft, hop, n_fft, window, center=True)
