@@ -10,9 +10,14 @@
 //   warp 1    MMA issuer: S = Q K_j^T (UMMA 128x128x16, K-major operands) into TMEM cols [0,128);
 //             O_j = P_j V_j (UMMA 128x64x16, A = P from smem, B = V as an MN-major operand) into
 //             TMEM cols [128,192).
-//   warps 2-5 softmax: thread == query row.  Pass 1 reads S for the running max, pass 2 re-reads S,
-//             exponentiates (ex2), writes bf16 P in the UMMA 128B-swizzled layout, and the per-block
-//             O_j is folded into fp32 register accumulators with the usual online-softmax rescale.
+//             O accumulates ACROSS key blocks in TMEM (tcgen05.mma accumulate), it is never read back per block.
+//   warps 2-5 softmax: thread == query row.  S_j is read from TMEM exactly once (128 fp32 registers, one wait) and
+//             released immediately so QK_{j+1} overlaps the softmax math; row max, ex2, row sum and the bf16 P tile
+//             (UMMA 128B-swizzled layout in shared memory) come from registers.  The running maximum is LAZY
+//             (FlashAttention-4 style): O in TMEM is rescaled (tcgen05.ld / tcgen05.st) only when a row's maximum grew
+//             by more than 2^8 since the last rescale, which after the first block is rare; P and the row sum use
+//             the same stale reference so the final O / l is exact.  TMEM reads per 128x128 block drop from
+//             160 KB (S twice + O) to 64 KB - TMEM read bandwidth was the limiter of the first version.
 // Input layout: qkv [rows, 3*inner] with Q | K | V column blocks (what the fused QKV GEMM writes,
 // RoPE already applied); output [rows, inner].
 #include "host.h"
@@ -125,7 +130,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __res
         for (int k = 0; k < ATT_BN / 16; ++k) {
           const uint64_t pdesc = umma_desc_kmajor_sw128(p_addr + (k >> 2) * ATT_TILE_BYTES) + 2 * (k & 3);
           const uint64_t vdesc = umma_desc_mnmajor_sw128(v_addr + k * 2048, 1024, 1024);
-          umma_f16_ss(tmem_base + ATT_TMEM_O, pdesc, vdesc, idesc_pv, k != 0);
+          umma_f16_ss(tmem_base + ATT_TMEM_O, pdesc, vdesc, idesc_pv, (j | k) != 0);  // O accumulates over key blocks
         }
         umma_commit(&kv_empty[sl]);
         umma_commit(o_full);
@@ -137,7 +142,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __res
           tc_fence_after();
           do_qk(j + 1);
         }
-        mbar_wait(p_full, j & 1);  // P_j in smem, O_{j-1} drained
+        mbar_wait(p_full, j & 1);  // P_j in smem, O rescaled if needed
         tc_fence_after();
         do_pv(j);
       }
@@ -149,104 +154,99 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __res
     const uint32_t t_o = t_s + ATT_TMEM_O;
     uint8_t* p_row = smem + ATT_SMEM_P + r * 128;
     const int sw = r & 7;
-    float m = -INFINITY, l = 0.f, alpha_prev = 1.f;
-    float o[ATT_DH];
-#pragma unroll
-    for (int i = 0; i < ATT_DH; ++i) o[i] = 0.f;
-
-    auto fold_o = [&](float a) {
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        uint32_t raw[32];
-        tmem_ld_32x32(t_o + c * 32, raw);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o[c * 32 + i] = fmaf(o[c * 32 + i], a, __uint_as_float(raw[i]));
-      }
-    };
+    float m_ref = -INFINITY;  // exponent reference (scaled log2 units); lags the true row maximum by at most 8
+    float l = 0.f;
 
     for (int j = 0; j < nb; ++j) {
-      const int kbase = j * ATT_BN;
-      const int kvalid = klen - kbase;  // keys [0, kvalid) of this block are real (>= 128 except last block)
+      const int kvalid = klen - j * ATT_BN;  // keys [0, kvalid) of this block are real (>= 128 except in the last block)
       mbar_wait(s_full, j & 1);
       tc_fence_after();
-      float mx = m;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t raw[32];
-        tmem_ld_32x32(t_s + c * 32, raw);
+      float s[ATT_BN];
+      {
+        uint32_t* raw = reinterpret_cast<uint32_t*>(s);
+        tmem_ld_32x32(t_s, *reinterpret_cast<uint32_t(*)[32]>(raw));
+        tmem_ld_32x32(t_s + 32, *reinterpret_cast<uint32_t(*)[32]>(raw + 32));
+        tmem_ld_32x32(t_s + 64, *reinterpret_cast<uint32_t(*)[32]>(raw + 64));
+        tmem_ld_32x32(t_s + 96, *reinterpret_cast<uint32_t(*)[32]>(raw + 96));
         tmem_ld_wait();
-        if (kvalid >= (c + 1) * 32) {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(raw[i]) * scale_log2);
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (c * 32 + i < kvalid) mx = fmaxf(mx, __uint_as_float(raw[i]) * scale_log2);
-        }
       }
-      const float alpha = ex2_approx(m - mx);  // first block: ex2(-inf) = 0
-      m = mx;
-      if (j > 0) {
-        mbar_wait(o_full, (j - 1) & 1);  // PV_{j-1} done: O_{j-1} readable, P buffer reusable
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(s_free);  // S_j is in registers: QK_{j+1} may overwrite the TMEM columns now
+      if (kvalid < ATT_BN) {
+#pragma unroll
+        for (int i = 0; i < ATT_BN; ++i)
+          if (i >= kvalid) s[i] = -INFINITY;
+      }
+      float mx = s[0];
+#pragma unroll
+      for (int i = 1; i < ATT_BN; ++i) mx = fmaxf(mx, s[i]);
+      const float m_new = fmaxf(m_ref, mx * scale_log2);
+      const bool grow = m_new - m_ref > 8.0f;  // always true in the first block (m_ref = -inf)
+      if (j > 0) {  // PV_{j-1} finished: O_{j-1} is complete and the P buffer may be rewritten
+        mbar_wait(o_full, (j - 1) & 1);
         tc_fence_after();
-        fold_o(alpha_prev);
       }
-      alpha_prev = alpha;
-      float rowsum = 0.f;
-      const float neg_m = -m;
+      if (__any_sync(0xffffffffu, grow)) {
+        const float alpha = grow ? ex2_approx(m_ref - m_new) : 1.0f;  // first block: ex2(-inf) = 0
+        if (grow) m_ref = m_new;
+        l *= alpha;
+        if (j > 0) {
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t raw[32];
-        tmem_ld_32x32(t_s + c * 32, raw);
-        tmem_ld_wait();
-        float p[32];
-        if (kvalid >= (c + 1) * 32) {
+          for (int c = 0; c < ATT_DH / 16; ++c) {
+            uint32_t o16[16];
+            tmem_ld_32x16(t_o + c * 16, o16);
+            tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 32; ++i) p[i] = ex2_approx(fmaf(__uint_as_float(raw[i]), scale_log2, neg_m));
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i)
-            p[i] = (c * 32 + i < kvalid) ? ex2_approx(fmaf(__uint_as_float(raw[i]), scale_log2, neg_m)) : 0.f;
-        }
-#pragma unroll
-        for (int i = 0; i < 32; ++i) rowsum += p[i];
-        // 32 keys = 4 chunks of 16 B; chunk g (0..15 over the 128 keys) lives in atom g>>3, position (g&7)^sw
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int g = c * 4 + q;
-          uint4 u;
-          u.x = pack_bf16x2(p[q * 8 + 0], p[q * 8 + 1]);
-          u.y = pack_bf16x2(p[q * 8 + 2], p[q * 8 + 3]);
-          u.z = pack_bf16x2(p[q * 8 + 4], p[q * 8 + 5]);
-          u.w = pack_bf16x2(p[q * 8 + 6], p[q * 8 + 7]);
-          *reinterpret_cast<uint4*>(p_row + (g >> 3) * ATT_TILE_BYTES + (((g & 7) ^ sw) << 4)) = u;
+            for (int i = 0; i < 16; ++i) o16[i] = __float_as_uint(__uint_as_float(o16[i]) * alpha);
+            tmem_st_32x16(t_o + c * 16, o16);
+          }
+          tmem_st_wait();
         }
       }
-      l = fmaf(l, alpha, rowsum);
+      const float neg_m = -m_ref;
+      float rowsum = 0.f;
+#pragma unroll
+      for (int i = 0; i < ATT_BN; ++i) {
+        s[i] = ex2_approx(fmaf(s[i], scale_log2, neg_m));  // masked keys: ex2(-inf) = 0
+        rowsum += s[i];
+      }
+      l += rowsum;
+      // 128 keys = 16 chunks of 16 B; chunk g lives in atom g>>3, position (g&7)^sw
+#pragma unroll
+      for (int g = 0; g < 16; ++g) {
+        uint4 u;
+        u.x = pack_bf16x2(s[g * 8 + 0], s[g * 8 + 1]);
+        u.y = pack_bf16x2(s[g * 8 + 2], s[g * 8 + 3]);
+        u.z = pack_bf16x2(s[g * 8 + 4], s[g * 8 + 5]);
+        u.w = pack_bf16x2(s[g * 8 + 6], s[g * 8 + 7]);
+        *reinterpret_cast<uint4*>(p_row + (g >> 3) * ATT_TILE_BYTES + (((g & 7) ^ sw) << 4)) = u;
+      }
       tc_fence_before();
       fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) {
-        mbar_arrive(s_free);
-        mbar_arrive(p_full);
-      }
+      if (lane == 0) mbar_arrive(p_full);
     }
     mbar_wait(o_full, (nb - 1) & 1);
     tc_fence_after();
-    fold_o(alpha_prev);
     const int q = q0 + r;
-    if (q < n_pad) {
-      const float inv = 1.0f / l;
-      __nv_bfloat16* orow = out + (size_t)(row_base + q) * ldo + head * ATT_DH;
+    const float inv = 1.0f / l;
+    __nv_bfloat16* orow = out + (size_t)(row_base + q) * ldo + head * ATT_DH;
+#pragma unroll 1
+    for (int c = 0; c < ATT_DH / 32; ++c) {
+      uint32_t raw[32];
+      tmem_ld_32x32(t_o + c * 32, raw);
+      tmem_ld_wait();
+      if (q < n_pad) {
 #pragma unroll
-      for (int i = 0; i < ATT_DH; i += 8) {
-        uint4 u;
-        u.x = pack_bf16x2(o[i] * inv, o[i + 1] * inv);
-        u.y = pack_bf16x2(o[i + 2] * inv, o[i + 3] * inv);
-        u.z = pack_bf16x2(o[i + 4] * inv, o[i + 5] * inv);
-        u.w = pack_bf16x2(o[i + 6] * inv, o[i + 7] * inv);
-        *reinterpret_cast<uint4*>(orow + i) = u;
+        for (int i = 0; i < 32; i += 8) {
+          uint4 u;
+          u.x = pack_bf16x2(__uint_as_float(raw[i]) * inv, __uint_as_float(raw[i + 1]) * inv);
+          u.y = pack_bf16x2(__uint_as_float(raw[i + 2]) * inv, __uint_as_float(raw[i + 3]) * inv);
+          u.z = pack_bf16x2(__uint_as_float(raw[i + 4]) * inv, __uint_as_float(raw[i + 5]) * inv);
+          u.w = pack_bf16x2(__uint_as_float(raw[i + 6]) * inv, __uint_as_float(raw[i + 7]) * inv);
+          *reinterpret_cast<uint4*>(orow + c * 32 + i) = u;
+        }
       }
     }
   }

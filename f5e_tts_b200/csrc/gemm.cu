@@ -1,13 +1,16 @@
 // Dense bf16 GEMM for sm_100a:  C[M,N] = epilogue(A[M,K] @ W[N,K]^T), fp32 accumulation.
 //
-// Persistent, warp-specialised kernel (one CTA per SM):
+// Persistent, warp-specialised kernel (one CTA per SM, 320 threads):
 //   warp 0   : TMA producer  - streams 128x64 A tiles and BNx64 W tiles (128B swizzle) through a
 //              STAGES-deep shared-memory ring guarded by full/empty mbarriers.
 //   warp 1   : MMA issuer    - one thread issues tcgen05.mma (UMMA 128 x BN x 16) into one of TWO
 //              TMEM accumulator stages, tcgen05.commit releases ring slots / publishes accumulators.
-//   warps 2-5: epilogue      - tcgen05.ld the accumulator (thread == row, 32 columns at a time),
-//              apply the fused epilogue (bias / RoPE / activation / row mask / gate / residual)
-//              and store.  It overlaps with the next tile's main loop thanks to the second TMEM stage.
+//   warps 2-9: epilogue      - warp w owns TMEM lanes 32*(w%4).. (its 32 rows) and one half of the tile's columns,
+//              64 columns at a time: tcgen05.ld -> registers -> fused epilogue (bias / RoPE / activation / row mask /
+//              gate) -> 128B-swizzled staging block in shared memory -> ONE TMA store per 32x64 block.  A residual that
+//              aliases the output (x += gate * branch, every DiT block) is not read at all: the block is sent with a
+//              TMA reduce-add (cp.reduce.async.bulk.tensor .add), so the read-modify-write happens in L2.
+//              The epilogue of tile i overlaps the main loop of tile i+1 through the second TMEM stage.
 //
 // Replaces the F.linear (cuBLAS) calls of reference model/modules.py:442-449 (to_q/k/v), :494
 // (to_out), :342-353 (FeedForward), dit.py:169-177 (InputEmbedding.proj), dit.py:470 (proj_out).
@@ -17,21 +20,52 @@ namespace f5e {
 
 constexpr int GEMM_BM = 128;
 constexpr int GEMM_BK = 64;
-constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_EPI_WARPS = 8;
+constexpr int GEMM_THREADS = 64 + 32 * GEMM_EPI_WARPS;
+constexpr int GEMM_STAGING_BYTES = 4096;  // 32 rows x 128 bytes per epilogue warp
 
 template <int BN, int STAGES>
 struct GemmSmem {
   static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
   static constexpr int B_BYTES = BN * GEMM_BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
+  static constexpr int STAGING_OFFSET = STAGES * STAGE_BYTES;
+  static constexpr int BAR_OFFSET = STAGING_OFFSET + GEMM_EPI_WARPS * GEMM_STAGING_BYTES;
   static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;  // barriers + alignment slack
 };
 
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, const void* smem_src, int c0, int c1) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+
+// Send the warp's staged 32 x 128-byte block to global memory (plain store or reduce-add); lane 0 issues.
+__device__ __forceinline__ void staging_flush(const CUtensorMap* tmC, const uint8_t* stage, int c0, int c1, bool accumulate,
+                                              int lane) {
+  fence_proxy_async_smem();
+  __syncwarp();
+  if (lane == 0) {
+    if (accumulate) tma_reduce_add_2d(tmC, stage, c0, c1);
+    else tma_store_2d(tmC, stage, c0, c1);
+    tma_store_commit();
+  }
+}
+// The staging block may be rewritten once the previous bulk store has finished READING it.
+__device__ __forceinline__ void staging_acquire(int lane) {
+  if (lane == 0) tma_store_wait_read<0>();
+  __syncwarp();
+}
+// 16-byte slot j (0..7) of row r inside a 128B-swizzled 32-row block
+__device__ __forceinline__ uint4* staging_slot(uint8_t* stage, int r, int j) {
+  return reinterpret_cast<uint4*>(stage + r * 128 + ((j ^ (r & 7)) << 4));
+}
+
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
-gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N,
-                 int K, EpiParams ep) {
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const __grid_constant__ CUtensorMap tmC, int M, int N, int K, EpiParams ep, int accumulate) {
   using S = GemmSmem<BN, STAGES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -52,13 +86,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmC);
     for (int i = 0; i < STAGES; ++i) {
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull_bar[i], 1);
-      mbar_init(&tempty_bar[i], 4);
+      mbar_init(&tempty_bar[i], GEMM_EPI_WARPS);
     }
     mbar_fence_init();
   }
@@ -113,30 +148,184 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else {
-    const int quarter = warp & 3;  // TMEM lane quarter this warp may read
+    const int quarter = warp & 3;            // TMEM lane quarter this warp may read
+    const int half = (warp - 2) >> 2;        // which half of the tile's columns
+    constexpr int WCOLS = BN / 2;            // columns per epilogue warp
+    uint8_t* stage_buf = smem + S::STAGING_OFFSET + (warp - 2) * GEMM_STAGING_BYTES;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m_blk = tile / n_blocks, n_blk = tile - m_blk * n_blocks;
+      const int row0 = m_blk * GEMM_BM + quarter * 32;
+      const int row = row0 + lane;
+      const int rowc = row < M ? row : M - 1;  // clamped row for table look-ups (stores are clipped by TMA)
+      const int sample = rowc / ep.n_pad, frame = rowc - sample * ep.n_pad;
+      const bool row_masked = ep.row_len && frame >= __ldg(ep.row_len + sample);
+      const int wcol0 = n_blk * BN + half * WCOLS;
+      // RoPE angles of this row: the same 32 (cos, sin) pairs serve every head of the tile
+      float rc[32], rs[32];
+      const bool tile_rope = ep.rope_cos && wcol0 < 2 * ep.rope_inner && wcol0 < N;
+      if (tile_rope) {
+        const float4* cp = reinterpret_cast<const float4*>(ep.rope_cos + (size_t)frame * 32);
+        const float4* sp = reinterpret_cast<const float4*>(ep.rope_sin + (size_t)frame * 32);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const float4 c4 = __ldg(cp + q), s4 = __ldg(sp + q);
+          rc[4 * q] = c4.x; rc[4 * q + 1] = c4.y; rc[4 * q + 2] = c4.z; rc[4 * q + 3] = c4.w;
+          rs[4 * q] = s4.x; rs[4 * q + 1] = s4.y; rs[4 * q + 2] = s4.z; rs[4 * q + 3] = s4.w;
+        }
+      }
+      const float* gate = ep.gate ? ep.gate + (ep.gate_stride ? (size_t)sample * ep.gate_stride : 0) : nullptr;
+
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
-      const int row = m_blk * GEMM_BM + quarter * 32 + lane;
-      const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16) + acc * BN;
+      const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16) + acc * BN + half * WCOLS;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t raw[32];
-        tmem_ld_32x32(taddr + c * 32, raw);
-        tmem_ld_wait();
-        float v[32];
+      for (int cc = 0; cc < WCOLS / 64; ++cc) {
+        const int col0 = wcol0 + cc * 64;
+        if (col0 >= N) break;  // warp-uniform
+        float v[64];
+        {
+          uint32_t r0[32], r1[32];
+          tmem_ld_32x32(taddr + cc * 64, r0);
+          tmem_ld_32x32(taddr + cc * 64 + 32, r1);
+          tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[i]);
-        epilogue_chunk(v, row, n_blk * BN + c * 32, M, N, ep);
+          for (int i = 0; i < 32; ++i) { v[i] = __uint_as_float(r0[i]); v[32 + i] = __uint_as_float(r1[i]); }
+        }
+        const bool full = col0 + 64 <= N;
+        if (ep.bias) {
+          if (full) {
+#pragma unroll
+            for (int i = 0; i < 64; i += 4) {
+              const float4 b = __ldg(reinterpret_cast<const float4*>(ep.bias + col0 + i));
+              v[i] += b.x; v[i + 1] += b.y; v[i + 2] += b.z; v[i + 3] += b.w;
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 64; ++i)
+              if (col0 + i < N) v[i] += __ldg(ep.bias + col0 + i);
+          }
+        }
+        if (tile_rope && col0 < 2 * ep.rope_inner && ((col0 % ep.rope_inner) >> 6) < ep.rope_heads) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {  // interleaved pairs (2j, 2j+1) share angle j
+            const float a = v[2 * j], b = v[2 * j + 1];
+            v[2 * j] = a * rc[j] - b * rs[j];
+            v[2 * j + 1] = b * rc[j] + a * rs[j];
+          }
+        }
+        switch (ep.act) {
+          case ACT_GELU_TANH:
+#pragma unroll
+            for (int i = 0; i < 64; ++i) v[i] = gelu_tanh_fast(v[i]);
+            break;
+          case ACT_GELU_ERF:
+#pragma unroll
+            for (int i = 0; i < 64; ++i) v[i] = gelu_erf(v[i]);
+            break;
+          case ACT_MISH:
+#pragma unroll
+            for (int i = 0; i < 64; ++i) v[i] = mish(v[i]);
+            break;
+          case ACT_RELU:
+#pragma unroll
+            for (int i = 0; i < 64; ++i) v[i] = fmaxf(v[i], 0.0f);
+            break;
+          case ACT_SILU:
+#pragma unroll
+            for (int i = 0; i < 64; ++i) v[i] = silu(v[i]);
+            break;
+          default:
+            break;
+        }
+        if (row_masked) {
+#pragma unroll
+          for (int i = 0; i < 64; ++i) v[i] = 0.0f;
+        }
+        if (gate) {
+          if (full) {
+#pragma unroll
+            for (int i = 0; i < 64; i += 4) {
+              const float4 g = __ldg(reinterpret_cast<const float4*>(gate + col0 + i));
+              v[i] *= g.x; v[i + 1] *= g.y; v[i + 2] *= g.z; v[i + 3] *= g.w;
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 64; ++i)
+              if (col0 + i < N) v[i] *= __ldg(gate + col0 + i);
+          }
+        }
+        if (ep.residual && !accumulate && row < M) {  // residual that does NOT alias the output: read it here
+          if (ep.res_f32) {
+            const float* r = reinterpret_cast<const float*>(ep.residual) + (size_t)row * ep.ldr + col0;
+#pragma unroll
+            for (int i = 0; i < 64; ++i)
+              if (col0 + i < N) v[i] += r[i];
+          } else {
+            const __nv_bfloat16* r = ep.residual + (size_t)row * ep.ldr + col0;
+#pragma unroll
+            for (int i = 0; i < 64; ++i)
+              if (col0 + i < N) v[i] += __bfloat162float(r[i]);
+          }
+        }
+        // ---- registers -> swizzled staging -> TMA store / reduce-add
+        if (ep.out_f32) {
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {  // 32 fp32 columns = 128 bytes per row per block
+            if (col0 + 32 * h >= N) break;
+            staging_acquire(lane);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              *staging_slot(stage_buf, lane, j) =
+                  make_uint4(__float_as_uint(v[32 * h + 4 * j]), __float_as_uint(v[32 * h + 4 * j + 1]),
+                             __float_as_uint(v[32 * h + 4 * j + 2]), __float_as_uint(v[32 * h + 4 * j + 3]));
+            staging_flush(&tmC, stage_buf, col0 + 32 * h, row0, accumulate != 0, lane);
+          }
+        } else if (ep.split3 > 0) {
+          uint4 lo[8];
+          staging_acquire(lane);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            uint4 hi;
+            uint32_t* hp = &hi.x;
+            uint32_t* lp = &lo[j].x;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const float a = v[8 * j + 2 * q], b = v[8 * j + 2 * q + 1];
+              const float ah = __bfloat162float(__float2bfloat16(a)), bh = __bfloat162float(__float2bfloat16(b));
+              hp[q] = pack_bf16x2(ah, bh);
+              lp[q] = pack_bf16x2(a - ah, b - bh);
+            }
+            *staging_slot(stage_buf, lane, j) = hi;
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmC, stage_buf, col0, row0);
+            tma_store_2d(&tmC, stage_buf, col0 + ep.split3, row0);
+            tma_store_commit();
+          }
+          staging_acquire(lane);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) *staging_slot(stage_buf, lane, j) = lo[j];
+          staging_flush(&tmC, stage_buf, col0 + 2 * ep.split3, row0, false, lane);
+        } else {
+          staging_acquire(lane);
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *staging_slot(stage_buf, lane, j) =
+                make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                           pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+          staging_flush(&tmC, stage_buf, col0, row0, accumulate != 0, lane);
+        }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    if (lane == 0) tma_store_wait<0>();  // every bulk store has completed before the CTA's shared memory goes away
   }
 
   tc_fence_before();
@@ -148,13 +337,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 }
 
 template <int BN, int STAGES>
-static int launch_gemm(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& tmB, int M, int N, int K,
-                       const EpiParams& ep) {
+static int launch_gemm(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, int M, int N,
+                       int K, const EpiParams& ep, int accumulate) {
   using S = GemmSmem<BN, STAGES>;
   const int tiles = ((M + GEMM_BM - 1) / GEMM_BM) * ((N + BN - 1) / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
   LaunchScope ls(st, PROF_GEMM, M, N, K);
-  gemm_bf16_kernel<BN, STAGES><<<grid, GEMM_THREADS, S::TOTAL, st>>>(tmA, tmB, M, N, K, ep);
+  gemm_bf16_kernel<BN, STAGES><<<grid, GEMM_THREADS, S::TOTAL, st>>>(tmA, tmB, tmC, M, N, K, ep, accumulate);
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -172,14 +361,24 @@ int gemm_bf16(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloa
   { int rc0 = ensure_configured(); if (rc0) return rc0; }
   F5E_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_bf16: empty problem (M=%d N=%d K=%d)", M, N, K);
   F5E_REQUIRE(ep.out != nullptr, "gemm_bf16: null output");
+  F5E_REQUIRE(ep.n_pad > 0, "gemm_bf16: n_pad must be positive");
+  F5E_REQUIRE(!(ep.split3 > 0) || (N % 64 == 0 && !ep.out_f32), "gemm_bf16: split3 output needs N %% 64 == 0 and bf16");
   const bool wide = N > 128;
-  CUtensorMap tmA, tmB;
+  // x += epilogue(...) with the residual aliasing the output: the read-modify-write is a TMA reduce-add
+  const bool alias = ep.residual && (const void*)ep.residual == (const void*)ep.out && ep.ldr == ep.ldo &&
+                     (ep.res_f32 != 0) == (ep.out_f32 != 0) && ep.split3 == 0;
+  CUtensorMap tmA, tmB, tmC;
   int rc = make_tmap_2d(&tmA, A, 2, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, GEMM_BK, GEMM_BM);
   if (rc) return rc;
   rc = make_tmap_2d(&tmB, W, 2, (uint64_t)K, (uint64_t)N, (uint64_t)ldw * 2, GEMM_BK, wide ? 256 : 128);
   if (rc) return rc;
-  if (wide) return launch_gemm<256, 4>(st, tmA, tmB, M, N, K, ep);
-  return launch_gemm<128, 6>(st, tmA, tmB, M, N, K, ep);
+  if (ep.out_f32)
+    rc = make_tmap_2d(&tmC, ep.out, 4, (uint64_t)N, (uint64_t)M, (uint64_t)ep.ldo * 4, 32, 32);
+  else
+    rc = make_tmap_2d(&tmC, ep.out, 2, (uint64_t)(ep.split3 > 0 ? 3 * ep.split3 : N), (uint64_t)M, (uint64_t)ep.ldo * 2, 64, 32);
+  if (rc) return rc;
+  if (wide) return launch_gemm<256, 4>(st, tmA, tmB, tmC, M, N, K, ep, alias ? 1 : 0);
+  return launch_gemm<128, 6>(st, tmA, tmB, tmC, M, N, K, ep, alias ? 1 : 0);
 }
 
 }  // namespace f5e
