@@ -17,7 +17,7 @@ FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
     "-Xcompiler", "-fPIC", "--use_fast_math_placeholder",
 ]
-FLAGS = [f for f in FLAGS if f != "--use_fast_math_placeholder"]
+FLAGS = [f for f in FLAGS if f != "--use_fast_math_placeholder"] + os.environ.get("F5E_NVCC_FLAGS", "").split()
 
 
 def _sources():

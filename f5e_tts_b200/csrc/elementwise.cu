@@ -6,57 +6,83 @@ namespace f5e {
 
 // ---------------------------------------------------------------------------------------------
 // norm_mod: out = LN(x) * (plus_one + mul) + add      (reference model/modules.py:301-336, :636)
-// One warp per row; each lane keeps CH chunks of 8 bf16 in registers (D = 256 * CH).
+// Persistent warps: a warp walks rows (row = first, first + stride, ...), keeps the modulation vectors of the current
+// sample in registers (they are shared by all of its rows) and prefetches the next row while it reduces the current
+// one, so per row only the 2*D bytes of x and 2*D bytes of out move.  D = 256 * CH, each lane owns CH chunks of 8.
 // Algorithmic bytes: 2 * M * D * 2.
 // ---------------------------------------------------------------------------------------------
+constexpr int NM_THREADS = 128;
 template <int CH>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(NM_THREADS)
 norm_mod_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, int M,
                 const float* __restrict__ mul, const float* __restrict__ add, int mod_stride, int n_pad,
                 float plus_one, float eps) {
   constexpr int D = CH * 256;
-  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
+  const int wstride = gridDim.x * (NM_THREADS / 32);
+  int row = blockIdx.x * (NM_THREADS / 32) + (threadIdx.x >> 5);
   if (row >= M) return;
-  const uint4* xr = reinterpret_cast<const uint4*>(x + (size_t)row * D);
-  float v[CH][8];
-  float sum = 0.f;
+  float gm[CH][8], ga[CH][8];  // (plus_one + mul), add for this lane's columns
+  int cur_sample = -1;
+  uint4 nxt[CH];
+  {
+    const uint4* xr = reinterpret_cast<const uint4*>(x + (size_t)row * D);
 #pragma unroll
-  for (int c = 0; c < CH; ++c) {
-    uint4 u = xr[c * 32 + lane];
-    float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
-    v[c][0] = a.x; v[c][1] = a.y; v[c][2] = b.x; v[c][3] = b.y;
-    v[c][4] = cc.x; v[c][5] = cc.y; v[c][6] = d.x; v[c][7] = d.y;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) sum += v[c][i];
+    for (int c = 0; c < CH; ++c) nxt[c] = xr[c * 32 + lane];
   }
-  const float mean = warp_sum(sum) * (1.0f / D);
-  float sq = 0.f;
+  for (; row < M; row += wstride) {
+    float v[CH][8];
+    float sum = 0.f;
 #pragma unroll
-  for (int c = 0; c < CH; ++c)
+    for (int c = 0; c < CH; ++c) {
+      const uint4 u = nxt[c];
+      float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+      v[c][0] = a.x; v[c][1] = a.y; v[c][2] = b.x; v[c][3] = b.y;
+      v[c][4] = cc.x; v[c][5] = cc.y; v[c][6] = d.x; v[c][7] = d.y;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float d = v[c][i] - mean;
-      sq += d * d;
+      for (int i = 0; i < 8; ++i) sum += v[c][i];
     }
-  const float rstd = rsqrtf(warp_sum(sq) * (1.0f / D) + eps);
-  const size_t moff = mod_stride ? (size_t)(row / n_pad) * mod_stride : 0;
-  const float4* mp = reinterpret_cast<const float4*>(mul + moff);
-  const float4* ap = reinterpret_cast<const float4*>(add + moff);
-  uint4* orow = reinterpret_cast<uint4*>(out + (size_t)row * D);
+    if (row + wstride < M) {  // prefetch the next row of this warp
+      const uint4* xr = reinterpret_cast<const uint4*>(x + (size_t)(row + wstride) * D);
 #pragma unroll
-  for (int c = 0; c < CH; ++c) {
-    const int e4 = (c * 32 + lane) * 2;  // float4 index of the first of 8 elements
-    float4 m0 = __ldg(mp + e4), m1 = __ldg(mp + e4 + 1), a0 = __ldg(ap + e4), a1 = __ldg(ap + e4 + 1);
-    float m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-    float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-    float r[8];
+      for (int c = 0; c < CH; ++c) nxt[c] = xr[c * 32 + lane];
+    }
+    const int sample = mod_stride ? row / n_pad : 0;
+    if (sample != cur_sample) {
+      cur_sample = sample;
+      const float4* mp = reinterpret_cast<const float4*>(mul + (size_t)sample * mod_stride);
+      const float4* ap = reinterpret_cast<const float4*>(add + (size_t)sample * mod_stride);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) r[i] = (v[c][i] - mean) * rstd * (plus_one + m[i]) + a[i];
-    uint4 u;
-    u.x = pack_bf16x2(r[0], r[1]); u.y = pack_bf16x2(r[2], r[3]);
-    u.z = pack_bf16x2(r[4], r[5]); u.w = pack_bf16x2(r[6], r[7]);
-    orow[c * 32 + lane] = u;
+      for (int c = 0; c < CH; ++c) {
+        const int e4 = (c * 32 + lane) * 2;
+        const float4 m0 = __ldg(mp + e4), m1 = __ldg(mp + e4 + 1), a0 = __ldg(ap + e4), a1 = __ldg(ap + e4 + 1);
+        gm[c][0] = plus_one + m0.x; gm[c][1] = plus_one + m0.y; gm[c][2] = plus_one + m0.z; gm[c][3] = plus_one + m0.w;
+        gm[c][4] = plus_one + m1.x; gm[c][5] = plus_one + m1.y; gm[c][6] = plus_one + m1.z; gm[c][7] = plus_one + m1.w;
+        ga[c][0] = a0.x; ga[c][1] = a0.y; ga[c][2] = a0.z; ga[c][3] = a0.w;
+        ga[c][4] = a1.x; ga[c][5] = a1.y; ga[c][6] = a1.z; ga[c][7] = a1.w;
+      }
+    }
+    const float mean = warp_sum(sum) * (1.0f / D);
+    float sq = 0.f;
+#pragma unroll
+    for (int c = 0; c < CH; ++c)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float d = v[c][i] - mean;
+        sq += d * d;
+      }
+    const float rstd = rsqrtf(warp_sum(sq) * (1.0f / D) + eps);
+    uint4* orow = reinterpret_cast<uint4*>(out + (size_t)row * D);
+#pragma unroll
+    for (int c = 0; c < CH; ++c) {
+      float r[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) r[i] = (v[c][i] - mean) * rstd * gm[c][i] + ga[c][i];
+      uint4 u;
+      u.x = pack_bf16x2(r[0], r[1]); u.y = pack_bf16x2(r[2], r[3]);
+      u.z = pack_bf16x2(r[4], r[5]); u.w = pack_bf16x2(r[6], r[7]);
+      orow[c * 32 + lane] = u;
+    }
   }
 }
 
@@ -65,11 +91,14 @@ int norm_mod(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int M,
   F5E_REQUIRE(M > 0, "norm_mod: M must be positive");
   F5E_REQUIRE(D % 256 == 0 && D >= 256 && D <= 2048, "norm_mod: D=%d must be a multiple of 256 in [256,2048]", D);
   if (n_pad <= 0) n_pad = M;
-  const int grid = (M + 7) / 8;
+  const int wpb = NM_THREADS / 32;
+  int grid = (M + wpb - 1) / wpb;
+  const int cap = num_sms() * 3;  // persistent: 3 resident CTAs per SM (140 registers x 128 threads)
+  if (grid > cap) grid = cap;
   LaunchScope ls(st, PROF_NORM, M, D, 0);
-#define F5E_NM(CH)                                                                                             \
-  case CH:                                                                                                     \
-    norm_mod_kernel<CH><<<grid, 256, 0, st>>>(x, out, M, mul, add, mod_stride, n_pad, plus_one, eps);          \
+#define F5E_NM(CH)                                                                                                    \
+  case CH:                                                                                                            \
+    norm_mod_kernel<CH><<<grid, NM_THREADS, 0, st>>>(x, out, M, mul, add, mod_stride, n_pad, plus_one, eps);         \
     break;
   switch (D / 256) {
     F5E_NM(1) F5E_NM(2) F5E_NM(3) F5E_NM(4) F5E_NM(5) F5E_NM(6) F5E_NM(7) F5E_NM(8)
