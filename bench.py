@@ -183,15 +183,11 @@ def cpu_arm(sd_fp32, w, nfe, budget_s):
                        f"{steps_done} of {nfe} Euler steps timed ({t_used:.1f} s) and extrapolated linearly, Vocos decode timed in full"), per_step
 
 
-def run_reference(a, rank):
-    if rank != 0:
-        return
+def reference_weights():
+    """The same seeded weights as the B200 arm, on the CPU (the drop-in DiT is used as a parameter container only)."""
     import torch
 
-    torch.manual_seed(1234)
-    w = make_workload(a.batch, a.seconds, 0)
-    _, sd = build_model("cpu") if False else (None, None)
-    from f5e_tts_b200.model import DiT  # parameter container only (no device work): same weights as the B200 arm
+    from f5e_tts_b200.model import DiT
 
     torch.manual_seed(1234)
     dit = DiT(**ARCH)
@@ -202,9 +198,18 @@ def run_reference(a, rank):
         for m in (dit.norm_out.linear, dit.proj_out):
             m.weight.normal_(0, 0.02)
             m.bias.normal_(0, 0.02)
-    sd = {k: v.detach() for k, v in dit.state_dict().items()}
+    return {k: v.detach() for k, v in dit.state_dict().items()}
+
+
+def run_reference(a, rank):
+    """--impl reference: the reference algorithm (oracle port) on the host cores; rank 0 only."""
+    if rank != 0:
+        return
+    w = make_workload(a.batch, a.seconds, 0)
+    sd = reference_weights()
     vals, per = [], []
     budget = max(2.0, min(a.cpu_budget_s, 120.0 / max(1, a.steps + a.warmup)))
+    r = None
     for s in range(a.warmup + a.steps):
         r, per_step = cpu_arm(sd, w, a.nfe, budget)
         if s >= a.warmup:
