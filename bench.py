@@ -329,7 +329,7 @@ def run_b200(a, rank, local_rank, world):
     for i in range(nrec):
         lib.f5e_prof_read(C.c_int64(i), C.byref(cls), C.byref(ms_), dims)
         M, N, K = dims[0], dims[1], dims[2]
-        if cls.value == 1 and M == rows_padded and (N, K) in DIT_GEMM_NK:
+        if cls.value == 1 and M in (rows_padded, int(rows_valid)) and (N, K) in DIT_GEMM_NK:  # padded or packed rows
             g_ms += ms_.value
             g_fl += 2.0 * rows_valid * N * K  # algorithmic: valid rows only, padding not credited
             g_n += 1

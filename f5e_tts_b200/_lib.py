@@ -26,7 +26,7 @@ class Epilogue(C.Structure):
         ("row_len", C.c_void_p), ("n_pad", C.c_int32),
         ("rope_cos", C.c_void_p), ("rope_sin", C.c_void_p),
         ("rope_inner", C.c_int32), ("rope_heads", C.c_int32),
-        ("residual_f32", C.c_int32), ("out_split3", C.c_int32),
+        ("residual_f32", C.c_int32), ("out_split3", C.c_int32), ("row_info", C.c_void_p),
     ]
 
 

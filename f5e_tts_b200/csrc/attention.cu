@@ -48,24 +48,27 @@ __device__ __forceinline__ float ex2_approx(float x) {
 }
 
 struct AttItem {
-  int sample, head, q0, klen, nb;
+  int sample, head, q0, klen, nb, row_base, q_limit;
 };
 // Work item w -> (sample, head, query tile); false when the tile holds padded queries only (skipped by every role).
-__device__ __forceinline__ bool att_decode(int w, int qtiles, int heads, const int* __restrict__ klen_ptr, int n_pad,
-                                           AttItem& it) {
+__device__ __forceinline__ bool att_decode(int w, int qtiles, int heads, const int* __restrict__ klen_ptr,
+                                           const int* __restrict__ row_start, int n_pad, AttItem& it) {
   const int qt = w % qtiles, sh = w / qtiles;
   it.head = sh % heads;
   it.sample = sh / heads;
   it.klen = klen_ptr ? min(__ldg(klen_ptr + it.sample), n_pad) : n_pad;
   it.q0 = qt * ATT_BM;
   it.nb = (it.klen + ATT_BN - 1) / ATT_BN;
+  // padded layout: sample s owns rows [s * n_pad, (s+1) * n_pad); packed layout: rows [row_start[s], row_start[s] + klen)
+  it.row_base = row_start ? __ldg(row_start + it.sample) : it.sample * n_pad;
+  it.q_limit = row_start ? it.klen : n_pad;  // query rows at or beyond this are not stored
   return it.q0 < it.klen;
 }
 
 __global__ void __launch_bounds__(ATT_THREADS, 2)
 attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __restrict__ out, int ldo,
-                 const int* __restrict__ klen_ptr, int n_pad, int inner, int heads, int qtiles, int total_items,
-                 float scale_log2) {
+                 const int* __restrict__ klen_ptr, const int* __restrict__ row_start, int n_pad, int inner, int heads,
+                 int qtiles, int total_items, float scale_log2) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + ATT_SMEM_BAR);
@@ -103,8 +106,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __res
       uint32_t phase = 0;
       for (int w = blockIdx.x; w < total_items; w += gridDim.x) {
         AttItem it;
-        if (!att_decode(w, qtiles, heads, klen_ptr, n_pad, it)) continue;
-        const int row_base = it.sample * n_pad;
+        if (!att_decode(w, qtiles, heads, klen_ptr, row_start, n_pad, it)) continue;
+        const int row_base = it.row_base;
         if (item > 0) mbar_wait(q_empty, (item - 1) & 1);  // every QK of the previous item has read Q
         mbar_expect_tx(q_full, ATT_TILE_BYTES);
         tma_load_2d(smem + ATT_SMEM_Q, &tmQKV, q_full, it.head * ATT_DH, row_base + it.q0);
@@ -156,7 +159,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __res
       int item = 0, blk = 0;
       for (int w = blockIdx.x; w < total_items; w += gridDim.x) {
         AttItem it;
-        if (!att_decode(w, qtiles, heads, klen_ptr, n_pad, it)) continue;
+        if (!att_decode(w, qtiles, heads, klen_ptr, row_start, n_pad, it)) continue;
         mbar_wait(q_full, item & 1);
         if (blk > 0) {  // the softmax warps hold the previous item's last S block in registers
           mbar_wait(s_free, (blk - 1) & 1);
@@ -190,7 +193,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __res
     int blk = 0;
     for (int w = blockIdx.x; w < total_items; w += gridDim.x) {
       AttItem it;
-      if (!att_decode(w, qtiles, heads, klen_ptr, n_pad, it)) continue;
+      if (!att_decode(w, qtiles, heads, klen_ptr, row_start, n_pad, it)) continue;
       float m_ref = -INFINITY;  // exponent reference (scaled log2 units); lags the true row maximum by at most 8
       float l = 0.f;
       for (int j = 0; j < it.nb; ++j) {
@@ -277,13 +280,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __res
       tc_fence_after();
       const int q = it.q0 + r;
       const float inv = 1.0f / l;
-      __nv_bfloat16* orow = out + (size_t)(it.sample * n_pad + q) * ldo + it.head * ATT_DH;
+      __nv_bfloat16* orow = out + (size_t)(it.row_base + q) * ldo + it.head * ATT_DH;
 #pragma unroll 1
       for (int c = 0; c < ATT_DH / 32; ++c) {
         uint32_t raw[32];
         tmem_ld_32x32(t_o + c * 32, raw);
         tmem_ld_wait();
-        if (q < n_pad) {
+        if (q < it.q_limit) {
 #pragma unroll
           for (int i = 0; i < 32; i += 8) {
             uint4 u;
@@ -313,20 +316,23 @@ int attention_configure() {
 }
 
 int attention(cudaStream_t st, const __nv_bfloat16* qkv, int ld_qkv, __nv_bfloat16* out, int ldo, const int* klen,
-              int samples, int n_pad, int heads, float scale) {
+              int samples, int n_pad, int heads, float scale, const int* row_start, int total_rows) {
   { int rc0 = ensure_configured(); if (rc0) return rc0; }
   F5E_REQUIRE(samples > 0 && n_pad > 0 && heads > 0, "attention: empty problem");
   F5E_REQUIRE(ldo % 8 == 0, "attention: ldo must be a multiple of 8");
+  F5E_REQUIRE(row_start == nullptr || (klen != nullptr && total_rows > 0), "attention: packed rows need klen and total_rows");
   const int inner = heads * ATT_DH;
   CUtensorMap tm;
-  int rc = make_tmap_2d(&tm, qkv, 2, (uint64_t)3 * inner, (uint64_t)samples * n_pad, (uint64_t)ld_qkv * 2, ATT_DH, 128);
+  int rc = make_tmap_2d(&tm, qkv, 2, (uint64_t)3 * inner, (uint64_t)(row_start ? total_rows : samples * n_pad), (uint64_t)ld_qkv * 2,
+                        ATT_DH, 128);
   if (rc) return rc;
   const int qtiles = (n_pad + ATT_BM - 1) / ATT_BM;
   const long long total = (long long)samples * heads * qtiles;
   F5E_REQUIRE(total < (1ll << 30), "attention: too many work items");
   const int grid = (int)(total < 2 * num_sms() ? total : 2 * num_sms());
   LaunchScope ls(st, PROF_ATTN, samples, n_pad, heads);
-  attention_kernel<<<grid, ATT_THREADS, ATT_SMEM_TOTAL, st>>>(tm, out, ldo, klen, n_pad, inner, heads, qtiles, (int)total,
+  attention_kernel<<<grid, ATT_THREADS, ATT_SMEM_TOTAL, st>>>(tm, out, ldo, klen, row_start, n_pad, inner, heads, qtiles,
+                                                              (int)total,
                                                               scale * 1.4426950408889634f);
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;

@@ -13,8 +13,9 @@ using namespace f5e;
 
 static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_dit_buffers* b, const float* mod,
                             int mod_stride, const int* klen, const float* rope_cos, const float* rope_sin, int samples,
-                            int n_pad) {
-  const int D = m->dim, rows = samples * n_pad, inner = m->heads * 64;
+                            int n_pad, const f5e_dit_packing* pack) {
+  const int D = m->dim, inner = m->heads * 64;
+  int rows = samples * n_pad;
   auto bf = [](const void* p) { return reinterpret_cast<const __nv_bfloat16*>(p); };
   auto bfm = [](void* p) { return reinterpret_cast<__nv_bfloat16*>(p); };
 
@@ -32,45 +33,60 @@ static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_d
     ep.out = b->x; ep.bias = m->b_conv2; ep.residual = bf(b->h0); ep.ldr = D;
     F5E_TRY(conv_pos(st, bf(b->h1), bf(m->w_conv2), samples, n_pad, D, m->conv_groups, ep));
   }
+  // Everything up to here runs on the padded [samples, n_pad] layout (the reference's unmasked convolution sees the
+  // padded frames).  From here on no op mixes frames except attention, which masks padded keys: with a packing the 22
+  // blocks run on the valid frames only (rows = sum of klen), padded query rows are never computed.
+  void* xs = b->x;  // residual stream
+  const int* row_info = nullptr;
+  const int* row_start = nullptr;
+  const int* row_len = klen;
+  if (pack) {
+    F5E_TRY(gather_rows(st, bf(b->x), bfm(b->h0), pack->row_map, pack->rows_packed, D));
+    xs = b->h0;
+    rows = pack->rows_packed;
+    row_info = pack->row_info;
+    row_start = pack->row_start;
+    row_len = nullptr;  // there are no padded rows left to zero
+  }
   for (int l = 0; l < m->depth; ++l) {
     const f5e_dit_layer& L = m->layers[l];
     const float* ml = mod + (size_t)l * 6 * D;
     const float *shift_msa = ml, *scale_msa = ml + D, *gate_msa = ml + 2 * D;
     const float *shift_mlp = ml + 3 * D, *scale_mlp = ml + 4 * D, *gate_mlp = ml + 5 * D;
     // adaLN-modulated LayerNorm (modules.py:310-315)
-    F5E_TRY(norm_mod(st, bf(b->x), bfm(b->xn), rows, D, scale_msa, shift_msa, mod_stride, n_pad, 1.0f, 1e-6f));
+    F5E_TRY(norm_mod(st, bf(xs), bfm(b->xn), rows, D, scale_msa, shift_msa, mod_stride, n_pad, 1.0f, 1e-6f, row_info));
     {  // fused q/k/v projection + RoPE (modules.py:442-480)
       EpiParams ep{};
-      ep.out = b->qkv; ep.ldo = 3 * inner; ep.bias = L.b_qkv; ep.n_pad = n_pad;
+      ep.out = b->qkv; ep.ldo = 3 * inner; ep.bias = L.b_qkv; ep.n_pad = n_pad; ep.row_info = row_info;
       if (m->rope_heads > 0) {
         ep.rope_cos = rope_cos; ep.rope_sin = rope_sin; ep.rope_inner = inner; ep.rope_heads = m->rope_heads;
       }
       F5E_TRY(gemm_bf16(st, bf(b->xn), D, bf(L.w_qkv), D, rows, 3 * inner, D, ep));
     }
-    F5E_TRY(attention(st, bf(b->qkv), 3 * inner, bfm(b->attn), inner, klen, samples, n_pad, m->heads, 0.125f));
+    F5E_TRY(attention(st, bf(b->qkv), 3 * inner, bfm(b->attn), inner, klen, samples, n_pad, m->heads, 0.125f, row_start, rows));
     {  // to_out + masked_fill + gate_msa * attn + residual (modules.py:494-501, :634)
       EpiParams ep{};
-      ep.out = b->x; ep.ldo = D; ep.bias = L.b_out; ep.n_pad = n_pad; ep.row_len = klen;
-      ep.gate = gate_msa; ep.gate_stride = mod_stride; ep.residual = bf(b->x); ep.ldr = D;
+      ep.out = xs; ep.ldo = D; ep.bias = L.b_out; ep.n_pad = n_pad; ep.row_info = row_info; ep.row_len = row_len;
+      ep.gate = gate_msa; ep.gate_stride = mod_stride; ep.residual = bf(xs); ep.ldr = D;
       F5E_TRY(gemm_bf16(st, bf(b->attn), inner, bf(L.w_out), inner, rows, D, inner, ep));
     }
-    F5E_TRY(norm_mod(st, bf(b->x), bfm(b->xn), rows, D, scale_mlp, shift_mlp, mod_stride, n_pad, 1.0f, 1e-6f));
+    F5E_TRY(norm_mod(st, bf(xs), bfm(b->xn), rows, D, scale_mlp, shift_mlp, mod_stride, n_pad, 1.0f, 1e-6f, row_info));
     {  // FeedForward (modules.py:342-353) with GELU(tanh) fused, then gate_mlp * ff + residual (:638)
       EpiParams ep{};
-      ep.out = b->ff; ep.ldo = m->ff_dim; ep.bias = L.b_ff1; ep.act = ACT_GELU_TANH; ep.n_pad = n_pad;
+      ep.out = b->ff; ep.ldo = m->ff_dim; ep.bias = L.b_ff1; ep.act = ACT_GELU_TANH; ep.n_pad = n_pad; ep.row_info = row_info;
       F5E_TRY(gemm_bf16(st, bf(b->xn), D, bf(L.w_ff1), D, rows, m->ff_dim, D, ep));
       EpiParams e2{};
-      e2.out = b->x; e2.ldo = D; e2.bias = L.b_ff2; e2.n_pad = n_pad;
-      e2.gate = gate_mlp; e2.gate_stride = mod_stride; e2.residual = bf(b->x); e2.ldr = D;
+      e2.out = xs; e2.ldo = D; e2.bias = L.b_ff2; e2.n_pad = n_pad; e2.row_info = row_info;
+      e2.gate = gate_mlp; e2.gate_stride = mod_stride; e2.residual = bf(xs); e2.ldr = D;
       F5E_TRY(gemm_bf16(st, bf(b->ff), m->ff_dim, bf(L.w_ff2), m->ff_dim, rows, D, m->ff_dim, e2));
     }
   }
   // AdaLayerNorm_Final (chunk order scale, shift: modules.py:331-336) + proj_out (dit.py:469-470)
   const float* mf = mod + (size_t)m->depth * 6 * D;
-  F5E_TRY(norm_mod(st, bf(b->x), bfm(b->xn), rows, D, mf, mf + D, mod_stride, n_pad, 1.0f, 1e-6f));
+  F5E_TRY(norm_mod(st, bf(xs), bfm(b->xn), rows, D, mf, mf + D, mod_stride, n_pad, 1.0f, 1e-6f, row_info));
   {
     EpiParams ep{};
-    ep.out = b->pred; ep.ldo = m->mel_dim; ep.out_f32 = 1; ep.bias = m->b_proj; ep.n_pad = n_pad;
+    ep.out = b->pred; ep.ldo = m->mel_dim; ep.out_f32 = 1; ep.bias = m->b_proj; ep.n_pad = n_pad; ep.row_info = row_info;
     F5E_TRY(gemm_bf16(st, bf(b->xn), D, bf(m->w_proj), D, rows, m->mel_dim, D, ep));
   }
   return 0;
@@ -85,20 +101,30 @@ static int check_model(const f5e_dit_model* m, const f5e_dit_buffers* b) {
   return 0;
 }
 
+static int check_pack(const f5e_dit_packing* p, const int* klen, int samples, int n_pad) {
+  if (!p) return 0;
+  F5E_REQUIRE(klen != nullptr, "dit: a row packing needs klen");
+  F5E_REQUIRE(p->row_map && p->row_info && p->row_start, "dit: null packing array");
+  F5E_REQUIRE(p->rows_packed > 0 && p->rows_packed <= samples * n_pad, "dit: rows_packed=%d out of range", p->rows_packed);
+  F5E_REQUIRE(n_pad <= 65535, "dit: packed rows need n_pad <= 65535");
+  return 0;
+}
+
 extern "C" {
 
 int f5e_dit_forward(const f5e_dit_model* model, const f5e_dit_buffers* buf, const float* mod, int32_t mod_stride,
                     const int32_t* klen, const float* rope_cos, const float* rope_sin, int32_t samples, int32_t n_pad,
-                    void* stream) {
+                    const f5e_dit_packing* pack, void* stream) {
   F5E_TRY(check_model(model, buf));
   F5E_REQUIRE(mod && samples > 0 && n_pad > 0, "f5e_dit_forward: bad arguments");
-  return dit_forward_impl((cudaStream_t)stream, model, buf, mod, mod_stride, klen, rope_cos, rope_sin, samples, n_pad);
+  F5E_TRY(check_pack(pack, klen, samples, n_pad));
+  return dit_forward_impl((cudaStream_t)stream, model, buf, mod, mod_stride, klen, rope_cos, rope_sin, samples, n_pad, pack);
 }
 
 int f5e_ode_solve(const f5e_dit_model* model, const f5e_dit_buffers* buf, float* y, const float* mod, int32_t mod_size,
                   const float* dt_host, int32_t steps, float cfg_strength, const int32_t* klen, const float* rope_cos,
                   const float* rope_sin, int32_t batch, int32_t n_pad, float* traj, int32_t round_bf16,
-                  int32_t use_graph, void* stream) {
+                  int32_t use_graph, const f5e_dit_packing* pack, void* stream) {
   F5E_TRY(check_model(model, buf));
   F5E_REQUIRE(y && mod && dt_host && steps > 0 && batch > 0 && n_pad > 0, "f5e_ode_solve: bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
@@ -106,18 +132,24 @@ int f5e_ode_solve(const f5e_dit_model* model, const f5e_dit_buffers* buf, float*
   const bool cfg = cfg_strength >= 1e-5f;
   const int samples = cfg ? 2 * batch : batch;
   const int rows_half = batch * n_pad;
+  F5E_TRY(check_pack(pack, klen, samples, n_pad));
+  F5E_REQUIRE(!pack || !cfg || pack->rows_packed % 2 == 0, "f5e_ode_solve: both CFG halves must pack to the same rows");
+  // packed: pred holds the valid frames back to back (cond half, then uncond half); row_map[0 .. rows_upd) maps the
+  // first half onto the padded state rows
+  const int rows_upd = pack ? (cfg ? pack->rows_packed / 2 : pack->rows_packed) : rows_half;
+  const int* upd_map = pack ? pack->row_map : nullptr;
   auto enqueue = [&](cudaStream_t es) -> int {
     for (int i = 0; i < steps; ++i) {
-      F5E_TRY(dit_forward_impl(es, model, buf, mod + (size_t)i * mod_size, 0, klen, rope_cos, rope_sin, samples, n_pad));
+      F5E_TRY(dit_forward_impl(es, model, buf, mod + (size_t)i * mod_size, 0, klen, rope_cos, rope_sin, samples, n_pad, pack));
       // when cfg is off only the first half of x_cat exists: cfg_euler's second x_cat write would be out of
       // bounds, so the state is written back by pack_cols instead
       float* tr = traj ? traj + (size_t)i * rows_half * model->mel_dim : nullptr;
       if (cfg) {
-        F5E_TRY(cfg_euler(es, buf->pred, model->mel_dim, y, (__nv_bfloat16*)buf->x_cat, model->in_dim, tr, rows_half,
-                          model->mel_dim, dt_host[i], cfg_strength, round_bf16));
+        F5E_TRY(cfg_euler(es, buf->pred, model->mel_dim, y, (__nv_bfloat16*)buf->x_cat, model->in_dim, tr, rows_upd,
+                          model->mel_dim, dt_host[i], cfg_strength, round_bf16, upd_map, rows_half));
       } else {
-        F5E_TRY(cfg_euler(es, buf->pred, model->mel_dim, y, nullptr, 0, tr, rows_half, model->mel_dim, dt_host[i], 0.0f,
-                          round_bf16));
+        F5E_TRY(cfg_euler(es, buf->pred, model->mel_dim, y, nullptr, 0, tr, rows_upd, model->mel_dim, dt_host[i], 0.0f,
+                          round_bf16, upd_map, rows_half));
         F5E_TRY(pack_cols(es, (__nv_bfloat16*)buf->x_cat, model->in_dim, 0, y, 1, model->mel_dim, rows_half,
                           model->mel_dim));
       }

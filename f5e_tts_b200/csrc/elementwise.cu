@@ -16,7 +16,7 @@ template <int CH>
 __global__ void __launch_bounds__(NM_THREADS)
 norm_mod_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, int M,
                 const float* __restrict__ mul, const float* __restrict__ add, int mod_stride, int n_pad,
-                float plus_one, float eps) {
+                float plus_one, float eps, const int* __restrict__ row_info) {
   constexpr int D = CH * 256;
   const int lane = threadIdx.x & 31;
   const int wstride = gridDim.x * (NM_THREADS / 32);
@@ -47,7 +47,7 @@ norm_mod_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__
 #pragma unroll
       for (int c = 0; c < CH; ++c) nxt[c] = xr[c * 32 + lane];
     }
-    const int sample = mod_stride ? row / n_pad : 0;
+    const int sample = mod_stride ? (row_info ? (__ldg(row_info + row) >> 16) : row / n_pad) : 0;
     if (sample != cur_sample) {
       cur_sample = sample;
       const float4* mp = reinterpret_cast<const float4*>(mul + (size_t)sample * mod_stride);
@@ -87,7 +87,7 @@ norm_mod_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__
 }
 
 int norm_mod(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int M, int D, const float* mul,
-             const float* add, int mod_stride, int n_pad, float plus_one, float eps) {
+             const float* add, int mod_stride, int n_pad, float plus_one, float eps, const int* row_info) {
   F5E_REQUIRE(M > 0, "norm_mod: M must be positive");
   F5E_REQUIRE(D % 256 == 0 && D >= 256 && D <= 2048, "norm_mod: D=%d must be a multiple of 256 in [256,2048]", D);
   if (n_pad <= 0) n_pad = M;
@@ -98,7 +98,7 @@ int norm_mod(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int M,
   LaunchScope ls(st, PROF_NORM, M, D, 0);
 #define F5E_NM(CH)                                                                                                    \
   case CH:                                                                                                            \
-    norm_mod_kernel<CH><<<grid, NM_THREADS, 0, st>>>(x, out, M, mul, add, mod_stride, n_pad, plus_one, eps);         \
+    norm_mod_kernel<CH><<<grid, NM_THREADS, 0, st>>>(x, out, M, mul, add, mod_stride, n_pad, plus_one, eps, row_info); \
     break;
   switch (D / 256) {
     F5E_NM(1) F5E_NM(2) F5E_NM(3) F5E_NM(4) F5E_NM(5) F5E_NM(6) F5E_NM(7) F5E_NM(8)
@@ -115,7 +115,7 @@ int norm_mod(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int M,
 __global__ void __launch_bounds__(256)
 cfg_euler_kernel(const float* __restrict__ pred, int ld_pred, float* __restrict__ y,
                  __nv_bfloat16* __restrict__ x_cat, int ld_cat, float* __restrict__ traj, int rows, int C,
-                 float dt, float cfg, int round_bf16) {
+                 float dt, float cfg, int round_bf16, const int* __restrict__ row_map, int rows_state) {
   const int quads = C >> 2;  // C % 4 == 0
   const long long total = (long long)rows * quads;
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
@@ -128,7 +128,9 @@ cfg_euler_kernel(const float* __restrict__ pred, int ld_pred, float* __restrict_
       v.x = pc.x + (pc.x - pu.x) * cfg; v.y = pc.y + (pc.y - pu.y) * cfg;
       v.z = pc.z + (pc.z - pu.z) * cfg; v.w = pc.w + (pc.w - pu.w) * cfg;
     }
-    float4* yp = reinterpret_cast<float4*>(y + (size_t)r * C + q * 4);
+    // packed mode: pred rows are the valid frames back to back, row_map gives their row in the padded state / concat buffer
+    const int sr = row_map ? __ldg(row_map + r) : r;
+    float4* yp = reinterpret_cast<float4*>(y + (size_t)sr * C + q * 4);
     float4 yy = *yp;
     yy.x += dt * v.x; yy.y += dt * v.y; yy.z += dt * v.z; yy.w += dt * v.w;
     if (round_bf16) {
@@ -136,19 +138,19 @@ cfg_euler_kernel(const float* __restrict__ pred, int ld_pred, float* __restrict_
       yy.z = __bfloat162float(__float2bfloat16(yy.z)); yy.w = __bfloat162float(__float2bfloat16(yy.w));
     }
     *yp = yy;
-    if (traj) *reinterpret_cast<float4*>(traj + (size_t)r * C + q * 4) = yy;
+    if (traj) *reinterpret_cast<float4*>(traj + (size_t)sr * C + q * 4) = yy;
     if (x_cat) {
       uint2 u;
       u.x = pack_bf16x2(yy.x, yy.y);
       u.y = pack_bf16x2(yy.z, yy.w);
-      *reinterpret_cast<uint2*>(x_cat + (size_t)r * ld_cat + q * 4) = u;
-      *reinterpret_cast<uint2*>(x_cat + ((size_t)rows + r) * ld_cat + q * 4) = u;
+      *reinterpret_cast<uint2*>(x_cat + (size_t)sr * ld_cat + q * 4) = u;
+      *reinterpret_cast<uint2*>(x_cat + ((size_t)rows_state + sr) * ld_cat + q * 4) = u;
     }
   }
 }
 
 int cfg_euler(cudaStream_t st, const float* pred, int ld_pred, float* y, __nv_bfloat16* x_cat, int ld_cat,
-              float* traj, int rows, int C, float dt, float cfg, int round_bf16) {
+              float* traj, int rows, int C, float dt, float cfg, int round_bf16, const int* row_map, int rows_state) {
   F5E_REQUIRE(rows > 0 && C > 0 && C % 4 == 0, "cfg_euler: need rows>0 and C%%4==0 (rows=%d C=%d)", rows, C);
   F5E_REQUIRE(ld_pred % 4 == 0 && (x_cat == nullptr || ld_cat % 4 == 0), "cfg_euler: leading dims must be multiples of 4");
   const long long total = (long long)rows * (C / 4);
@@ -156,7 +158,8 @@ int cfg_euler(cudaStream_t st, const float* pred, int ld_pred, float* y, __nv_bf
   const int cap = num_sms() * 8;
   if (grid > cap) grid = cap;
   LaunchScope ls(st, PROF_ELEM, rows, C, 0);
-  cfg_euler_kernel<<<grid, 256, 0, st>>>(pred, ld_pred, y, x_cat, ld_cat, traj, rows, C, dt, cfg, round_bf16);
+  cfg_euler_kernel<<<grid, 256, 0, st>>>(pred, ld_pred, y, x_cat, ld_cat, traj, rows, C, dt, cfg, round_bf16, row_map,
+                                         row_map ? rows_state : rows);
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -230,4 +230,30 @@ int unfold_frames(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, i
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// gather_rows: dst[r, :] = src[row_map[r], :]  (bf16, C % 8 == 0).  Drops the padded frames after the (unmasked, hence
+// padded-layout) ConvPositionEmbedding so that the 22 DiT blocks only see valid frames.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(const __nv_bfloat16* __restrict__ src, __nv_bfloat16* __restrict__ dst, const int* __restrict__ row_map,
+                   int rows, int C) {
+  const int vec = C / 8;
+  const long long total = (long long)rows * vec;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)(i / vec), c = (int)(i - (long long)r * vec);
+    reinterpret_cast<uint4*>(dst + (size_t)r * C)[c] = reinterpret_cast<const uint4*>(src + (size_t)__ldg(row_map + r) * C)[c];
+  }
+}
+
+int gather_rows(cudaStream_t st, const __nv_bfloat16* src, __nv_bfloat16* dst, const int* row_map, int rows, int C) {
+  F5E_REQUIRE(rows > 0 && C % 8 == 0, "gather_rows: bad shape");
+  const long long total = (long long)rows * (C / 8);
+  int grid = (int)((total + 255) / 256);
+  if (grid > num_sms() * 16) grid = num_sms() * 16;
+  LaunchScope ls(st, PROF_ELEM, rows, C, 10);
+  gather_rows_kernel<<<grid, 256, 0, st>>>(src, dst, row_map, rows, C);
+  F5E_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
 }  // namespace f5e

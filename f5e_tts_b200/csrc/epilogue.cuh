@@ -25,6 +25,8 @@ struct EpiParams {
   const float* rope_sin;
   int rope_inner;                  // heads*64 (columns [0, 2*rope_inner) hold Q then K)
   int rope_heads;                  // heads [0, rope_heads) of Q and of K get rotated
+  const int* row_info;             // [M] or null: (sample << 16 | frame) per row, for PACKED rows (valid frames of all
+                                   // samples back to back, no padding); replaces the row / n_pad arithmetic
   int res_f32;                     // residual is fp32 [M, ldr] instead of bf16
   int split3;                      // > 0: bf16 output written as the 3-term split [hi | hi | lo] at columns
                                    // c, c + split3, c + 2*split3 (A operand of a following fp32-accurate bf16x3 GEMM)

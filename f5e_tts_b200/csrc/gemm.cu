@@ -159,7 +159,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int row0 = m_blk * GEMM_BM + quarter * 32;
       const int row = row0 + lane;
       const int rowc = row < M ? row : M - 1;  // clamped row for table look-ups (stores are clipped by TMA)
-      const int sample = rowc / ep.n_pad, frame = rowc - sample * ep.n_pad;
+      int sample, frame;
+      if (ep.row_info) {
+        const int ri = __ldg(ep.row_info + rowc);
+        sample = ri >> 16;
+        frame = ri & 0xffff;
+      } else {
+        sample = rowc / ep.n_pad;
+        frame = rowc - sample * ep.n_pad;
+      }
       const bool row_masked = ep.row_len && frame >= __ldg(ep.row_len + sample);
       const int wcol0 = n_blk * BN + half * WCOLS;
       // RoPE angles of this row: the same 32 (cos, sin) pairs serve every head of the tile

@@ -39,6 +39,25 @@ class _Buffers(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("x_cat", "h0", "h1", "x", "xn", "qkv", "attn", "ff", "pred")]
 
 
+class _Packing(C.Structure):  # f5e_dit_packing
+    _fields_ = [("row_map", C.c_void_p), ("row_info", C.c_void_p), ("row_start", C.c_void_p), ("rows_packed", C.c_int32)]
+
+
+def make_packing(klen: torch.Tensor, n_pad: int):
+    """Row packing of `samples` sequences with klen[s] valid frames each (include/f5e_b200.h: f5e_dit_packing).
+    Integer index plumbing in torch; returns (struct, tensors to keep alive)."""
+    klen = klen.to(torch.int64)
+    S = klen.numel()
+    frame = torch.arange(n_pad, device=klen.device)
+    valid = frame[None, :] < klen[:, None]                                   # [S, n_pad]
+    sample = torch.arange(S, device=klen.device)[:, None].expand(S, n_pad)
+    row_map = (sample * n_pad + frame[None, :])[valid].to(torch.int32).contiguous()
+    row_info = ((sample << 16) | frame[None, :])[valid].to(torch.int32).contiguous()
+    row_start = (torch.cumsum(klen, 0) - klen).to(torch.int32).contiguous()
+    pk = _Packing(row_map.data_ptr(), row_info.data_ptr(), row_start.data_ptr(), int(row_map.numel()))
+    return pk, (row_map, row_info, row_start)
+
+
 # ---- parameter containers with the reference's state-dict names ---------------------------------------
 def _seq(mods: dict) -> nn.ModuleDict:
     """nn.Sequential-compatible naming with gaps ("0", "2", ...)."""
@@ -354,7 +373,7 @@ class DiT(nn.Module):
             klen = mask.sum(-1).to(torch.int32).to(dev)
         cos, sin = self._rope(N)
         check(_lib.load().f5e_dit_forward(C.byref(P.model), C.byref(buf), ptr(mod), P.mod_size, ptr(klen), ptr(cos), ptr(sin),
-                                          B, N, stream_ptr()), "f5e_dit_forward")
+                                          B, N, None, stream_ptr()), "f5e_dit_forward")
         return tens["pred"].view(B, N, md).to(x.dtype)
 
 
@@ -403,6 +422,7 @@ class CFM(nn.Module):
         self.use_cuda_graph = False       # capture the whole Euler loop in one CUDA graph launch
         self.store_trajectory = True      # False: return only [y0, y1] instead of steps+1 states
         self.emulate_lowp_state = False   # True: round the ODE state to bf16 every step like a bf16 reference run
+        self.pack_valid_rows = True       # batch > 1: run the DiT blocks on valid frames only (padding costs no FLOPs)
 
     @property
     def device(self):
@@ -489,6 +509,8 @@ class CFM(nn.Module):
                 ops.pack_cols(xh, 2 * md + td, dit._ppg_embed(ppg, N, drop, B).view(rows, td))
         mod = dit._modulation(t[:-1])
         klen = duration.to(torch.int32).repeat(2 if use_cfg else 1).contiguous() if batch > 1 else None
+        # batch > 1: the DiT blocks run on the valid frames only (no FLOPs on padding)
+        pack, pack_keep = (make_packing(klen, N) if (klen is not None and self.pack_valid_rows) else (None, None))
         cos, sin = dit._rope(N)
         y = y0.float().contiguous()
         traj = torch.empty(steps, B, N, md, device=y.device, dtype=torch.float32) if self.store_trajectory else None
@@ -496,7 +518,8 @@ class CFM(nn.Module):
         check(_lib.load().f5e_ode_solve(C.byref(P.model), C.byref(buf), ptr(y), ptr(mod), P.mod_size, dt_arr, steps,
                                         C.c_float(cfg_strength), ptr(klen), ptr(cos), ptr(sin), B, N, ptr(traj),
                                         int(self.emulate_lowp_state and dtype != torch.float32), int(self.use_cuda_graph),
-                                        stream_ptr()), "f5e_ode_solve")
+                                        None if pack is None else C.byref(pack), stream_ptr()), "f5e_ode_solve")
+        del pack_keep
         dit.clear_cache()
         sampled = y.to(dtype)
         if traj is not None:

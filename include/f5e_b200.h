@@ -62,6 +62,7 @@ typedef struct f5e_epilogue {
   int32_t out_split3;      /* > 0: bf16 output as the 3-term split [hi | hi | lo] at columns c, c+out_split3,
                               c+2*out_split3: the A operand of a following fp32-accurate "bf16x3" GEMM whose weight
                               is packed [W_hi | W_lo | W_hi] along K (used by the fp32 Vocos / VQ paths) */
+  const int32_t* row_info; /* [M] sample << 16 | frame for packed rows (see f5e_dit_packing), or NULL */
 } f5e_epilogue;
 
 /* C[M,N] = epilogue(A[M,K] @ W[N,K]^T); bf16 operands, tcgen05 / TMEM fp32 accumulation.
@@ -155,6 +156,18 @@ typedef struct f5e_dit_buffers {   /* caller-allocated scratch, rows = samples *
   float* pred;    /* fp32 [rows, mel_dim]                                                          */
 } f5e_dit_buffers;
 
+/* Optional row packing: after the (unmasked, hence padded-layout) ConvPositionEmbedding nothing but the key-masked
+ * attention mixes frames, so the DiT blocks can run on the VALID frames only.  rows_packed = sum of klen;
+ * row_map[r] = row of packed row r in the padded [samples * n_pad] layout, row_info[r] = sample << 16 | frame,
+ * row_start[s] = first packed row of sample s.  With a packing, buf->pred holds [rows_packed, mel_dim] (packed), and in
+ * f5e_ode_solve the first half of row_map addresses the state rows.  NULL = padded layout everywhere. */
+typedef struct f5e_dit_packing {
+  const int32_t* row_map;
+  const int32_t* row_info;
+  const int32_t* row_start;
+  int32_t rows_packed;
+} f5e_dit_packing;
+
 /* One flow evaluation over `samples` sequences of n_pad frames (DiT.sample after the embeddings:
  * backbones/dit.py:450-470).  mod: fp32 modulation vectors for this time step, laid out
  * [depth][shift_msa|scale_msa|gate_msa|shift_mlp|scale_mlp|gate_mlp][dim] then [scale|shift][dim] of norm_out
@@ -164,7 +177,7 @@ typedef struct f5e_dit_buffers {   /* caller-allocated scratch, rows = samples *
  * rope_cos/sin: fp32 [n_pad, 32].  Result in buf->pred. */
 int f5e_dit_forward(const f5e_dit_model* model, const f5e_dit_buffers* buf, const float* mod, int32_t mod_stride,
                     const int32_t* klen, const float* rope_cos, const float* rope_sin, int32_t samples, int32_t n_pad,
-                    void* stream);
+                    const f5e_dit_packing* pack, void* stream);
 
 /* The whole sampler loop (model/cfm.py:431-447, 471 with torchdiffeq fixed-grid Euler): for i in [0, steps):
  *   pred = DiT(x_cat; mod[i]) on the doubled batch (cond half then uncond half; a single half when
@@ -175,7 +188,7 @@ int f5e_dit_forward(const f5e_dit_model* model, const f5e_dit_buffers* buf, cons
 int f5e_ode_solve(const f5e_dit_model* model, const f5e_dit_buffers* buf, float* y, const float* mod, int32_t mod_size,
                   const float* dt_host, int32_t steps, float cfg_strength, const int32_t* klen, const float* rope_cos,
                   const float* rope_sin, int32_t batch, int32_t n_pad, float* traj, int32_t round_bf16,
-                  int32_t use_graph, void* stream);
+                  int32_t use_graph, const f5e_dit_packing* pack, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------
  * fp32 front end / back end / codebook
