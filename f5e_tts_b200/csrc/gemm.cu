@@ -23,14 +23,21 @@ constexpr int GEMM_BK = 64;
 constexpr int GEMM_EPI_WARPS = 8;
 constexpr int GEMM_THREADS = 64 + 32 * GEMM_EPI_WARPS;
 constexpr int GEMM_STAGING_BYTES = 4096;  // 32 rows x 128 bytes per epilogue warp
+#ifndef GEMM_PAIR
+#define GEMM_PAIR 1                       // 0: never use CTA pairs (A/B switch for measurements)
+#endif
 
-template <int BN, int STAGES>
+// CG = CTAs per tile: 1, or 2 = a CTA PAIR (cta_group::2) computing a 256 x BN tile; every CTA then stages only half of
+// the W tile, which halves the shared-memory operand traffic per MMA: a single-CTA 128x256 tile needs 192 B/clk of
+// operand reads (A 4 KB + B 8 KB per 64-cycle UMMA), above the 128 B/clk an SM's shared memory delivers.
+template <int BN, int STAGES, int CG = 1>
 struct GemmSmem {
   static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
-  static constexpr int B_BYTES = BN * GEMM_BK * 2;
+  static constexpr int B_BYTES = (BN / CG) * GEMM_BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGING_OFFSET = STAGES * STAGE_BYTES;
-  static constexpr int BAR_OFFSET = STAGING_OFFSET + GEMM_EPI_WARPS * GEMM_STAGING_BYTES;
+  static constexpr int NBUF = CG;  // staging blocks per epilogue warp: the pair kernel has room to double-buffer them
+  static constexpr int BAR_OFFSET = STAGING_OFFSET + GEMM_EPI_WARPS * NBUF * GEMM_STAGING_BYTES;
   static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;  // barriers + alignment slack
 };
 
@@ -53,8 +60,9 @@ __device__ __forceinline__ void staging_flush(const CUtensorMap* tmC, const uint
   }
 }
 // The staging block may be rewritten once the previous bulk store has finished READING it.
+template <int NBUF>
 __device__ __forceinline__ void staging_acquire(int lane) {
-  if (lane == 0) tma_store_wait_read<0>();
+  if (lane == 0) tma_store_wait_read<NBUF - 1>();  // the block flushed NBUF flushes ago has been read out
   __syncwarp();
 }
 // 16-byte slot j (0..7) of row r inside a 128B-swizzled 32-row block
@@ -62,11 +70,11 @@ __device__ __forceinline__ uint4* staging_slot(uint8_t* stage, int r, int j) {
   return reinterpret_cast<uint4*>(stage + r * 128 + ((j ^ (r & 7)) << 4));
 }
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, int CG>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, int M, int N, int K, EpiParams ep, int accumulate) {
-  using S = GemmSmem<BN, STAGES>;
+  using S = GemmSmem<BN, STAGES, CG>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::BAR_OFFSET);
@@ -77,11 +85,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int m_blocks = (M + GEMM_BM - 1) / GEMM_BM;
+  constexpr int TILE_M = GEMM_BM * CG;
+  const int m_blocks = (M + TILE_M - 1) / TILE_M;
   const int n_blocks = (N + BN - 1) / BN;
   const int num_tiles = m_blocks * n_blocks;
   const int nkb = (K + GEMM_BK - 1) / GEMM_BK;
   constexpr uint32_t TMEM_COLS = 2 * BN;  // 256 or 512: power of two
+  const int rank = CG == 2 ? (int)cluster_ctarank() : 0;   // 0 = leader: issues the MMAs of the pair
+  const int tile0 = blockIdx.x / CG, tile_stride = gridDim.x / CG;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -93,13 +104,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull_bar[i], 1);
-      mbar_init(&tempty_bar[i], GEMM_EPI_WARPS);
+      mbar_init(&tempty_bar[i], GEMM_EPI_WARPS * CG);  // the leader's barrier collects the epilogue warps of both CTAs
     }
     mbar_fence_init();
   }
-  if (warp == 1) tmem_alloc(tmem_holder, TMEM_COLS);
+  if (warp == 1) {
+    if (CG == 2) tmem_alloc_2cta(tmem_holder, TMEM_COLS);
+    else tmem_alloc(tmem_holder, TMEM_COLS);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all();  // the peer's barriers are initialised before anything signals them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
 
@@ -107,27 +122,33 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
         const int m_blk = tile / n_blocks, n_blk = tile - m_blk * n_blocks;
         for (int kb = 0; kb < nkb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * S::STAGE_BYTES;
           uint8_t* sb = sa + S::A_BYTES;
-          mbar_expect_tx(&full_bar[stage], S::STAGE_BYTES);
-          tma_load_2d(sa, &tmA, &full_bar[stage], kb * GEMM_BK, m_blk * GEMM_BM);
-          tma_load_2d(sb, &tmB, &full_bar[stage], kb * GEMM_BK, n_blk * BN);
+          if (CG == 2) {  // both CTAs' bytes complete on the leader's barrier
+            if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * S::STAGE_BYTES);
+            tma_load_2d_2cta(sa, &tmA, &full_bar[stage], kb * GEMM_BK, m_blk * TILE_M + rank * GEMM_BM);
+            tma_load_2d_2cta(sb, &tmB, &full_bar[stage], kb * GEMM_BK, n_blk * BN + rank * (BN / 2));
+          } else {
+            mbar_expect_tx(&full_bar[stage], S::STAGE_BYTES);
+            tma_load_2d(sa, &tmA, &full_bar[stage], kb * GEMM_BK, m_blk * GEMM_BM);
+            tma_load_2d(sb, &tmB, &full_bar[stage], kb * GEMM_BK, n_blk * BN);
+          }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc(kFmtBF16, GEMM_BM, BN, 0, 0);
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = umma_idesc(kFmtBF16, TILE_M, BN, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
@@ -138,12 +159,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const uint64_t adesc = umma_desc_kmajor_sw128(sa);
           const uint64_t bdesc = umma_desc_kmajor_sw128(sa + S::A_BYTES);
 #pragma unroll
-          for (int k = 0; k < GEMM_BK / 16; ++k)  // +32 bytes (2 x 16B units) per UMMA_K inside the swizzle atom
-            umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
-          umma_commit(&empty_bar[stage]);
+          for (int k = 0; k < GEMM_BK / 16; ++k) {  // +32 bytes (2 x 16B units) per UMMA_K inside the swizzle atom
+            if (CG == 2) umma_f16_ss_2cta(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+            else umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+          }
+          if (CG == 2) umma_commit_2cta(&empty_bar[stage], 3);  // frees the slot in both CTAs
+          else umma_commit(&empty_bar[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull_bar[acc]);
+        if (CG == 2) umma_commit_2cta(&tfull_bar[acc], 3);
+        else umma_commit(&tfull_bar[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -151,12 +176,19 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int quarter = warp & 3;            // TMEM lane quarter this warp may read
     const int half = (warp - 2) >> 2;        // which half of the tile's columns
     constexpr int WCOLS = BN / 2;            // columns per epilogue warp
-    uint8_t* stage_buf = smem + S::STAGING_OFFSET + (warp - 2) * GEMM_STAGING_BYTES;
+    uint8_t* const stage_base = smem + S::STAGING_OFFSET + (warp - 2) * S::NBUF * GEMM_STAGING_BYTES;
+    uint8_t* stage_buf = stage_base;
+    int sbuf = 0;
+    auto acquire = [&]() {  // next staging block of this warp (round robin), free once its last bulk store has read it
+      stage_buf = stage_base + sbuf * GEMM_STAGING_BYTES;
+      sbuf = (sbuf + 1) % S::NBUF;
+      staging_acquire<S::NBUF>(lane);
+    };
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
       const int m_blk = tile / n_blocks, n_blk = tile - m_blk * n_blocks;
-      const int row0 = m_blk * GEMM_BM + quarter * 32;
+      const int row0 = m_blk * TILE_M + rank * GEMM_BM + quarter * 32;
       const int row = row0 + lane;
       const int rowc = row < M ? row : M - 1;  // clamped row for table look-ups (stores are clipped by TMA)
       int sample, frame;
@@ -226,7 +258,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         switch (ep.act) {
           case ACT_GELU_TANH:
 #pragma unroll
-            for (int i = 0; i < 64; ++i) v[i] = gelu_tanh_fast(v[i]);
+            for (int i = 0; i < 64; i += 2) {
+              const float2 g = gelu_tanh_fast2(make_float2(v[i], v[i + 1]));
+              v[i] = g.x;
+              v[i + 1] = g.y;
+            }
             break;
           case ACT_GELU_ERF:
 #pragma unroll
@@ -282,7 +318,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
           for (int h = 0; h < 2; ++h) {  // 32 fp32 columns = 128 bytes per row per block
             if (col0 + 32 * h >= N) break;
-            staging_acquire(lane);
+            acquire();
 #pragma unroll
             for (int j = 0; j < 8; ++j)
               *staging_slot(stage_buf, lane, j) =
@@ -292,7 +328,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         } else if (ep.split3 > 0) {
           uint4 lo[8];
-          staging_acquire(lane);
+          acquire();
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             uint4 hi;
@@ -314,12 +350,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tma_store_2d(&tmC, stage_buf, col0 + ep.split3, row0);
             tma_store_commit();
           }
-          staging_acquire(lane);
+          acquire();
 #pragma unroll
           for (int j = 0; j < 8; ++j) *staging_slot(stage_buf, lane, j) = lo[j];
           staging_flush(&tmC, stage_buf, col0 + 2 * ep.split3, row0, false, lane);
         } else {
-          staging_acquire(lane);
+          acquire();
 #pragma unroll
           for (int j = 0; j < 8; ++j)
             *staging_slot(stage_buf, lane, j) =
@@ -330,37 +366,56 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (lane == 0) {
+        if (CG == 2) mbar_arrive_cluster(&tempty_bar[acc], 0);
+        else mbar_arrive(&tempty_bar[acc]);
+      }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
     if (lane == 0) tma_store_wait<0>();  // every bulk store has completed before the CTA's shared memory goes away
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all();  // no CTA leaves while its peer may still signal its barriers / read its smem
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    if (CG == 2) tmem_dealloc_2cta(tmem_base, TMEM_COLS);
+    else tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, int CG>
 static int launch_gemm(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, int M, int N,
                        int K, const EpiParams& ep, int accumulate) {
-  using S = GemmSmem<BN, STAGES>;
-  const int tiles = ((M + GEMM_BM - 1) / GEMM_BM) * ((N + BN - 1) / BN);
-  const int grid = tiles < num_sms() ? tiles : num_sms();
+  using S = GemmSmem<BN, STAGES, CG>;
+  const int tiles = ((M + GEMM_BM * CG - 1) / (GEMM_BM * CG)) * ((N + BN - 1) / BN);
+  const int slots = num_sms() / CG;  // CTAs (CG = 1) or CTA pairs (CG = 2) that can be resident
+  const int grid = (tiles < slots ? tiles : slots) * CG;
   LaunchScope ls(st, PROF_GEMM, M, N, K);
-  gemm_bf16_kernel<BN, STAGES><<<grid, GEMM_THREADS, S::TOTAL, st>>>(tmA, tmB, tmC, M, N, K, ep, accumulate);
-  F5E_CUDA_CHECK(cudaGetLastError());
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = S::TOTAL;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  F5E_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<BN, STAGES, CG>, tmA, tmB, tmC, M, N, K, ep, accumulate));
   return 0;
 }
 
 int gemm_configure() {
-  F5E_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      GemmSmem<256, 4>::TOTAL));
-  F5E_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<128, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      GemmSmem<128, 6>::TOTAL));
+  F5E_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<256, 4, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      GemmSmem<256, 4, 1>::TOTAL));
+  F5E_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<256, 5, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      GemmSmem<256, 5, 2>::TOTAL));
+  F5E_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<128, 6, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      GemmSmem<128, 6, 1>::TOTAL));
   return 0;
 }
 
@@ -378,15 +433,18 @@ int gemm_bf16(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloa
   CUtensorMap tmA, tmB, tmC;
   int rc = make_tmap_2d(&tmA, A, 2, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, GEMM_BK, GEMM_BM);
   if (rc) return rc;
-  rc = make_tmap_2d(&tmB, W, 2, (uint64_t)K, (uint64_t)N, (uint64_t)ldw * 2, GEMM_BK, wide ? 256 : 128);
+  // CTA pairs when there are enough 256-row tiles to fill the 74 pairs; each CTA then loads a 128-row half of the W tile
+  const bool pair = wide && GEMM_PAIR && ((M + 255) / 256) * ((N + 255) / 256) >= num_sms() / 2;
+  rc = make_tmap_2d(&tmB, W, 2, (uint64_t)K, (uint64_t)N, (uint64_t)ldw * 2, GEMM_BK, (wide && !pair) ? 256 : 128);
   if (rc) return rc;
   if (ep.out_f32)
     rc = make_tmap_2d(&tmC, ep.out, 4, (uint64_t)N, (uint64_t)M, (uint64_t)ep.ldo * 4, 32, 32);
   else
     rc = make_tmap_2d(&tmC, ep.out, 2, (uint64_t)(ep.split3 > 0 ? 3 * ep.split3 : N), (uint64_t)M, (uint64_t)ep.ldo * 2, 64, 32);
   if (rc) return rc;
-  if (wide) return launch_gemm<256, 4>(st, tmA, tmB, tmC, M, N, K, ep, alias ? 1 : 0);
-  return launch_gemm<128, 6>(st, tmA, tmB, tmC, M, N, K, ep, alias ? 1 : 0);
+  if (pair) return launch_gemm<256, 5, 2>(st, tmA, tmB, tmC, M, N, K, ep, alias ? 1 : 0);
+  if (wide) return launch_gemm<256, 4, 1>(st, tmA, tmB, tmC, M, N, K, ep, alias ? 1 : 0);
+  return launch_gemm<128, 6, 1>(st, tmA, tmB, tmC, M, N, K, ep, alias ? 1 : 0);
 }
 
 }  // namespace f5e

@@ -62,10 +62,13 @@ def main():
             b = torch.randn(n, device=dev)
             f32 = n % 8 != 0
             o = torch.empty(M, n, device=dev, dtype=torch.float32 if f32 else torch.bfloat16)
-            res = torch.randn(M, n, device=dev).bfloat16() if tag in ("out", "ff2") else None
+            res = o if tag in ("out", "ff2") else None  # in place (x += gate * branch), as in the DiT block
             gate = torch.randn(n, device=dev) if res is not None else None
             ms = timeit(lambda: ops.gemm(x, w, bias=b, act=act, out=o, residual=res, gate=gate, n_pad=N))
             rec(f"gemm_{tag}", ms, flops=2.0 * M * n * k, M=M, N=n, K=k)
+            if tag in ("qkv", "ff1"):
+                ms = timeit(lambda: ops.gemm(x, w, out=o, n_pad=N))
+                rec(f"gemm_{tag}_plain", ms, flops=2.0 * M * n * k, M=M, N=n, K=k)
             ms = timeit(lambda: torch.matmul(x, w.t()))
             rec(f"cublas_{tag}", ms, flops=2.0 * M * n * k, M=M, N=n, K=k)
     if not a.only or "attn" in a.only:
