@@ -24,9 +24,9 @@ class Epilogue(C.Structure):
         ("gate", C.c_void_p), ("gate_stride", C.c_int32),
         ("residual", C.c_void_p), ("ldr", C.c_int32),
         ("row_len", C.c_void_p), ("n_pad", C.c_int32),
-        ("rope_cos", C.c_void_p), ("rope_sin", C.c_void_p),
         ("rope_inner", C.c_int32), ("rope_heads", C.c_int32),
         ("residual_f32", C.c_int32), ("out_split3", C.c_int32), ("row_info", C.c_void_p),
+        ("rope_inv_freq", C.c_void_p),
     ]
 
 

@@ -11,9 +11,9 @@ static EpiParams to_epi(const f5e_epilogue* e, int M) {
   p.gate = e->gate; p.gate_stride = e->gate_stride;
   p.residual = reinterpret_cast<const __nv_bfloat16*>(e->residual); p.ldr = e->ldr;
   p.row_len = e->row_len; p.n_pad = e->n_pad > 0 ? e->n_pad : M;
-  p.rope_cos = e->rope_cos; p.rope_sin = e->rope_sin;
   p.rope_inner = e->rope_inner; p.rope_heads = e->rope_heads;
   p.res_f32 = e->residual_f32; p.split3 = e->out_split3; p.row_info = e->row_info;
+  p.rope_inv_freq = e->rope_inv_freq;
   return p;
 }
 

@@ -12,8 +12,7 @@ using namespace f5e;
   } while (0)
 
 static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_dit_buffers* b, const float* mod,
-                            int mod_stride, const int* klen, const float* rope_cos, const float* rope_sin, int samples,
-                            int n_pad, const f5e_dit_packing* pack) {
+                            int mod_stride, const int* klen, int samples, int n_pad, const f5e_dit_packing* pack) {
   const int D = m->dim, inner = m->heads * 64;
   int rows = samples * n_pad;
   auto bf = [](const void* p) { return reinterpret_cast<const __nv_bfloat16*>(p); };
@@ -59,7 +58,7 @@ static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_d
       EpiParams ep{};
       ep.out = b->qkv; ep.ldo = 3 * inner; ep.bias = L.b_qkv; ep.n_pad = n_pad; ep.row_info = row_info;
       if (m->rope_heads > 0) {
-        ep.rope_cos = rope_cos; ep.rope_sin = rope_sin; ep.rope_inner = inner; ep.rope_heads = m->rope_heads;
+        ep.rope_inv_freq = m->rope_inv_freq; ep.rope_inner = inner; ep.rope_heads = m->rope_heads;
       }
       F5E_TRY(gemm_bf16(st, bf(b->xn), D, bf(L.w_qkv), D, rows, 3 * inner, D, ep));
     }
@@ -97,6 +96,7 @@ static int check_model(const f5e_dit_model* m, const f5e_dit_buffers* b) {
   F5E_REQUIRE(m->dim % 256 == 0, "dit: dim %d must be a multiple of 256", m->dim);
   F5E_REQUIRE(m->in_dim % 8 == 0 && m->mel_dim % 4 == 0, "dit: in_dim %d must be a multiple of 8, mel_dim %d of 4",
               m->in_dim, m->mel_dim);
+  F5E_REQUIRE(m->rope_heads == 0 || m->rope_inv_freq, "dit: rope_inv_freq is null");
   F5E_REQUIRE(b->x_cat && b->h0 && b->h1 && b->x && b->xn && b->qkv && b->attn && b->ff && b->pred, "dit: null scratch buffer");
   return 0;
 }
@@ -113,18 +113,17 @@ static int check_pack(const f5e_dit_packing* p, const int* klen, int samples, in
 extern "C" {
 
 int f5e_dit_forward(const f5e_dit_model* model, const f5e_dit_buffers* buf, const float* mod, int32_t mod_stride,
-                    const int32_t* klen, const float* rope_cos, const float* rope_sin, int32_t samples, int32_t n_pad,
-                    const f5e_dit_packing* pack, void* stream) {
+                    const int32_t* klen, int32_t samples, int32_t n_pad, const f5e_dit_packing* pack, void* stream) {
   F5E_TRY(check_model(model, buf));
   F5E_REQUIRE(mod && samples > 0 && n_pad > 0, "f5e_dit_forward: bad arguments");
   F5E_TRY(check_pack(pack, klen, samples, n_pad));
-  return dit_forward_impl((cudaStream_t)stream, model, buf, mod, mod_stride, klen, rope_cos, rope_sin, samples, n_pad, pack);
+  return dit_forward_impl((cudaStream_t)stream, model, buf, mod, mod_stride, klen, samples, n_pad, pack);
 }
 
 int f5e_ode_solve(const f5e_dit_model* model, const f5e_dit_buffers* buf, float* y, const float* mod, int32_t mod_size,
-                  const float* dt_host, int32_t steps, float cfg_strength, const int32_t* klen, const float* rope_cos,
-                  const float* rope_sin, int32_t batch, int32_t n_pad, float* traj, int32_t round_bf16,
-                  int32_t use_graph, const f5e_dit_packing* pack, void* stream) {
+                  const float* dt_host, int32_t steps, float cfg_strength, const int32_t* klen, int32_t batch,
+                  int32_t n_pad, float* traj, int32_t round_bf16, int32_t use_graph, const f5e_dit_packing* pack,
+                  void* stream) {
   F5E_TRY(check_model(model, buf));
   F5E_REQUIRE(y && mod && dt_host && steps > 0 && batch > 0 && n_pad > 0, "f5e_ode_solve: bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
@@ -140,7 +139,7 @@ int f5e_ode_solve(const f5e_dit_model* model, const f5e_dit_buffers* buf, float*
   const int* upd_map = pack ? pack->row_map : nullptr;
   auto enqueue = [&](cudaStream_t es) -> int {
     for (int i = 0; i < steps; ++i) {
-      F5E_TRY(dit_forward_impl(es, model, buf, mod + (size_t)i * mod_size, 0, klen, rope_cos, rope_sin, samples, n_pad, pack));
+      F5E_TRY(dit_forward_impl(es, model, buf, mod + (size_t)i * mod_size, 0, klen, samples, n_pad, pack));
       // when cfg is off only the first half of x_cat exists: cfg_euler's second x_cat write would be out of
       // bounds, so the state is written back by pack_cols instead
       float* tr = traj ? traj + (size_t)i * rows_half * model->mel_dim : nullptr;

@@ -21,10 +21,10 @@ struct EpiParams {
   int ldr;
   const int* row_len;              // [M / n_pad] or null : rows with (row % n_pad) >= row_len[row / n_pad] -> 0
   int n_pad;                       // frames per sample (row -> (sample, frame)); needed by row_len / rope
-  const float* rope_cos;           // [n_pad, 32] or null (interleaved-pair RoPE, dim_head 64)
-  const float* rope_sin;
   int rope_inner;                  // heads*64 (columns [0, 2*rope_inner) hold Q then K)
   int rope_heads;                  // heads [0, rope_heads) of Q and of K get rotated
+  const float* rope_inv_freq;      // [32] or null: interleaved-pair RoPE (dim_head 64) on Q and K; the angles
+                                   // frame * inv_freq[j] are evaluated in the epilogue (Cody-Waite reduction + sin/cos.approx)
   const int* row_info;             // [M] or null: (sample << 16 | frame) per row, for PACKED rows (valid frames of all
                                    // samples back to back, no padding); replaces the row / n_pad arithmetic
   int res_f32;                     // residual is fp32 [M, ldr] instead of bf16
@@ -49,32 +49,6 @@ __device__ __forceinline__ void epilogue_chunk(float (&v)[32], int row, int col0
 #pragma unroll
       for (int i = 0; i < 32; ++i)
         if (col0 + i < N) v[i] += __ldg(p.bias + col0 + i);
-    }
-  }
-
-  if (p.rope_cos) {
-    const int inner = p.rope_inner;
-    if (col0 < 2 * inner) {
-      const int c = col0 % inner;
-      const int head = c >> 6;
-      if (head < p.rope_heads) {
-        const int n = row % p.n_pad;
-        const int j0 = (c & 63) >> 1;  // first frequency index of this chunk (0 or 16)
-        const float4* cp = reinterpret_cast<const float4*>(p.rope_cos + (size_t)n * 32 + j0);
-        const float4* sp = reinterpret_cast<const float4*>(p.rope_sin + (size_t)n * 32 + j0);
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          float4 c4 = __ldg(cp + q), s4 = __ldg(sp + q);
-          float cs[4] = {c4.x, c4.y, c4.z, c4.w}, sn[4] = {s4.x, s4.y, s4.z, s4.w};
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const int i = (q * 4 + k) * 2;
-            const float a = v[i], b = v[i + 1];
-            v[i] = a * cs[k] - b * sn[k];
-            v[i + 1] = b * cs[k] + a * sn[k];
-          }
-        }
-      }
     }
   }
 

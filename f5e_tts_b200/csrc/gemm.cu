@@ -202,19 +202,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       const bool row_masked = ep.row_len && frame >= __ldg(ep.row_len + sample);
       const int wcol0 = n_blk * BN + half * WCOLS;
-      // RoPE angles of this row: the same 32 (cos, sin) pairs serve every head of the tile
-      float rc[32], rs[32];
-      const bool tile_rope = ep.rope_cos && wcol0 < 2 * ep.rope_inner && wcol0 < N;
-      if (tile_rope) {
-        const float4* cp = reinterpret_cast<const float4*>(ep.rope_cos + (size_t)frame * 32);
-        const float4* sp = reinterpret_cast<const float4*>(ep.rope_sin + (size_t)frame * 32);
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const float4 c4 = __ldg(cp + q), s4 = __ldg(sp + q);
-          rc[4 * q] = c4.x; rc[4 * q + 1] = c4.y; rc[4 * q + 2] = c4.z; rc[4 * q + 3] = c4.w;
-          rs[4 * q] = s4.x; rs[4 * q + 1] = s4.y; rs[4 * q + 2] = s4.z; rs[4 * q + 3] = s4.w;
-        }
-      }
+      // RoPE: angle(frame, j) = frame * inv_freq[j], shared by the interleaved pair (2j, 2j+1) of every head.  The angles
+      // are evaluated per 64-column chunk (= one head): no table traffic and nothing live across chunks.  (Reading
+      // per-row cos/sin tables cost 28 us per QKV launch: 512 scattered LSU wavefronts per warp and 64 live registers.)
+      const bool tile_rope = ep.rope_inv_freq && wcol0 < 2 * ep.rope_inner && wcol0 < N;
+      const float frame_f = (float)frame;
       const float* gate = ep.gate ? ep.gate + (ep.gate_stride ? (size_t)sample * ep.gate_stride : 0) : nullptr;
 
       mbar_wait(&tfull_bar[acc], acc_phase);
@@ -248,11 +240,22 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         }
         if (tile_rope && col0 < 2 * ep.rope_inner && ((col0 % ep.rope_inner) >> 6) < ep.rope_heads) {
+          {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {  // interleaved pairs (2j, 2j+1) share angle j
-            const float a = v[2 * j], b = v[2 * j + 1];
-            v[2 * j] = a * rc[j] - b * rs[j];
-            v[2 * j + 1] = b * rc[j] + a * rs[j];
+            for (int j = 0; j < 32; ++j) {
+              // x = frame * inv_freq[j] is the same fp32 product the reference's table holds; reduce to [-pi, pi] with a
+              // two-term 2*pi (error ~1e-7 rad), then the hardware sin / cos (abs error ~5e-7): far below bf16 rounding
+              const float x = frame_f * __ldg(ep.rope_inv_freq + j);
+              const float k = rintf(x * 0.15915494309189535f);
+              float r = fmaf(k, -6.2831854820251465f, x);
+              r = fmaf(k, 1.7484555e-7f, r);
+              float sn, cs;
+              asm("sin.approx.ftz.f32 %0, %1;" : "=f"(sn) : "f"(r));
+              asm("cos.approx.ftz.f32 %0, %1;" : "=f"(cs) : "f"(r));
+              const float a = v[2 * j], b = v[2 * j + 1];
+              v[2 * j] = a * cs - b * sn;
+              v[2 * j + 1] = b * cs + a * sn;
+            }
           }
         }
         switch (ep.act) {

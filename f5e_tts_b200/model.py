@@ -32,7 +32,7 @@ class _Model(C.Structure):
                                          "conv_groups")] + [
         ("w_in", C.c_void_p), ("b_in", C.c_void_p), ("w_conv1", C.c_void_p), ("b_conv1", C.c_void_p),
         ("w_conv2", C.c_void_p), ("b_conv2", C.c_void_p), ("layers", C.POINTER(_Layer)),
-        ("w_proj", C.c_void_p), ("b_proj", C.c_void_p)]
+        ("w_proj", C.c_void_p), ("b_proj", C.c_void_p), ("rope_inv_freq", C.c_void_p)]
 
 
 class _Buffers(C.Structure):
@@ -238,6 +238,7 @@ class DiT(nn.Module):
         m.w_conv2, m.b_conv2 = K(ops.pack_conv_pos_weight(c["2"].weight.detach().to(dev))), K(f32(c["2"].bias))
         m.layers = C.cast(layers, C.POINTER(_Layer))
         m.w_proj, m.b_proj = K(bf(self.proj_out.weight)), K(f32(self.proj_out.bias))
+        m.rope_inv_freq = K(f32(self.rotary_embed.inv_freq))  # angles are evaluated in the QKV epilogue
         P.layers, P.model = layers, m
         # text embedder
         te = self.text_embed
@@ -263,16 +264,8 @@ class DiT(nn.Module):
                 w = conv.weight.detach().float().to(dev) * s[:, None, None]                # fold eval-mode BatchNorm
                 b = (conv.bias.detach().float().to(dev) - bn.running_mean.detach().float().to(dev)) * s + bn.bias.detach().float().to(dev)
                 P.ppg["convs"].append((bf(w.permute(0, 2, 1).reshape(w.shape[0], -1)), f32(b)))  # [co, tap*C + ci]
-        P.rope = {}
         self._plan = P
         return P
-
-    def _rope(self, n_pad):
-        P = self._get_plan()
-        if n_pad not in P.rope:
-            from .tables import rope_tables
-            P.rope = {n_pad: rope_tables(n_pad, self.dim_head, P.w_mod.device)}
-        return P.rope[n_pad]
 
     def _workspace(self, samples, n_pad):
         key = (samples, n_pad)
@@ -371,9 +364,8 @@ class DiT(nn.Module):
         klen = None
         if mask is not None:
             klen = mask.sum(-1).to(torch.int32).to(dev)
-        cos, sin = self._rope(N)
-        check(_lib.load().f5e_dit_forward(C.byref(P.model), C.byref(buf), ptr(mod), P.mod_size, ptr(klen), ptr(cos), ptr(sin),
-                                          B, N, None, stream_ptr()), "f5e_dit_forward")
+        check(_lib.load().f5e_dit_forward(C.byref(P.model), C.byref(buf), ptr(mod), P.mod_size, ptr(klen), B, N, None,
+                                          stream_ptr()), "f5e_dit_forward")
         return tens["pred"].view(B, N, md).to(x.dtype)
 
 
@@ -511,12 +503,11 @@ class CFM(nn.Module):
         klen = duration.to(torch.int32).repeat(2 if use_cfg else 1).contiguous() if batch > 1 else None
         # batch > 1: the DiT blocks run on the valid frames only (no FLOPs on padding)
         pack, pack_keep = (make_packing(klen, N) if (klen is not None and self.pack_valid_rows) else (None, None))
-        cos, sin = dit._rope(N)
         y = y0.float().contiguous()
         traj = torch.empty(steps, B, N, md, device=y.device, dtype=torch.float32) if self.store_trajectory else None
         dt_arr = (C.c_float * steps)(*dts)
         check(_lib.load().f5e_ode_solve(C.byref(P.model), C.byref(buf), ptr(y), ptr(mod), P.mod_size, dt_arr, steps,
-                                        C.c_float(cfg_strength), ptr(klen), ptr(cos), ptr(sin), B, N, ptr(traj),
+                                        C.c_float(cfg_strength), ptr(klen), B, N, ptr(traj),
                                         int(self.emulate_lowp_state and dtype != torch.float32), int(self.use_cuda_graph),
                                         None if pack is None else C.byref(pack), stream_ptr()), "f5e_ode_solve")
         del pack_keep

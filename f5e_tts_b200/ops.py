@@ -39,8 +39,9 @@ def gemm(a, w, *, bias=None, act=_lib.ACT_NONE, gate=None, gate_stride=0, residu
     ep.ldr = 0 if residual is None else residual.stride(0)
     ep.row_len = 0 if row_len is None else row_len.data_ptr()
     ep.n_pad = n_pad
-    if rope is not None:
-        ep.rope_cos, ep.rope_sin = rope[0].data_ptr(), rope[1].data_ptr()
+    if rope is not None:  # the inv_freq vector [32] (x_transformers RotaryEmbedding.inv_freq, dim_head 64)
+        assert rope.dtype == torch.float32 and rope.numel() == 32 and rope.is_contiguous()
+        ep.rope_inv_freq = rope.data_ptr()
         ep.rope_inner, ep.rope_heads = rope_inner, rope_heads
     for t in (bias, gate):
         assert t is None or t.dtype == torch.float32

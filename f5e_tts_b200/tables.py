@@ -12,11 +12,3 @@ def text_pos_table(dim: int, end: int = 4096, theta: float = 10000.0) -> torch.T
     freqs = 1.0 / (theta ** (torch.arange(0, dim, 2)[: dim // 2].float() / dim))
     f = torch.outer(torch.arange(end), freqs).float()
     return torch.cat([f.cos(), f.sin()], dim=-1).contiguous()
-
-
-def rope_tables(n: int, dim_head: int, device):
-    """(cos, sin) fp32 [n, dim_head/2]: angle(n, j) = n * 10000^(-2j/dim_head), shared by the interleaved pair
-    (2j, 2j+1)  (x_transformers RotaryEmbedding as called at reference backbones/dit.py:245, 454)."""
-    inv = 1.0 / (10000 ** (torch.arange(0, dim_head, 2, device=device).float() / dim_head))
-    ang = torch.arange(n, device=device).float()[:, None] * inv[None]
-    return ang.cos().contiguous(), ang.sin().contiguous()

@@ -54,8 +54,6 @@ typedef struct f5e_epilogue {
   int32_t ldr;
   const int32_t* row_len;  /* [M / n_pad] valid frames per sample, or NULL (rows beyond are zeroed) */
   int32_t n_pad;           /* frames per sample */
-  const float* rope_cos;   /* [n_pad, 32] or NULL */
-  const float* rope_sin;
   int32_t rope_inner;      /* heads * 64 */
   int32_t rope_heads;      /* rotate heads [0, rope_heads) of Q and K */
   int32_t residual_f32;    /* residual is fp32 [M, ldr] */
@@ -63,6 +61,9 @@ typedef struct f5e_epilogue {
                               c+2*out_split3: the A operand of a following fp32-accurate "bf16x3" GEMM whose weight
                               is packed [W_hi | W_lo | W_hi] along K (used by the fp32 Vocos / VQ paths) */
   const int32_t* row_info; /* [M] sample << 16 | frame for packed rows (see f5e_dit_packing), or NULL */
+  const float* rope_inv_freq; /* [32] or NULL: interleaved-pair RoPE on the Q and K column blocks; the angles
+                              frame * inv_freq[j] are evaluated in the epilogue (x_transformers RotaryEmbedding.inv_freq,
+                              reference backbones/dit.py:245, modules.py:470-480) */
 } f5e_epilogue;
 
 /* C[M,N] = epilogue(A[M,K] @ W[N,K]^T); bf16 operands, tcgen05 / TMEM fp32 accumulation.
@@ -142,6 +143,7 @@ typedef struct f5e_dit_model {
   const void* w_conv2; const float* b_conv2;  /* conv_pos_embed.conv1d.2, packed */
   const f5e_dit_layer* layers;                /* HOST array [depth] */
   const void* w_proj;  const float* b_proj;   /* proj_out [mel_dim, dim] */
+  const float* rope_inv_freq;                 /* rotary_embed.inv_freq [32] fp32 (NULL only when rope_heads == 0) */
 } f5e_dit_model;
 
 typedef struct f5e_dit_buffers {   /* caller-allocated scratch, rows = samples * n_pad */
@@ -174,10 +176,9 @@ typedef struct f5e_dit_packing {
  * (AdaLayerNorm / AdaLayerNorm_Final chunk order, model/modules.py:310-315, 331-336); mod_stride = 0 when every
  * sample shares the time step, else the per-sample stride in floats.  klen: int32 [samples] valid frames
  * (attention key mask + zeroing of the attention branch on padded rows), NULL = no mask (batch 1).
- * rope_cos/sin: fp32 [n_pad, 32].  Result in buf->pred. */
+ * Result in buf->pred. */
 int f5e_dit_forward(const f5e_dit_model* model, const f5e_dit_buffers* buf, const float* mod, int32_t mod_stride,
-                    const int32_t* klen, const float* rope_cos, const float* rope_sin, int32_t samples, int32_t n_pad,
-                    const f5e_dit_packing* pack, void* stream);
+                    const int32_t* klen, int32_t samples, int32_t n_pad, const f5e_dit_packing* pack, void* stream);
 
 /* The whole sampler loop (model/cfm.py:431-447, 471 with torchdiffeq fixed-grid Euler): for i in [0, steps):
  *   pred = DiT(x_cat; mod[i]) on the doubled batch (cond half then uncond half; a single half when
@@ -186,9 +187,9 @@ int f5e_dit_forward(const f5e_dit_model* model, const f5e_dit_buffers* buf, cons
  * float [steps].  traj: optional fp32 [steps, batch*n_pad, mel_dim] (state after each step).  klen: int32
  * [2*batch] (both halves) or NULL.  use_graph != 0 captures the loop into one CUDA graph launch. */
 int f5e_ode_solve(const f5e_dit_model* model, const f5e_dit_buffers* buf, float* y, const float* mod, int32_t mod_size,
-                  const float* dt_host, int32_t steps, float cfg_strength, const int32_t* klen, const float* rope_cos,
-                  const float* rope_sin, int32_t batch, int32_t n_pad, float* traj, int32_t round_bf16,
-                  int32_t use_graph, const f5e_dit_packing* pack, void* stream);
+                  const float* dt_host, int32_t steps, float cfg_strength, const int32_t* klen, int32_t batch,
+                  int32_t n_pad, float* traj, int32_t round_bf16, int32_t use_graph, const f5e_dit_packing* pack,
+                  void* stream);
 
 /* ---------------------------------------------------------------------------------------------------
  * fp32 front end / back end / codebook

@@ -57,8 +57,8 @@ def test_gemm_qkv_rope(cuda_dev):
     inv = 1.0 / (10000 ** (torch.arange(0, 64, 2, device=cuda_dev).float() / 64))
     ang = torch.arange(n_pad, device=cuda_dev).float()[:, None] * inv[None]
     cos, sin = ang.cos().contiguous(), ang.sin().contiguous()
-    for heads in (16, 1):
-        out = ops.gemm(a, w, bias=bias, rope=(cos, sin), rope_heads=heads, rope_inner=D, n_pad=n_pad)
+    for heads, rope in ((16, inv.contiguous()), (1, inv.contiguous())):
+        out = ops.gemm(a, w, bias=bias, rope=rope, rope_heads=heads, rope_inner=D, n_pad=n_pad)
         y = (a.float() @ w.float().t() + bias).view(B, n_pad, 3, H, 32, 2)
         c, s = cos[None, :, None, :], sin[None, :, None, :]
         ref = y.clone()

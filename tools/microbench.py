@@ -66,6 +66,11 @@ def main():
             gate = torch.randn(n, device=dev) if res is not None else None
             ms = timeit(lambda: ops.gemm(x, w, bias=b, act=act, out=o, residual=res, gate=gate, n_pad=N))
             rec(f"gemm_{tag}", ms, flops=2.0 * M * n * k, M=M, N=n, K=k)
+            if tag == "qkv":
+                inv = 1.0 / (10000 ** (torch.arange(0, 64, 2, device=dev).float() / 64))
+                invc = inv.contiguous()
+                ms = timeit(lambda: ops.gemm(x, w, bias=b, out=o, n_pad=N, rope=invc, rope_heads=16, rope_inner=1024))
+                rec("gemm_qkv_rope_compute", ms, flops=2.0 * M * n * k, M=M, N=n, K=k)
             if tag in ("qkv", "ff1"):
                 ms = timeit(lambda: ops.gemm(x, w, out=o, n_pad=N))
                 rec(f"gemm_{tag}_plain", ms, flops=2.0 * M * n * k, M=M, N=n, K=k)
