@@ -30,6 +30,12 @@ class Epilogue(C.Structure):
     ]
 
 
+class Guidance(C.Structure):
+    """Mirror of `f5e_guidance` (include/f5e_b200.h)."""
+
+    _fields_ = [("branches", C.c_int32), ("c0", C.c_float), ("c1", C.c_float)]
+
+
 def lib_path() -> Path:
     return _LIB_PATH
 

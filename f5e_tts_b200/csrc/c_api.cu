@@ -54,8 +54,16 @@ int f5e_norm_mod(const void* x, void* out, int32_t M, int32_t D, const float* mu
 int f5e_cfg_euler(const float* pred, int32_t ld_pred, float* y, void* x_cat, int32_t ld_cat, float* traj,
                   int32_t rows, int32_t C, float dt, float cfg_strength, int32_t round_bf16, void* stream) {
   F5E_REQUIRE(pred && y, "f5e_cfg_euler: null argument");
-  return cfg_euler((cudaStream_t)stream, pred, ld_pred, y, (__nv_bfloat16*)x_cat, ld_cat, traj, rows, C, dt,
-                   cfg_strength, round_bf16);
+  const int nb = cfg_strength >= 1e-5f ? 2 : 1;
+  return guided_euler((cudaStream_t)stream, pred, ld_pred, y, (__nv_bfloat16*)x_cat, ld_cat, traj, rows, C, dt, nb,
+                      cfg_strength, 0.0f, round_bf16);
+}
+
+int f5e_guided_euler(const float* pred, int32_t ld_pred, float* y, void* x_cat, int32_t ld_cat, float* traj,
+                     int32_t rows, int32_t C, float dt, const f5e_guidance* g, int32_t round_bf16, void* stream) {
+  F5E_REQUIRE(pred && y && g, "f5e_guided_euler: null argument");
+  return guided_euler((cudaStream_t)stream, pred, ld_pred, y, (__nv_bfloat16*)x_cat, ld_cat, traj, rows, C, dt,
+                      g->branches, g->c0, g->c1, round_bf16);
 }
 
 int f5e_attention(const void* qkv, int32_t ld_qkv, void* out, int32_t ldo, const int32_t* klen, int32_t samples,

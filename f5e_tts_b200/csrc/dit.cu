@@ -124,34 +124,35 @@ int f5e_ode_solve(const f5e_dit_model* model, const f5e_dit_buffers* buf, float*
                   const float* dt_host, int32_t steps, float cfg_strength, const int32_t* klen, int32_t batch,
                   int32_t n_pad, float* traj, int32_t round_bf16, int32_t use_graph, const f5e_dit_packing* pack,
                   void* stream) {
+  f5e_guidance g{cfg_strength >= 1e-5f ? 2 : 1, cfg_strength, 0.0f};
+  return f5e_ode_solve_guided(model, buf, y, mod, mod_size, dt_host, steps, &g, klen, batch, n_pad, traj, round_bf16,
+                              use_graph, pack, stream);
+}
+
+int f5e_ode_solve_guided(const f5e_dit_model* model, const f5e_dit_buffers* buf, float* y, const float* mod,
+                         int32_t mod_size, const float* dt_host, int32_t steps, const f5e_guidance* g,
+                         const int32_t* klen, int32_t batch, int32_t n_pad, float* traj, int32_t round_bf16,
+                         int32_t use_graph, const f5e_dit_packing* pack, void* stream) {
   F5E_TRY(check_model(model, buf));
-  F5E_REQUIRE(y && mod && dt_host && steps > 0 && batch > 0 && n_pad > 0, "f5e_ode_solve: bad arguments");
+  F5E_REQUIRE(y && mod && dt_host && g && steps > 0 && batch > 0 && n_pad > 0, "f5e_ode_solve: bad arguments");
+  F5E_REQUIRE(g->branches >= 1 && g->branches <= 3, "f5e_ode_solve: guidance.branches=%d (1, 2 or 3)", g->branches);
   cudaStream_t st = (cudaStream_t)stream;
   F5E_TRY(ensure_configured());  // attribute setup must not happen inside a stream capture
-  const bool cfg = cfg_strength >= 1e-5f;
-  const int samples = cfg ? 2 * batch : batch;
-  const int rows_half = batch * n_pad;
+  const int nb = g->branches;
+  const int samples = nb * batch;
+  const int rows_state = batch * n_pad;
   F5E_TRY(check_pack(pack, klen, samples, n_pad));
-  F5E_REQUIRE(!pack || !cfg || pack->rows_packed % 2 == 0, "f5e_ode_solve: both CFG halves must pack to the same rows");
-  // packed: pred holds the valid frames back to back (cond half, then uncond half); row_map[0 .. rows_upd) maps the
-  // first half onto the padded state rows
-  const int rows_upd = pack ? (cfg ? pack->rows_packed / 2 : pack->rows_packed) : rows_half;
+  F5E_REQUIRE(!pack || pack->rows_packed % nb == 0, "f5e_ode_solve: every guidance branch must pack to the same rows");
+  // packed: pred holds the valid frames back to back, branch after branch; row_map[0 .. rows_upd) maps the first
+  // branch onto the padded state rows
+  const int rows_upd = pack ? pack->rows_packed / nb : rows_state;
   const int* upd_map = pack ? pack->row_map : nullptr;
   auto enqueue = [&](cudaStream_t es) -> int {
     for (int i = 0; i < steps; ++i) {
       F5E_TRY(dit_forward_impl(es, model, buf, mod + (size_t)i * mod_size, 0, klen, samples, n_pad, pack));
-      // when cfg is off only the first half of x_cat exists: cfg_euler's second x_cat write would be out of
-      // bounds, so the state is written back by pack_cols instead
-      float* tr = traj ? traj + (size_t)i * rows_half * model->mel_dim : nullptr;
-      if (cfg) {
-        F5E_TRY(cfg_euler(es, buf->pred, model->mel_dim, y, (__nv_bfloat16*)buf->x_cat, model->in_dim, tr, rows_upd,
-                          model->mel_dim, dt_host[i], cfg_strength, round_bf16, upd_map, rows_half));
-      } else {
-        F5E_TRY(cfg_euler(es, buf->pred, model->mel_dim, y, nullptr, 0, tr, rows_upd, model->mel_dim, dt_host[i], 0.0f,
-                          round_bf16, upd_map, rows_half));
-        F5E_TRY(pack_cols(es, (__nv_bfloat16*)buf->x_cat, model->in_dim, 0, y, 1, model->mel_dim, rows_half,
-                          model->mel_dim));
-      }
+      float* tr = traj ? traj + (size_t)i * rows_state * model->mel_dim : nullptr;
+      F5E_TRY(guided_euler(es, buf->pred, model->mel_dim, y, (__nv_bfloat16*)buf->x_cat, model->in_dim, tr, rows_upd,
+                           model->mel_dim, dt_host[i], nb, g->c0, g->c1, round_bf16, upd_map, rows_state));
     }
     return 0;
   };

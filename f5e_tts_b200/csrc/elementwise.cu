@@ -109,24 +109,33 @@ int norm_mod(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int M,
 }
 
 // ---------------------------------------------------------------------------------------------
-// cfg_euler: v = pc + (pc - pu) * cfg ; y += dt * v     (reference model/cfm.py:431-447 + Euler)
-// Algorithmic bytes: rows*C*(2 pred reads + y read + y write)*4 (+ 2 bf16 writes into x_cat).
-// ---------------------------------------------------------------------------------------------
+// guided_euler: combine the flow predictions of the guidance branches, then one Euler step y += dt * v
+//   1 branch : v = p0
+//   2 branches (CFM.sample, reference model/cfm.py:431-447):        v = p0 + (p0 - p1) * c0
+//   3 branches (CFM.sample_tts / sample_vc, cfm.py:166-185, 298-317): v = c0 * (p0 - p1) + c1 * (p1 - p2) + p2
+// (same operation order as the reference expressions, in fp32)
+// =====================================================================================================
+template <int NB>
 __global__ void __launch_bounds__(256)
-cfg_euler_kernel(const float* __restrict__ pred, int ld_pred, float* __restrict__ y,
-                 __nv_bfloat16* __restrict__ x_cat, int ld_cat, float* __restrict__ traj, int rows, int C,
-                 float dt, float cfg, int round_bf16, const int* __restrict__ row_map, int rows_state) {
+guided_euler_kernel(const float* __restrict__ pred, int ld_pred, float* __restrict__ y,
+                    __nv_bfloat16* __restrict__ x_cat, int ld_cat, float* __restrict__ traj, int rows, int C,
+                    float dt, float c0, float c1, int round_bf16, const int* __restrict__ row_map, int rows_state) {
   const int quads = C >> 2;  // C % 4 == 0
   const long long total = (long long)rows * quads;
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
     const int r = (int)(idx / quads), q = (int)(idx - (long long)r * quads);
-    const float4 pc = *reinterpret_cast<const float4*>(pred + (size_t)r * ld_pred + q * 4);
-    float4 v = pc;
-    if (cfg >= 1e-5f) {
-      const float4 pu = *reinterpret_cast<const float4*>(pred + ((size_t)rows + r) * ld_pred + q * 4);
-      v.x = pc.x + (pc.x - pu.x) * cfg; v.y = pc.y + (pc.y - pu.y) * cfg;
-      v.z = pc.z + (pc.z - pu.z) * cfg; v.w = pc.w + (pc.w - pu.w) * cfg;
+    const float4 p0 = *reinterpret_cast<const float4*>(pred + (size_t)r * ld_pred + q * 4);
+    float4 v = p0;
+    if (NB == 2) {
+      const float4 p1 = *reinterpret_cast<const float4*>(pred + ((size_t)rows + r) * ld_pred + q * 4);
+      v.x = p0.x + (p0.x - p1.x) * c0; v.y = p0.y + (p0.y - p1.y) * c0;
+      v.z = p0.z + (p0.z - p1.z) * c0; v.w = p0.w + (p0.w - p1.w) * c0;
+    } else if (NB == 3) {
+      const float4 p1 = *reinterpret_cast<const float4*>(pred + ((size_t)rows + r) * ld_pred + q * 4);
+      const float4 p2 = *reinterpret_cast<const float4*>(pred + (2 * (size_t)rows + r) * ld_pred + q * 4);
+      v.x = c0 * (p0.x - p1.x) + c1 * (p1.x - p2.x) + p2.x; v.y = c0 * (p0.y - p1.y) + c1 * (p1.y - p2.y) + p2.y;
+      v.z = c0 * (p0.z - p1.z) + c1 * (p1.z - p2.z) + p2.z; v.w = c0 * (p0.w - p1.w) + c1 * (p1.w - p2.w) + p2.w;
     }
     // packed mode: pred rows are the valid frames back to back, row_map gives their row in the padded state / concat buffer
     const int sr = row_map ? __ldg(row_map + r) : r;
@@ -139,27 +148,35 @@ cfg_euler_kernel(const float* __restrict__ pred, int ld_pred, float* __restrict_
     }
     *yp = yy;
     if (traj) *reinterpret_cast<float4*>(traj + (size_t)sr * C + q * 4) = yy;
-    if (x_cat) {
+    if (x_cat) {  // the new state goes into the concat buffer of every branch
       uint2 u;
       u.x = pack_bf16x2(yy.x, yy.y);
       u.y = pack_bf16x2(yy.z, yy.w);
-      *reinterpret_cast<uint2*>(x_cat + (size_t)sr * ld_cat + q * 4) = u;
-      *reinterpret_cast<uint2*>(x_cat + ((size_t)rows_state + sr) * ld_cat + q * 4) = u;
+#pragma unroll
+      for (int b = 0; b < NB; ++b)
+        *reinterpret_cast<uint2*>(x_cat + ((size_t)b * rows_state + sr) * ld_cat + q * 4) = u;
     }
   }
 }
 
-int cfg_euler(cudaStream_t st, const float* pred, int ld_pred, float* y, __nv_bfloat16* x_cat, int ld_cat,
-              float* traj, int rows, int C, float dt, float cfg, int round_bf16, const int* row_map, int rows_state) {
-  F5E_REQUIRE(rows > 0 && C > 0 && C % 4 == 0, "cfg_euler: need rows>0 and C%%4==0 (rows=%d C=%d)", rows, C);
-  F5E_REQUIRE(ld_pred % 4 == 0 && (x_cat == nullptr || ld_cat % 4 == 0), "cfg_euler: leading dims must be multiples of 4");
+int guided_euler(cudaStream_t st, const float* pred, int ld_pred, float* y, __nv_bfloat16* x_cat, int ld_cat,
+                 float* traj, int rows, int C, float dt, int branches, float c0, float c1, int round_bf16,
+                 const int* row_map, int rows_state) {
+  F5E_REQUIRE(rows > 0 && C > 0 && C % 4 == 0, "guided_euler: need rows>0 and C%%4==0 (rows=%d C=%d)", rows, C);
+  F5E_REQUIRE(ld_pred % 4 == 0 && (x_cat == nullptr || ld_cat % 4 == 0), "guided_euler: leading dims must be multiples of 4");
+  F5E_REQUIRE(branches >= 1 && branches <= 3, "guided_euler: branches=%d (1, 2 or 3)", branches);
   const long long total = (long long)rows * (C / 4);
   int grid = (int)((total + 255) / 256);
   const int cap = num_sms() * 8;
   if (grid > cap) grid = cap;
   LaunchScope ls(st, PROF_ELEM, rows, C, 0);
-  cfg_euler_kernel<<<grid, 256, 0, st>>>(pred, ld_pred, y, x_cat, ld_cat, traj, rows, C, dt, cfg, round_bf16, row_map,
-                                         row_map ? rows_state : rows);
+  const int rs = row_map ? rows_state : rows;
+  if (branches == 1)
+    guided_euler_kernel<1><<<grid, 256, 0, st>>>(pred, ld_pred, y, x_cat, ld_cat, traj, rows, C, dt, c0, c1, round_bf16, row_map, rs);
+  else if (branches == 2)
+    guided_euler_kernel<2><<<grid, 256, 0, st>>>(pred, ld_pred, y, x_cat, ld_cat, traj, rows, C, dt, c0, c1, round_bf16, row_map, rs);
+  else
+    guided_euler_kernel<3><<<grid, 256, 0, st>>>(pred, ld_pred, y, x_cat, ld_cat, traj, rows, C, dt, c0, c1, round_bf16, row_map, rs);
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -26,9 +26,9 @@ int gemm_bf16(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloa
 
 int norm_mod(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int M, int D, const float* mul,
              const float* add, int mod_stride, int n_pad, float plus_one, float eps, const int* row_info = nullptr);
-int cfg_euler(cudaStream_t st, const float* pred, int ld_pred, float* y, __nv_bfloat16* x_cat, int ld_cat,
-              float* traj, int rows, int C, float dt, float cfg, int round_bf16, const int* row_map = nullptr,
-              int rows_state = 0);
+int guided_euler(cudaStream_t st, const float* pred, int ld_pred, float* y, __nv_bfloat16* x_cat, int ld_cat,
+                 float* traj, int rows, int C, float dt, int branches, float c0, float c1, int round_bf16,
+                 const int* row_map = nullptr, int rows_state = 0);
 int gather_rows(cudaStream_t st, const __nv_bfloat16* src, __nv_bfloat16* dst, const int* row_map, int rows, int C);
 // o[rows, inner] = softmax(q k^T * scale, keys < klen[sample]) v over qkv[rows, 3*inner] (Q|K|V column blocks)
 // row_start (optional): first row of every sample when the rows are PACKED (valid frames only); total_rows = rows of qkv

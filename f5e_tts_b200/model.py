@@ -427,7 +427,47 @@ class CFM(nn.Module):
     def sample(self, cond, text, ppg=None, duration=None, *, lens=None, steps=32, cfg_strength=1.0,
                sway_sampling_coef=None, seed=None, max_duration=4096, vocoder=None, no_ref_audio=False,
                duplicate_test=False, t_inter=0.1, edit_mask=None):
-        """Same contract as reference model/cfm.py:348-482; the Euler/CFG loop runs in libf5e_b200 on a doubled batch."""
+        """Same contract as reference model/cfm.py:348-482; the Euler/CFG loop runs in libf5e_b200 on a doubled batch
+        (conditional half, then the all-dropped half)."""
+        if cfg_strength >= 1e-5:
+            branches, g = [(False, False, False), (True, True, True)], _lib.Guidance(2, float(cfg_strength), 0.0)
+        else:
+            branches, g = [(False, False, False)], _lib.Guidance(1, 0.0, 0.0)
+        return self._solve(cond, text, ppg, duration, branches, g, lens=lens, steps=steps,
+                           sway_sampling_coef=sway_sampling_coef, seed=seed, max_duration=max_duration, vocoder=vocoder,
+                           no_ref_audio=no_ref_audio, duplicate_test=duplicate_test, t_inter=t_inter, edit_mask=edit_mask)
+
+    @torch.no_grad()
+    def sample_tts(self, cond, text, duration=None, *, lens=None, steps=32, alpha_spk=1.0, alpha_txt=1.0,
+                   sway_sampling_coef=None, seed=None, max_duration=4096, vocoder=None, no_ref_audio=False,
+                   duplicate_test=False, t_inter=0.1, edit_mask=None):
+        """Reference model/cfm.py:93-223: three-way guidance for TTS on a tripled batch, branch order
+        speaker+text | text only | null (drop_audio_cond, drop_text, drop_ppg per cfm.py:166-185); ppg is None."""
+        branches = [(False, False, True), (True, False, True), (True, True, True)]
+        g = _lib.Guidance(3, float(alpha_spk), float(alpha_txt))
+        return self._solve(cond, text, None, duration, branches, g, lens=lens, steps=steps,
+                           sway_sampling_coef=sway_sampling_coef, seed=seed, max_duration=max_duration, vocoder=vocoder,
+                           no_ref_audio=no_ref_audio, duplicate_test=duplicate_test, t_inter=t_inter, edit_mask=edit_mask)
+
+    @torch.no_grad()
+    def sample_vc(self, cond, ppg=None, duration=None, *, lens=None, steps=32, alpha_spk=1.0, alpha_ppg=1.0,
+                  sway_sampling_coef=None, seed=None, max_duration=4096, vocoder=None, no_ref_audio=False,
+                  duplicate_test=False, t_inter=0.1, edit_mask=None):
+        """Reference model/cfm.py:225-346: three-way guidance for voice conversion, branch order
+        speaker+ppg | ppg only | null (cfm.py:298-317); text is None (TextEmbedding's zero-token path, dit.py:55-56)."""
+        if self.transformer.text_mask_padding and self.transformer.conv_layers > 0:
+            # the reference raises NameError here (dit.py:81: text_mask is undefined when text is None)
+            raise ValueError("f5e_tts_b200.CFM.sample_vc needs a DiT built with text_mask_padding=False (as the reference)")
+        branches = [(False, True, False), (True, True, False), (True, True, True)]
+        g = _lib.Guidance(3, float(alpha_spk), float(alpha_ppg))
+        return self._solve(cond, None, ppg, duration, branches, g, lens=lens, steps=steps,
+                           sway_sampling_coef=sway_sampling_coef, seed=seed, max_duration=max_duration, vocoder=vocoder,
+                           no_ref_audio=no_ref_audio, duplicate_test=duplicate_test, t_inter=t_inter, edit_mask=edit_mask)
+
+    def _solve(self, cond, text, ppg, duration, branches, guidance, *, lens, steps, sway_sampling_coef, seed,
+               max_duration, vocoder, no_ref_audio, duplicate_test, t_inter, edit_mask):
+        """The part the three samplers of the reference share line for line (cfm.py:119-164 + 187-223, 250-296 + 319-346,
+        374-428 + 449-482).  `branches` = (drop_audio_cond, drop_text, drop_ppg) of every stacked evaluation."""
         self.eval()
         dit = self.transformer
         if self.odeint_kwargs.get("method", "euler") != "euler":
@@ -487,29 +527,36 @@ class CFM(nn.Module):
         # ---- device loop ----
         P = dit._get_plan()
         B, N, md, td = batch, max_duration, self.num_channels, dit.text_dim
-        use_cfg = cfg_strength >= 1e-5
-        S = 2 * B if use_cfg else B
+        nb = len(branches)
+        S = nb * B
         tens, buf = dit._workspace(S, N)
         xc = tens["x_cat"]
         rows = B * N
-        halves = [(False, xc[:rows])] + ([(True, xc[rows:])] if use_cfg else [])
-        for drop, xh in halves:
+        t_emb, p_emb = {}, {}  # the reference caches text_cond / text_uncond the same way (dit.py:433-441)
+        for i, (drop_audio, drop_text, drop_ppg) in enumerate(branches):
+            xh = xc[i * rows:(i + 1) * rows]
             ops.pack_cols(xh, 0, y0.reshape(rows, md))
-            ops.pack_cols(xh, md, None if drop else step_cond.reshape(rows, md), md)
-            ops.pack_cols(xh, 2 * md, dit._text_embed(text, B, N, drop).view(rows, td))
+            ops.pack_cols(xh, md, None if drop_audio else step_cond.reshape(rows, md), md)
+            if drop_text not in t_emb:
+                t_emb[drop_text] = dit._text_embed(text, B, N, drop_text)
+            ops.pack_cols(xh, 2 * md, t_emb[drop_text].view(rows, td))
             if dit.use_ppg:
-                ops.pack_cols(xh, 2 * md + td, dit._ppg_embed(ppg, N, drop, B).view(rows, td))
+                pk = drop_ppg or ppg is None
+                if pk not in p_emb:
+                    p_emb[pk] = dit._ppg_embed(ppg, N, drop_ppg, B)
+                ops.pack_cols(xh, 2 * md + td, p_emb[pk].view(rows, td))
+        del t_emb, p_emb
         mod = dit._modulation(t[:-1])
-        klen = duration.to(torch.int32).repeat(2 if use_cfg else 1).contiguous() if batch > 1 else None
+        klen = duration.to(torch.int32).repeat(nb).contiguous() if batch > 1 else None
         # batch > 1: the DiT blocks run on the valid frames only (no FLOPs on padding)
         pack, pack_keep = (make_packing(klen, N) if (klen is not None and self.pack_valid_rows) else (None, None))
         y = y0.float().contiguous()
         traj = torch.empty(steps, B, N, md, device=y.device, dtype=torch.float32) if self.store_trajectory else None
         dt_arr = (C.c_float * steps)(*dts)
-        check(_lib.load().f5e_ode_solve(C.byref(P.model), C.byref(buf), ptr(y), ptr(mod), P.mod_size, dt_arr, steps,
-                                        C.c_float(cfg_strength), ptr(klen), B, N, ptr(traj),
-                                        int(self.emulate_lowp_state and dtype != torch.float32), int(self.use_cuda_graph),
-                                        None if pack is None else C.byref(pack), stream_ptr()), "f5e_ode_solve")
+        check(_lib.load().f5e_ode_solve_guided(
+            C.byref(P.model), C.byref(buf), ptr(y), ptr(mod), P.mod_size, dt_arr, steps, C.byref(guidance), ptr(klen), B, N,
+            ptr(traj), int(self.emulate_lowp_state and dtype != torch.float32), int(self.use_cuda_graph),
+            None if pack is None else C.byref(pack), stream_ptr()), "f5e_ode_solve_guided")
         del pack_keep
         dit.clear_cache()
         sampled = y.to(dtype)

@@ -74,6 +74,17 @@ def cfg_euler(pred, y, dt, cfg, *, x_cat=None, traj=None, round_bf16=False):
     return y
 
 
+def guided_euler(pred, y, dt, branches, c0, c1=0.0, *, x_cat=None, traj=None, round_bf16=False):
+    """In-place Euler step under 1/2/3-branch guidance (f5e_guided_euler); pred is fp32 [branches, rows, ld]."""
+    assert pred.dtype == torch.float32 and y.dtype == torch.float32 and y.is_contiguous()
+    rows, Cc = y.numel() // y.shape[-1], y.shape[-1]
+    g = _lib.Guidance(int(branches), float(c0), float(c1))
+    check(_lib.load().f5e_guided_euler(ptr(pred), pred.stride(-2), ptr(y), ptr(x_cat),
+                                       0 if x_cat is None else x_cat.stride(-2), ptr(traj), rows, Cc, C.c_float(dt),
+                                       C.byref(g), int(round_bf16), stream_ptr()), "f5e_guided_euler")
+    return y
+
+
 def attention(qkv, heads, *, klen=None, n_pad=None, scale=None, out=None):
     """qkv: bf16 [samples*n_pad, 3*heads*64] -> bf16 [samples*n_pad, heads*64]."""
     _cuda_bf16(qkv, "qkv")

@@ -87,6 +87,23 @@ int f5e_norm_mod(const void* x, void* out, int32_t M, int32_t D, const float* mu
 int f5e_cfg_euler(const float* pred, int32_t ld_pred, float* y, void* x_cat, int32_t ld_cat, float* traj,
                   int32_t rows, int32_t C, float dt, float cfg_strength, int32_t round_bf16, void* stream);
 
+/* Guidance of the sampler: how the flow predictions of the `branches` stacked evaluations are combined.
+ *   branches 1: v = p0                                   (cfg_strength < 1e-5, model/cfm.py:440-441)
+ *   branches 2: v = p0 + (p0 - p1) * c0                  (CFM.sample: p0 = conditional, p1 = null, c0 = cfg_strength;
+ *                                                         model/cfm.py:431-447)
+ *   branches 3: v = c0 * (p0 - p1) + c1 * (p1 - p2) + p2 (CFM.sample_tts / sample_vc: p0 = speaker + content,
+ *                                                         p1 = content only, p2 = null, c0 = alpha_spk,
+ *                                                         c1 = alpha_txt / alpha_ppg; model/cfm.py:166-185, :298-317) */
+typedef struct f5e_guidance {
+  int32_t branches;
+  float c0, c1;
+} f5e_guidance;
+
+/* f5e_cfg_euler for any guidance: pred fp32 [branches, rows, ld_pred]; the new state is written into the first C
+ * columns of x_cat (bf16 [branches*rows, ld_cat]) for every branch. */
+int f5e_guided_euler(const float* pred, int32_t ld_pred, float* y, void* x_cat, int32_t ld_cat, float* traj,
+                     int32_t rows, int32_t C, float dt, const f5e_guidance* g, int32_t round_bf16, void* stream);
+
 /* Non-causal flash attention, dim_head 64, keys n >= klen[sample] masked (klen NULL = no mask).
  * qkv: bf16 [samples*n_pad, ld_qkv] with column blocks Q | K | V of heads*64 each (RoPE already applied);
  * out: bf16 [samples*n_pad, ldo] (heads merged).  Query tiles entirely beyond klen are not written.
@@ -190,6 +207,14 @@ int f5e_ode_solve(const f5e_dit_model* model, const f5e_dit_buffers* buf, float*
                   const float* dt_host, int32_t steps, float cfg_strength, const int32_t* klen, int32_t batch,
                   int32_t n_pad, float* traj, int32_t round_bf16, int32_t use_graph, const f5e_dit_packing* pack,
                   void* stream);
+
+/* The same loop under any guidance (CFM.sample_tts / CFM.sample_vc, model/cfm.py:93-346: three evaluations per step on
+ * a TRIPLED batch, branch order speaker+content | content | null).  x_cat, klen and the packing cover
+ * g->branches * batch samples; everything else as f5e_ode_solve. */
+int f5e_ode_solve_guided(const f5e_dit_model* model, const f5e_dit_buffers* buf, float* y, const float* mod,
+                         int32_t mod_size, const float* dt_host, int32_t steps, const f5e_guidance* g,
+                         const int32_t* klen, int32_t batch, int32_t n_pad, float* traj, int32_t round_bf16,
+                         int32_t use_graph, const f5e_dit_packing* pack, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------
  * fp32 front end / back end / codebook

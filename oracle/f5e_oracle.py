@@ -216,12 +216,17 @@ class OracleDiT:
     # -- TextEmbedding (dit.py:54-87) + ConvNeXtV2Block (modules.py:241-269) + GRN (:225-234)
     def text_embed(self, text, batch, seq_len, drop_text):
         sd, cfg = self.sd, self.cfg
-        text = text + 1
-        text = text[:, :seq_len]
-        text = F.pad(text, (0, seq_len - text.shape[1]), value=0)
-        text_mask = text == 0
-        if drop_text:
-            text = torch.zeros_like(text)
+        if text is None:  # dit.py:55-56 (the VC path); the reference has no text_mask here, so mask_padding must be off
+            assert not cfg.text_mask_padding, "reference raises NameError: text=None needs text_mask_padding=False"
+            text = torch.zeros((batch, seq_len), dtype=torch.long, device=self.device)
+            text_mask = None
+        else:
+            text = text + 1
+            text = text[:, :seq_len]
+            text = F.pad(text, (0, seq_len - text.shape[1]), value=0)
+            text_mask = text == 0
+            if drop_text:
+                text = torch.zeros_like(text)
         x = F.embedding(text, sd["text_embed.text_embed.weight"])
         if cfg.conv_layers > 0:
             pos_idx = torch.arange(seq_len, device=x.device).clamp(max=4095)
@@ -344,9 +349,16 @@ def sway_schedule(steps, sway, dtype, device, t_start=0.0):
 @torch.no_grad()
 def cfm_sample(dit: OracleDiT, cond, text, duration, *, ppg=None, lens=None, steps=32, cfg_strength=1.0,
                sway_sampling_coef=None, seed=None, max_duration=4096, no_ref_audio=False, edit_mask=None,
-               y0=None, return_aux=False):
+               y0=None, return_aux=False, mode="cfg", alpha_spk=1.0, alpha_cont=1.0):
     """cond: mel [B, T, 100] (or wave [B, nw]); text: int64 [B, nt] padded with -1.
-    Returns (out, trajectory) like the reference; with return_aux also the integer/bool side products."""
+    Returns (out, trajectory) like the reference; with return_aux also the integer/bool side products.
+    mode "cfg" = CFM.sample (model/cfm.py:348-482); "tts" = CFM.sample_tts (:93-223, text content, ppg must be None,
+    alpha_cont = alpha_txt); "vc" = CFM.sample_vc (:225-346, PPG content, text must be None, alpha_cont = alpha_ppg)."""
+    assert mode in ("cfg", "tts", "vc")
+    if mode == "tts":
+        assert ppg is None
+    if mode == "vc":
+        assert text is None
     dtype, device = dit.dtype, dit.device
     if cond.ndim == 2:
         cond = mel_spectrogram(cond).permute(0, 2, 1)
@@ -373,6 +385,12 @@ def cfm_sample(dit: OracleDiT, cond, text, duration, *, ppg=None, lens=None, ste
     mask = lens_to_mask(duration) if batch > 1 else None
 
     def fn(t, x):
+        if mode != "cfg":  # three evaluations: null, content only, speaker + content (cfm.py:166-185, :298-317)
+            keep_txt, keep_ppg = mode == "tts", mode == "vc"
+            null_flow = dit.sample(x, step_cond, text, ppg, t, True, True, True, mask)
+            cont_flow = dit.sample(x, step_cond, text, ppg, t, True, not keep_txt, not keep_ppg, mask)
+            full_flow = dit.sample(x, step_cond, text, ppg, t, False, not keep_txt, not keep_ppg, mask)
+            return alpha_spk * (full_flow - cont_flow) + alpha_cont * (cont_flow - null_flow) + null_flow
         pred = dit.sample(x, step_cond, text, ppg, t, False, False, False, mask)
         if cfg_strength < 1e-5:
             return pred

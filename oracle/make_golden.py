@@ -72,6 +72,37 @@ def case_sample(name, cfg, batch, seed, with_ppg=False):
     return model, sd
 
 
+def case_sample3(name, cfg, batch, seed, mode):
+    """CFM.sample_tts / CFM.sample_vc (three-way guidance, cfm.py:93-346) on the PPG-conditioned small model."""
+    model, sd = build_reference(cfg, seed)
+    g = torch.Generator().manual_seed(seed + 1)
+    ref_len = torch.randint(12, 20, (batch,), generator=g)
+    dur = torch.randint(40, 64, (batch,), generator=g)
+    tlen = torch.randint(5, 15, (batch,), generator=g)
+    cond = torch.randn(batch, int(ref_len.max()), cfg.mel_dim, generator=g)
+    text = torch.full((batch, int(tlen.max())), -1, dtype=torch.long)
+    for i in range(batch):
+        text[i, : tlen[i]] = torch.randint(0, cfg.text_num_embeds, (int(tlen[i]),), generator=g)
+    ppg = torch.randn(batch, 30, cfg.ppg_dim, generator=g)
+    kw = dict(steps=4, alpha_spk=2.5, sway_sampling_coef=-1.0, seed=9)
+    with torch.no_grad():
+        if mode == "tts":
+            out, traj = model.sample_tts(cond=cond, text=text, duration=dur, lens=ref_len, alpha_txt=3.0, **kw)
+            ppg = None
+        else:
+            out, traj = model.sample_vc(cond=cond, ppg=ppg, duration=dur, lens=ref_len, alpha_ppg=3.0, **kw)
+            text = None
+    dit = O.OracleDiT(cfg, sd)
+    o_out, o_traj, aux = O.cfm_sample(dit, cond, text, dur, ppg=ppg, lens=ref_len, return_aux=True, mode=mode,
+                                      alpha_spk=2.5, alpha_cont=3.0, steps=4, sway_sampling_coef=-1.0, seed=9)
+    print(f"[{name}] oracle vs reference: out rel-L2 {rel(o_out, out):.2e}  max-abs {(o_out - out).abs().max():.2e}; "
+          f"traj rel-L2 {rel(o_traj, traj):.2e}")
+    torch.save(dict(cfg=cfg.__dict__, seed=seed, mode=mode, cond=cond, text=text, ppg=ppg, duration_in=dur, lens=ref_len,
+                    kw=dict(steps=4, alpha_spk=2.5, alpha_cont=3.0, sway_sampling_coef=-1.0, seed=9),
+                    out=out, traj_last=traj[-1], traj_1=traj[1], duration=aux["duration"], mask=aux["mask"],
+                    cond_mask=aux["cond_mask"]), os.path.join(OUT, name + ".pt"))
+
+
 def case_single_eval(name, cfg, seed):
     """One DiT.sample call (cond and uncond) with a per-sample mask."""
     model, sd = build_reference(cfg, seed)
@@ -131,3 +162,5 @@ if __name__ == "__main__":
     case_sample("sample_b1", SMALL, 1, 200)
     case_sample("sample_b3", SMALL, 3, 201)
     case_sample("sample_b2_ppg", SMALL_PPG, 2, 202, with_ppg=True)
+    case_sample3("sample_tts_b2", SMALL_PPG, 2, 203, "tts")
+    case_sample3("sample_vc_b2", SMALL_PPG, 2, 204, "vc")

@@ -103,6 +103,26 @@ def test_cfg_euler(cuda_dev):
     assert xcat[:, 100:].abs().max().item() == 0
 
 
+def test_guided_euler_three_way(cuda_dev):
+    """sample_tts / sample_vc combine (reference cfm.py:184, :316), same operation order in fp32."""
+    from f5e_tts_b200 import ops
+    torch.manual_seed(14)
+    rows, Cc = 777, 100
+    pred = torch.randn(3, rows, Cc, device=cuda_dev)
+    y = torch.randn(rows, Cc, device=cuda_dev)
+    y0 = y.clone()
+    xcat = torch.zeros(3 * rows, 356, device=cuda_dev, dtype=torch.bfloat16)
+    ops.guided_euler(pred, y, 0.05, 3, 2.5, 3.0, x_cat=xcat)
+    ref = y0 + 0.05 * (2.5 * (pred[0] - pred[1]) + 3.0 * (pred[1] - pred[2]) + pred[2])
+    assert torch.allclose(y, ref, atol=2e-6, rtol=1e-6)
+    for b in range(3):
+        assert torch.equal(xcat[b * rows:(b + 1) * rows, :100], y.bfloat16())
+    assert xcat[:, 100:].abs().max().item() == 0
+    y1 = y0.clone()
+    ops.guided_euler(pred, y1, 0.05, 1, 0.0)
+    assert torch.allclose(y1, y0 + 0.05 * pred[0], atol=1e-6, rtol=1e-6)
+
+
 @pytest.mark.parametrize("samples,n_pad,heads,lens", [(1, 128, 1, None), (2, 300, 4, [300, 129]),
                                                        (3, 1031, 16, [1031, 850, 5]), (1, 940, 16, None)])
 def test_attention(cuda_dev, samples, n_pad, heads, lens):

@@ -138,3 +138,50 @@ def test_full_size_f5tts_v1_base_vs_oracle(cuda_dev):
     got1, _ = model.sample(cond[:1, : int(ref_len[0])], text[:1], None, dur[:1], lens=ref_len[:1], seed=5, **kw)
     L0 = int(aux["duration"][0])
     assert rel_l2(got1[0, : L0 - 64].float(), got[0, : L0 - 64].float()) < 2e-2
+
+
+@pytest.mark.parametrize("mode,B", [("tts", 1), ("tts", 3), ("vc", 2)])
+def test_three_way_samplers_vs_oracle(cuda_dev, mode, B):
+    """CFM.sample_tts / CFM.sample_vc (reference cfm.py:93-346): tripled batch, alpha_spk / alpha_txt / alpha_ppg."""
+    cfg = SMALL_PPG
+    model, sd = build(cfg, 27, cuda_dev)
+    g = torch.Generator().manual_seed(28)
+    ref_len = torch.randint(40, 80, (B,), generator=g).to(cuda_dev)
+    dur = torch.randint(150, 300, (B,), generator=g).to(cuda_dev)
+    cond = torch.randn(B, int(ref_len.max()), cfg.mel_dim, generator=g).to(cuda_dev)
+    text = torch.randint(0, cfg.text_num_embeds, (B, 30), generator=g).to(cuda_dev)
+    if B > 1:
+        text[1, 20:] = -1
+    ppg = torch.randn(B, 120, cfg.ppg_dim, generator=g).to(cuda_dev)
+    text, ppg = (text, None) if mode == "tts" else (None, ppg)
+    kw = dict(steps=6, sway_sampling_coef=-1.0)
+    okw = dict(mode=mode, alpha_spk=2.5, alpha_cont=3.0, **kw)
+    o32 = O.OracleDiT(cfg, sd, torch.float32, cuda_dev)
+    o16 = O.OracleDiT(cfg, sd, torch.bfloat16, cuda_dev)
+    out16, traj16, aux = O.cfm_sample(o16, cond, text, dur, ppg=ppg, lens=ref_len, seed=3, return_aux=True, **okw)
+    out32, traj32 = O.cfm_sample(o32, cond.bfloat16().float(), text, dur, ppg=ppg, lens=ref_len, y0=aux["y0"].float(), **okw)
+    if mode == "tts":
+        got, traj = model.sample_tts(cond, text, dur, lens=ref_len, seed=3, alpha_spk=2.5, alpha_txt=3.0, **kw)
+    else:
+        got, traj = model.sample_vc(cond, ppg, dur, lens=ref_len, seed=3, alpha_spk=2.5, alpha_ppg=3.0, **kw)
+    assert traj.shape == traj16.shape and torch.equal(traj[0], aux["y0"])
+    cm = aux["cond_mask"].expand_as(got)
+    assert torch.equal(got[cm], out16[cm])
+    for step in (1, kw["steps"]):
+        for i in range(B):
+            L = int(aux["duration"][i])
+            e_got, e_ref = rel_l2(traj[step][i, :L], traj32[step][i, :L]), rel_l2(traj16[step][i, :L], traj32[step][i, :L])
+            print(f"{mode} B={B} step {step} sample {i}: product-vs-fp32 {e_got:.3e}  oracle-bf16-vs-fp32 {e_ref:.3e}")
+            assert e_got <= K_TOL * e_ref + 5e-3, (step, i, e_got, e_ref)
+    model.use_cuda_graph = True
+    if mode == "tts":
+        got2, _ = model.sample_tts(cond, text, dur, lens=ref_len, seed=3, alpha_spk=2.5, alpha_txt=3.0, **kw)
+    else:
+        got2, _ = model.sample_vc(cond, ppg, dur, lens=ref_len, seed=3, alpha_spk=2.5, alpha_ppg=3.0, **kw)
+    assert torch.equal(got2, got)
+
+
+def test_sample_vc_needs_unmasked_text_embedder(cuda_dev):
+    model, _ = build(SMALL, 7, cuda_dev)  # text_mask_padding=True: the reference raises on text=None
+    with pytest.raises(ValueError):
+        model.sample_vc(torch.randn(1, 30, 100, device=cuda_dev), None, 80)
