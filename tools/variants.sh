@@ -1,3 +1,6 @@
-for v in "-DGEMM_PAIR=0" "-DGEMM_PAIR=1"; do
-  echo "== $v"; F5E_NVCC_FLAGS="$v" timeout 200 python tools/microbench.py --only gemm 2>&1 | grep -E "qkv|ff1|ff2|gemm_out"
+# developer tool: time one microbench group under several compile-time variants of the library
+#   bash tools/variants.sh attn "-DATT_DEFER_OWAIT=0" "-DATT_DEFER_OWAIT=1"
+grp=$1; shift
+for v in "$@"; do
+  echo "== $v"; F5E_NVCC_FLAGS="$v" timeout 300 python tools/microbench.py --only "$grp" 2>&1 | grep -vE "sdpa|cublas"
 done
