@@ -22,12 +22,14 @@ static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_d
   {
     EpiParams ep{};
     ep.out = b->h0; ep.ldo = D; ep.bias = m->b_in; ep.n_pad = n_pad;
+    if (m->isolate_samples) ep.row_len = klen;  // padded frames read as zeros by the convolutions below
     F5E_TRY(gemm_bf16(st, bf(b->x_cat), m->in_dim, bf(m->w_in), m->in_dim, rows, D, m->in_dim, ep));
   }
   // ConvPositionEmbedding: conv+Mish, conv+Mish, + residual (modules.py:167-190, dit.py:176)
   {
     EpiParams ep{};
     ep.out = b->h1; ep.ldo = D; ep.bias = m->b_conv1; ep.act = ACT_MISH; ep.n_pad = n_pad;
+    if (m->isolate_samples) ep.row_len = klen;
     F5E_TRY(conv_pos(st, bf(b->h0), bf(m->w_conv1), samples, n_pad, D, m->conv_groups, ep));
     ep.out = b->x; ep.bias = m->b_conv2; ep.residual = bf(b->h0); ep.ldr = D;
     F5E_TRY(conv_pos(st, bf(b->h1), bf(m->w_conv2), samples, n_pad, D, m->conv_groups, ep));
@@ -97,6 +99,7 @@ static int check_model(const f5e_dit_model* m, const f5e_dit_buffers* b) {
   F5E_REQUIRE(m->in_dim % 8 == 0 && m->mel_dim % 4 == 0, "dit: in_dim %d must be a multiple of 8, mel_dim %d of 4",
               m->in_dim, m->mel_dim);
   F5E_REQUIRE(m->rope_heads == 0 || m->rope_inv_freq, "dit: rope_inv_freq is null");
+  F5E_REQUIRE(m->isolate_samples == 0 || m->isolate_samples == 1, "dit: isolate_samples must be 0 or 1");
   F5E_REQUIRE(b->x_cat && b->h0 && b->h1 && b->x && b->xn && b->qkv && b->attn && b->ff && b->pred, "dit: null scratch buffer");
   return 0;
 }

@@ -32,7 +32,7 @@ class _Model(C.Structure):
                                          "conv_groups")] + [
         ("w_in", C.c_void_p), ("b_in", C.c_void_p), ("w_conv1", C.c_void_p), ("b_conv1", C.c_void_p),
         ("w_conv2", C.c_void_p), ("b_conv2", C.c_void_p), ("layers", C.POINTER(_Layer)),
-        ("w_proj", C.c_void_p), ("b_proj", C.c_void_p), ("rope_inv_freq", C.c_void_p)]
+        ("w_proj", C.c_void_p), ("b_proj", C.c_void_p), ("rope_inv_freq", C.c_void_p), ("isolate_samples", C.c_int32)]
 
 
 class _Buffers(C.Structure):
@@ -364,6 +364,7 @@ class DiT(nn.Module):
         klen = None
         if mask is not None:
             klen = mask.sum(-1).to(torch.int32).to(dev)
+        P.model.isolate_samples = 0
         check(_lib.load().f5e_dit_forward(C.byref(P.model), C.byref(buf), ptr(mod), P.mod_size, ptr(klen), B, N, None,
                                           stream_ptr()), "f5e_dit_forward")
         return tens["pred"].view(B, N, md).to(x.dtype)
@@ -415,6 +416,11 @@ class CFM(nn.Module):
         self.store_trajectory = True      # False: return only [y0, y1] instead of steps+1 states
         self.emulate_lowp_state = False   # True: round the ODE state to bf16 every step like a bf16 reference run
         self.pack_valid_rows = True       # batch > 1: run the DiT blocks on valid frames only (padding costs no FLOPs)
+        # True: a sample's result does not depend on what it is batched with - padded frames are zeroed at the inputs of
+        # the ConvPositionEmbedding convs and the text / PPG embedders run per sample at the sample's own length, so a
+        # padded batch reproduces the batch-1 solves of infer/utils_infer.py:474-482 (pipeline.infer_batch_process).
+        # False (default) = the reference's batched behaviour, padding leaks included.
+        self.isolate_samples = False
 
     @property
     def device(self):
@@ -533,17 +539,27 @@ class CFM(nn.Module):
         xc = tens["x_cat"]
         rows = B * N
         t_emb, p_emb = {}, {}  # the reference caches text_cond / text_uncond the same way (dit.py:433-441)
+        isolate = bool(self.isolate_samples) and batch > 1
+        P.model.isolate_samples = int(isolate)
+
+        def embed(fn, src, drop):  # isolate: every sample embedded alone at its own length, zeros beyond it
+            if not isolate:
+                return fn(src, N, drop)
+            out = torch.zeros(B, N, td, device=xc.device, dtype=torch.bfloat16)
+            for i, d in enumerate(duration.tolist()):
+                out[i, :d] = fn(None if src is None else src[i:i + 1], d, drop)[0]
+            return out
         for i, (drop_audio, drop_text, drop_ppg) in enumerate(branches):
             xh = xc[i * rows:(i + 1) * rows]
             ops.pack_cols(xh, 0, y0.reshape(rows, md))
             ops.pack_cols(xh, md, None if drop_audio else step_cond.reshape(rows, md), md)
             if drop_text not in t_emb:
-                t_emb[drop_text] = dit._text_embed(text, B, N, drop_text)
+                t_emb[drop_text] = embed(lambda tx, n, dr: dit._text_embed(tx, B if not isolate else 1, n, dr), text, drop_text)
             ops.pack_cols(xh, 2 * md, t_emb[drop_text].view(rows, td))
             if dit.use_ppg:
                 pk = drop_ppg or ppg is None
                 if pk not in p_emb:
-                    p_emb[pk] = dit._ppg_embed(ppg, N, drop_ppg, B)
+                    p_emb[pk] = embed(lambda pg, n, dr: dit._ppg_embed(pg, n, dr, B if not isolate else 1), ppg, drop_ppg)
                 ops.pack_cols(xh, 2 * md + td, p_emb[pk].view(rows, td))
         del t_emb, p_emb
         mod = dit._modulation(t[:-1])

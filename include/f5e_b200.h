@@ -161,6 +161,11 @@ typedef struct f5e_dit_model {
   const f5e_dit_layer* layers;                /* HOST array [depth] */
   const void* w_proj;  const float* b_proj;   /* proj_out [mel_dim, dim] */
   const float* rope_inv_freq;                 /* rotary_embed.inv_freq [32] fp32 (NULL only when rope_heads == 0) */
+  int32_t isolate_samples;                    /* != 0 (needs klen): frames >= klen[s] are ZEROED at the inputs of both
+                                               * ConvPositionEmbedding convs, so a sample's result does not depend on
+                                               * what it is batched with (a padded batch then equals the per-sample
+                                               * solves of infer/utils_infer.py:474-482).  0 = the reference's batched
+                                               * behaviour: padded frames leak into the last 15 valid ones */
 } f5e_dit_model;
 
 typedef struct f5e_dit_buffers {   /* caller-allocated scratch, rows = samples * n_pad */
@@ -215,6 +220,34 @@ int f5e_ode_solve_guided(const f5e_dit_model* model, const f5e_dit_buffers* buf,
                          int32_t mod_size, const float* dt_host, int32_t steps, const f5e_guidance* g,
                          const int32_t* klen, int32_t batch, int32_t n_pad, float* traj, int32_t round_bf16,
                          int32_t use_graph, const f5e_dit_packing* pack, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * Prompt preparation / chunk assembly around the sampler
+ * ------------------------------------------------------------------------------------------------- */
+/* Prompt loudness (eval/utils_eval.py:120-123, infer/utils_infer.py:441-443):
+ *   rms[b] = sqrt(mean(wav[b, :lens[b]]^2));  out = rms < target_rms ? wav * target_rms / rms : wav  (zero past lens[b]).
+ * wav / out: fp32 [batch, n_max] with row strides ld_wav / ld_out (out may be NULL: RMS only); lens NULL = n_max each;
+ * scratch: f5e_rms_scratch_floats(batch, n_max) floats.  The sum of squares is reduced in a fixed order (deterministic). */
+int f5e_rms_normalize(const float* wav, int64_t ld_wav, const int32_t* lens, int32_t batch, int32_t n_max,
+                      float target_rms, float* scratch, float* rms_out, float* out, int64_t ld_out, void* stream);
+int f5e_rms_scratch_floats(int32_t batch, int32_t n_max);
+
+/* torchaudio.transforms.Resample(orig, new) as called at eval/utils_eval.py:125-127 and infer/utils_infer.py:444-446
+ * (third-party torchaudio; sinc_interp_hann, lowpass_filter_width 6, rolloff 0.99), as a polyphase FIR:
+ *   out[b, q*up + p] = sum_k kern[p, k] * wav[b, q*down + k - width],  up = new/gcd, down = orig/gcd, taps = 2*width + down,
+ * samples outside [0, lens[b]) read as zero; ceil(up * lens[b] / down) samples are produced per row, the rest of
+ * out[b, :out_max] is zero.  kern: fp32 [up, taps], built by the caller like torchaudio's _get_sinc_resample_kernel. */
+int f5e_resample(const float* wav, int64_t ld_wav, const int32_t* lens, int32_t batch, int32_t n_max, const float* kern,
+                 int32_t taps, int32_t down, int32_t up, int32_t width, float* out, int64_t ld_out, int32_t out_max,
+                 void* stream);
+
+/* One step of the chunk cross-fade chain of infer/utils_infer.py:525-556 (numpy, float64): the float64 wave `acc`
+ * (n_acc samples) is extended in place by the fp32 chunk `next` (n_next samples): cf = min(cf_samples, n_acc, n_next),
+ * the last cf samples become acc * linspace(1, 0, cf) + next[:cf] * linspace(0, 1, cf), the rest of `next` is appended;
+ * *n_out = n_acc + n_next - cf (HOST).  apply_gain != 0 first scales the chunk like `generated_wave * rms / target_rms`
+ * (utils_infer.py:495-496) with gain_num = rms, gain_den = target_rms in fp32.  Bit-identical to the numpy chain. */
+int f5e_crossfade_append(double* acc, int64_t n_acc, const float* next, int32_t n_next, int32_t cf_samples,
+                         float gain_num, float gain_den, int32_t apply_gain, int64_t* n_out, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------
  * fp32 front end / back end / codebook

@@ -501,3 +501,136 @@ def istft_head(x: torch.Tensor, n_fft=1024, hop=256) -> torch.Tensor:
     S = mag * (torch.cos(p) + 1j * torch.sin(p))
     window = torch.hann_window(n_fft, device=x.device, dtype=x.dtype)
     return torch.istft(S, n_fft, hop, n_fft, window, center=True)
+
+
+# -------------------------------------------------------------------------------------------------------
+# Prompt preparation and long-form glue (TEST INFRASTRUCTURE, like the rest of this file)
+# -------------------------------------------------------------------------------------------------------
+def rms_floor(audio: torch.Tensor, target_rms=0.1):
+    """eval/utils_eval.py:120-123 / infer/utils_infer.py:441-443."""
+    rms = torch.sqrt(torch.mean(torch.square(audio)))
+    if rms < target_rms:
+        audio = audio * target_rms / rms
+    return audio, rms
+
+
+def resample(wave: torch.Tensor, orig_freq: int, new_freq: int, lowpass_filter_width=6, rolloff=0.99) -> torch.Tensor:
+    """torchaudio.transforms.Resample(orig, new)(wave) (torchaudio is a third-party dependency of the reference,
+    pyproject.toml; call sites eval/utils_eval.py:125-127, infer/utils_infer.py:444-446), restated from
+    torchaudio.functional.functional._get_sinc_resample_kernel / _apply_sinc_resample_kernel (sinc_interp_hann).
+    Pinned against torchaudio itself by tests/golden/resample.pt."""
+    import math
+    if orig_freq == new_freq:
+        return wave
+    g = math.gcd(int(orig_freq), int(new_freq))
+    orig, new = int(orig_freq) // g, int(new_freq) // g
+    base_freq = min(orig, new) * rolloff
+    width = math.ceil(lowpass_filter_width * orig / base_freq)
+    idx = torch.arange(-width, width + orig, dtype=torch.float64)[None, None] / orig
+    t = torch.arange(0, -new, -1, dtype=torch.float64)[:, None, None] / new + idx
+    t *= base_freq
+    t = t.clamp_(-lowpass_filter_width, lowpass_filter_width)
+    window = torch.cos(t * math.pi / lowpass_filter_width / 2) ** 2
+    t *= math.pi
+    scale = base_freq / orig
+    kernels = torch.where(t == 0, torch.tensor(1.0).to(t), t.sin() / t)
+    kernels *= window * scale
+    kernels = kernels.to(dtype=torch.float32, device=wave.device)
+    shape = wave.size()
+    w = wave.reshape(-1, shape[-1])
+    length = w.shape[1]
+    w = F.pad(w, (width, width + orig))
+    res = F.conv1d(w[:, None], kernels, stride=orig).transpose(1, 2).reshape(w.shape[0], -1)
+    target_length = int(math.ceil(new * length / orig))
+    return res[..., :target_length].reshape(shape[:-1] + (target_length,))
+
+
+def crossfade_chain(waves, cross_fade_duration=0.15, sample_rate=24000):
+    """infer/utils_infer.py:521-556 (numpy; float32 chunks, float64 fades)."""
+    import numpy as np
+    if cross_fade_duration <= 0:
+        return np.concatenate(waves)
+    final = waves[0]
+    for i in range(1, len(waves)):
+        prev, nxt = final, waves[i]
+        n = min(int(cross_fade_duration * sample_rate), len(prev), len(nxt))
+        if n <= 0:
+            final = np.concatenate([prev, nxt])
+            continue
+        mixed = prev[-n:] * np.linspace(1, 0, n) + nxt[:n] * np.linspace(0, 1, n)
+        final = np.concatenate([prev[:-n], mixed, nxt[n:]])
+    return final
+
+
+def long_form(dit: OracleDiT, vocos_sd, ref_audio, sr, ref_text_ids, gen_text_ids, gen_text_bytes, ref_text_bytes, *,
+              steps, cfg_strength=2.0, sway=-1.0, speed=1.0, target_rms=0.1, cross_fade_duration=0.15, seed=None,
+              hop=256, target_sr=24000):
+    """infer_batch_process (infer/utils_infer.py:418-564) with the tokenizer factored out: chunk c has token ids
+    ref_text_ids + gen_text_ids[c] and UTF-8 byte counts ref_text_bytes / gen_text_bytes[c] (the duration rule uses
+    bytes).  One batch-1 solve per chunk, like the reference.  Returns (final wave float64 numpy, [mel per chunk])."""
+    if ref_audio.shape[0] > 1:
+        ref_audio = torch.mean(ref_audio, dim=0, keepdim=True)
+    audio, rms = rms_floor(ref_audio, target_rms)
+    audio = resample(audio, sr, target_sr)
+    ref_len = audio.shape[-1] // hop
+    waves, mels = [], []
+    for ids, nbytes in zip(gen_text_ids, gen_text_bytes):
+        local_speed = 0.3 if nbytes < 10 else speed
+        duration = ref_len + int(ref_len / ref_text_bytes * nbytes / local_speed)
+        text = torch.tensor([list(ref_text_ids) + list(ids)], dtype=torch.long, device=dit.device)
+        out, _ = cfm_sample(dit, audio.to(dit.device), text, duration, steps=steps, cfg_strength=cfg_strength,
+                            sway_sampling_coef=sway, seed=seed)
+        gen = out.to(torch.float32)[:, ref_len:, :].permute(0, 2, 1)
+        wave = vocos_decode(vocos_sd, gen)
+        if rms < target_rms:
+            wave = wave * rms / target_rms
+        waves.append(wave.squeeze().cpu().numpy())
+        mels.append(gen[0].cpu().numpy())
+    return crossfade_chain(waves, cross_fade_duration, target_sr), mels
+
+
+def get_inference_prompt(metainfo, speed=1.0, target_sample_rate=24000, hop_length=256, target_rms=0.1,
+                         infer_batch_size=1, num_buckets=200, min_secs=3, max_secs=40):
+    """eval/utils_eval.py:77-219 with waveforms in place of file names and the tokenizer left out (text_list = raw
+    strings): one prompt at a time on the CPU, like the reference."""
+    import math
+    import random
+    prompts_all = []
+    min_tokens = min_secs * target_sample_rate // hop_length
+    max_tokens = max_secs * target_sample_rate // hop_length
+    acc = [0] * num_buckets
+    cols = [[[] for _ in range(num_buckets)] for _ in range(6)]
+
+    def emit(b):
+        mels = cols[2][b]
+        T = max(m.shape[-1] for m in mels)
+        padded = torch.stack([F.pad(m, (0, T - m.shape[-1]), value=0) for m in mels]).permute(0, 2, 1)
+        prompts_all.append((cols[0][b], cols[1][b], padded, cols[3][b], cols[4][b], cols[5][b]))
+
+    for utt, prompt_text, (ref_audio, ref_sr), gt_text, _ in metainfo:
+        ref_audio = ref_audio.reshape(1, -1)
+        ref_audio, ref_rms = rms_floor(ref_audio, target_rms)
+        ref_audio = resample(ref_audio, ref_sr, target_sample_rate)
+        if len(prompt_text[-1].encode("utf-8")) == 1:
+            prompt_text = prompt_text + " "
+        text_list = [prompt_text + gt_text]
+        ref_mel_len = ref_audio.shape[-1] // hop_length
+        total = ref_mel_len + int(ref_mel_len / len(prompt_text.encode("utf-8")) * len(gt_text.encode("utf-8")) / speed)
+        ref_mel = mel_spectrogram(ref_audio).squeeze(0)
+        assert min_tokens <= total <= max_tokens
+        b = math.floor((total - min_tokens) / (max_tokens - min_tokens + 1) * num_buckets)
+        for c, v in zip(cols, (utt, ref_rms, ref_mel, ref_mel_len, total)):
+            c[b].append(v)
+        cols[5][b].extend(text_list)
+        acc[b] += total
+        if acc[b] >= infer_batch_size:
+            emit(b)
+            acc[b] = 0
+            for c in cols:
+                c[b] = []
+    for b, frames in enumerate(acc):
+        if frames > 0:
+            emit(b)
+    random.seed(666)
+    random.shuffle(prompts_all)
+    return prompts_all

@@ -154,6 +154,41 @@ def case_vq(name):
                     prob_perplexity=r["prob_perplexity"]), os.path.join(OUT, name + ".pt"))
 
 
+def case_resample(name):
+    """torchaudio.transforms.Resample (the reference's resampler, eval/utils_eval.py:125-127) on seeded noise."""
+    import torchaudio
+    g = torch.Generator().manual_seed(21)
+    cases = []
+    for orig, new, n in [(16000, 24000, 9001), (44100, 24000, 12345), (48000, 24000, 8000), (22050, 24000, 7001)]:
+        x = 0.1 * torch.randn(2, n, generator=g)
+        y = torchaudio.transforms.Resample(orig, new)(x)
+        print(f"[{name}] {orig}->{new}: oracle vs torchaudio max-abs {(O.resample(x, orig, new) - y).abs().max():.2e}")
+        cases.append(dict(orig=orig, new=new, x=x, y=y))
+    torch.save(cases, os.path.join(OUT, name + ".pt"))
+
+
+def case_chunk_text(name):
+    """chunk_text of the reference (infer/utils_infer.py:70-98), executed from its source without importing the module
+    (the module pulls pydub / transformers pipelines at import time)."""
+    import ast
+    import re
+    src = open("/root/reference/src/f5_tts/infer/utils_infer.py").read()
+    fn = next(n for n in ast.parse(src).body if isinstance(n, ast.FunctionDef) and n.name == "chunk_text")
+    ns = {"re": re}
+    exec(compile(ast.Module(body=[fn], type_ignores=[]), "utils_infer.py", "exec"), ns)
+    texts = [
+        "Hello there. This is a test of the chunker, which splits on punctuation; it keeps going: really! Does it? Yes.",
+        "短句。这是一个比较长的中文句子，用来测试全角标点的切分；没有空格！对吗？是的。",
+        "No punctuation at all just a very long run of words that never ends " * 5,
+        "Mixed 中文 and English, with commas, and periods. 还有句号。And more!",
+        "",
+        "One.",
+    ]
+    rows = [dict(text=t, max_chars=m, chunks=ns["chunk_text"](t, max_chars=m)) for t in texts for m in (135, 40)]
+    torch.save(rows, os.path.join(OUT, name + ".pt"))
+    print(f"[{name}] {len(rows)} cases")
+
+
 if __name__ == "__main__":
     case_mel("melspec")
     case_vq("vq")
@@ -164,3 +199,5 @@ if __name__ == "__main__":
     case_sample("sample_b2_ppg", SMALL_PPG, 2, 202, with_ppg=True)
     case_sample3("sample_tts_b2", SMALL_PPG, 2, 203, "tts")
     case_sample3("sample_vc_b2", SMALL_PPG, 2, 204, "vc")
+    case_resample("resample")
+    case_chunk_text("chunk_text")
