@@ -92,5 +92,15 @@ def stream_ptr() -> C.c_void_p:
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+_checked_devices: set = set()
+
+
 def require_device() -> None:
+    """The current CUDA device must be sm_100 (checked once per device: cudaGetDeviceProperties costs ~1 ms)."""
+    import torch
+
+    dev = torch.cuda.current_device() if torch.cuda.is_available() else -1
+    if dev in _checked_devices:
+        return
     check(load().f5e_check_device(), "f5e_check_device")
+    _checked_devices.add(dev)
