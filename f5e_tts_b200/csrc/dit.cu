@@ -11,8 +11,11 @@ using namespace f5e;
     if (_rc) return _rc;    \
   } while (0)
 
+static_assert(sizeof(f5e_fold_job) == sizeof(FoldJob), "f5e_fold_job must mirror FoldJob");
+
 static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_dit_buffers* b, const float* mod,
-                            int mod_stride, const int* klen, int samples, int n_pad, const f5e_dit_packing* pack) {
+                            int mod_stride, const int* klen, int samples, int n_pad, const f5e_dit_packing* pack,
+                            bool folded = false) {
   const int D = m->dim, inner = m->heads * 64;
   int rows = samples * n_pad;
   auto bf = [](const void* p) { return reinterpret_cast<const __nv_bfloat16*>(p); };
@@ -54,15 +57,21 @@ static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_d
     const float* ml = mod + (size_t)l * 6 * D;
     const float *shift_msa = ml, *scale_msa = ml + D, *gate_msa = ml + 2 * D;
     const float *shift_mlp = ml + 3 * D, *scale_mlp = ml + 4 * D, *gate_mlp = ml + 5 * D;
-    // adaLN-modulated LayerNorm (modules.py:310-315)
-    F5E_TRY(norm_mod(st, bf(xs), bfm(b->xn), rows, D, scale_msa, shift_msa, mod_stride, n_pad, 1.0f, 1e-6f, row_info));
+    // adaLN-modulated LayerNorm (modules.py:310-315): materialised (norm_mod) or folded into the GEMM (row_stats + W')
+    if (folded) F5E_TRY(row_stats(st, bf(xs), b->stats, bfm(b->stats_a), rows, D, 1e-6f));
+    else F5E_TRY(norm_mod(st, bf(xs), bfm(b->xn), rows, D, scale_msa, shift_msa, mod_stride, n_pad, 1.0f, 1e-6f, row_info));
     {  // fused q/k/v projection + RoPE (modules.py:442-480)
       EpiParams ep{};
       ep.out = b->qkv; ep.ldo = 3 * inner; ep.bias = L.b_qkv; ep.n_pad = n_pad; ep.row_info = row_info;
       if (m->rope_heads > 0) {
         ep.rope_inv_freq = m->rope_inv_freq; ep.rope_inner = inner; ep.rope_heads = m->rope_heads;
       }
-      F5E_TRY(gemm_bf16(st, bf(b->xn), D, bf(L.w_qkv), D, rows, 3 * inner, D, ep));
+      if (folded) {
+        ep.ln_rstd = b->stats; ep.ln_a2 = bf(b->stats_a); ep.bias = L.d_qkv;
+        F5E_TRY(gemm_bf16(st, bf(xs), D, bf(L.wf_qkv), D + 64, rows, 3 * inner, D + 64, ep));
+      } else {
+        F5E_TRY(gemm_bf16(st, bf(b->xn), D, bf(L.w_qkv), D, rows, 3 * inner, D, ep));
+      }
     }
     F5E_TRY(attention(st, bf(b->qkv), 3 * inner, bfm(b->attn), inner, klen, samples, n_pad, m->heads, 0.125f, row_start, rows));
     {  // to_out + masked_fill + gate_msa * attn + residual (modules.py:494-501, :634)
@@ -71,11 +80,17 @@ static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_d
       ep.gate = gate_msa; ep.gate_stride = mod_stride; ep.residual = bf(xs); ep.ldr = D;
       F5E_TRY(gemm_bf16(st, bf(b->attn), inner, bf(L.w_out), inner, rows, D, inner, ep));
     }
-    F5E_TRY(norm_mod(st, bf(xs), bfm(b->xn), rows, D, scale_mlp, shift_mlp, mod_stride, n_pad, 1.0f, 1e-6f, row_info));
+    if (folded) F5E_TRY(row_stats(st, bf(xs), b->stats, bfm(b->stats_a), rows, D, 1e-6f));
+    else F5E_TRY(norm_mod(st, bf(xs), bfm(b->xn), rows, D, scale_mlp, shift_mlp, mod_stride, n_pad, 1.0f, 1e-6f, row_info));
     {  // FeedForward (modules.py:342-353) with GELU(tanh) fused, then gate_mlp * ff + residual (:638)
       EpiParams ep{};
       ep.out = b->ff; ep.ldo = m->ff_dim; ep.bias = L.b_ff1; ep.act = ACT_GELU_TANH; ep.n_pad = n_pad; ep.row_info = row_info;
-      F5E_TRY(gemm_bf16(st, bf(b->xn), D, bf(L.w_ff1), D, rows, m->ff_dim, D, ep));
+      if (folded) {
+        ep.ln_rstd = b->stats; ep.ln_a2 = bf(b->stats_a); ep.bias = L.d_ff1;
+        F5E_TRY(gemm_bf16(st, bf(xs), D, bf(L.wf_ff1), D + 64, rows, m->ff_dim, D + 64, ep));
+      } else {
+        F5E_TRY(gemm_bf16(st, bf(b->xn), D, bf(L.w_ff1), D, rows, m->ff_dim, D, ep));
+      }
       EpiParams e2{};
       e2.out = xs; e2.ldo = D; e2.bias = L.b_ff2; e2.n_pad = n_pad; e2.row_info = row_info;
       e2.gate = gate_mlp; e2.gate_stride = mod_stride; e2.residual = bf(xs); e2.ldr = D;
@@ -150,9 +165,22 @@ int f5e_ode_solve_guided(const f5e_dit_model* model, const f5e_dit_buffers* buf,
   // branch onto the padded state rows
   const int rows_upd = pack ? pack->rows_packed / nb : rows_state;
   const int* upd_map = pack ? pack->row_map : nullptr;
+  // every sample shares the time step here, so the LayerNorms can be folded into the QKV / FF1 GEMMs
+  const bool folded = model->fold_jobs != nullptr;
+  if (folded) {
+    F5E_REQUIRE(buf->stats && buf->stats_a && model->fold_n_jobs == 2 * model->depth && model->fold_rows > 0, "f5e_ode_solve: bad fold set-up");
+    for (int l = 0; l < model->depth; ++l) {
+      const f5e_dit_layer& L = model->layers[l];
+      F5E_REQUIRE(L.wf_qkv && L.c_qkv && L.d_qkv && L.wf_ff1 && L.c_ff1 && L.d_ff1, "f5e_ode_solve: layer %d lacks fold scratch", l);
+    }
+  }
   auto enqueue = [&](cudaStream_t es) -> int {
     for (int i = 0; i < steps; ++i) {
-      F5E_TRY(dit_forward_impl(es, model, buf, mod + (size_t)i * mod_size, 0, klen, samples, n_pad, pack));
+      const float* mod_i = mod + (size_t)i * mod_size;
+      if (folded)
+        F5E_TRY(fold_ln_weights(es, reinterpret_cast<const FoldJob*>(model->fold_jobs), model->fold_n_jobs,
+                                model->fold_rows, model->dim, mod_i));
+      F5E_TRY(dit_forward_impl(es, model, buf, mod_i, 0, klen, samples, n_pad, pack, folded));
       float* tr = traj ? traj + (size_t)i * rows_state * model->mel_dim : nullptr;
       F5E_TRY(guided_euler(es, buf->pred, model->mel_dim, y, (__nv_bfloat16*)buf->x_cat, model->in_dim, tr, rows_upd,
                            model->mel_dim, dt_host[i], nb, g->c0, g->c1, round_bf16, upd_map, rows_state));

@@ -109,6 +109,138 @@ int norm_mod(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int M,
 }
 
 // ---------------------------------------------------------------------------------------------
+// LayerNorm folded into the following GEMM (the Euler loop: every sample shares the time step, so the adaLN
+// (1 + scale) is one vector per layer and step):
+//   LN(x) * (1 + scale) + shift, then @ W^T + b   ==   rstd_r * (x_r . W'_n  -  mu_r * c_n) + d_n
+//   W'_n = bf16(W_n * (1 + scale)),  c_n = sum_k W'_nk,  d_n = b_n + sum_k shift_k W_nk
+// so the GEMM reads the residual stream x itself and the normalised copy (2 * M * D bytes written and read back per
+// norm) is never materialised: row_stats reads x once (M * D * 2 bytes), fold_ln_weights rewrites the weights of all
+// layers once per step (a few hundred MB).  The mean term runs on the tensor core too: W' carries 64 extra K columns
+// (c_hi, c_hi, c_lo, 0...) and the GEMM takes its last K block of A from the [M, 64] matrix row_stats writes,
+// (-mu_hi, -mu_lo, -mu_hi, 0...) (bf16 hi / lo splits: 2^-17 relative), one UMMA_K = 16 step deep; the epilogue is then
+// a single FMA per element, v * rstd_r + d_n, where the plain GEMM has its bias add.  (Applying mean and c_n in the
+// epilogue instead cost two more instructions per element and made the GEMMs 10 % slower: they are epilogue-latency
+// sensitive.)  c_n is summed from the ROUNDED W' so the mean term cancels whatever the rounding of W' did.
+// ---------------------------------------------------------------------------------------------
+template <int CH>
+__global__ void __launch_bounds__(NM_THREADS)
+row_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ rstd_out, __nv_bfloat16* __restrict__ a2, int M,
+                 float eps) {
+  constexpr int D = CH * 256;
+  const int lane = threadIdx.x & 31;
+  const int wstride = gridDim.x * (NM_THREADS / 32);
+  for (int row = blockIdx.x * (NM_THREADS / 32) + (threadIdx.x >> 5); row < M; row += wstride) {
+    const uint4* xr = reinterpret_cast<const uint4*>(x + (size_t)row * D);
+    float v[CH][8];
+    float sum = 0.f;
+#pragma unroll
+    for (int c = 0; c < CH; ++c) {
+      const uint4 u = xr[c * 32 + lane];
+      float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+      v[c][0] = a.x; v[c][1] = a.y; v[c][2] = b.x; v[c][3] = b.y;
+      v[c][4] = cc.x; v[c][5] = cc.y; v[c][6] = d.x; v[c][7] = d.y;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) sum += v[c][i];
+    }
+    const float mean = warp_sum(sum) * (1.0f / D);  // same statistics as norm_mod_kernel
+    float sq = 0.f;
+#pragma unroll
+    for (int c = 0; c < CH; ++c)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float d = v[c][i] - mean;
+        sq += d * d;
+      }
+    const float rstd = rsqrtf(warp_sum(sq) * (1.0f / D) + eps);
+    if (lane == 0) {
+      rstd_out[row] = rstd;
+      const __nv_bfloat16 hi = __float2bfloat16(-mean);
+      const __nv_bfloat16 lo = __float2bfloat16(-mean - __bfloat162float(hi));
+      uint2 u;
+      u.x = (uint32_t)__bfloat16_as_ushort(hi) | ((uint32_t)__bfloat16_as_ushort(lo) << 16);
+      u.y = (uint32_t)__bfloat16_as_ushort(hi);
+      *reinterpret_cast<uint2*>(a2 + (size_t)row * 64) = u;  // columns 4..63 stay zero (allocated zeroed, never written)
+    }
+  }
+}
+
+int row_stats(cudaStream_t st, const __nv_bfloat16* x, float* rstd, __nv_bfloat16* a2, int M, int D, float eps) {
+  F5E_REQUIRE(M > 0 && D % 256 == 0 && D >= 256 && D <= 2048, "row_stats: bad shape M=%d D=%d", M, D);
+  const int wpb = NM_THREADS / 32;
+  int grid = (M + wpb - 1) / wpb;
+  const int cap = num_sms() * 8;
+  if (grid > cap) grid = cap;
+  LaunchScope ls(st, PROF_NORM, M, D, 1);
+#define F5E_RS(CH)                                                                              \
+  case CH:                                                                                      \
+    row_stats_kernel<CH><<<grid, NM_THREADS, 0, st>>>(x, rstd, a2, M, eps); \
+    break;
+  switch (D / 256) {
+    F5E_RS(1) F5E_RS(2) F5E_RS(3) F5E_RS(4) F5E_RS(5) F5E_RS(6) F5E_RS(7) F5E_RS(8)
+  }
+#undef F5E_RS
+  F5E_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// one warp per weight row; `jobs` (device) lists the matrices of every layer: rows [row0, row0 + N) of the launch
+__global__ void __launch_bounds__(256)
+fold_ln_weights_kernel(const FoldJob* __restrict__ jobs, int n_jobs, int total_rows, int D, const float* __restrict__ mod) {
+  const int lane = threadIdx.x & 31;
+  const int grow = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (grow >= total_rows) return;
+  int j = 0;
+  while (j + 1 < n_jobs && grow >= jobs[j + 1].row0) ++j;  // a few dozen jobs: linear scan
+  const FoldJob job = jobs[j];
+  const int n = grow - job.row0;
+  const float* scale = mod + job.scale_off;
+  const float* shift = mod + job.shift_off;
+  const __nv_bfloat16* w = job.w + (size_t)n * D;
+  __nv_bfloat16* wf = job.wf + (size_t)n * (D + 64);  // 64 extra K columns hold the column sum (hi, hi, lo, 0...)
+  float c = 0.f, d = 0.f;
+  for (int k0 = lane * 8; k0 < D; k0 += 256) {
+    const uint4 u = *reinterpret_cast<const uint4*>(w + k0);
+    const float4 s0 = __ldg(reinterpret_cast<const float4*>(scale + k0)), s1 = __ldg(reinterpret_cast<const float4*>(scale + k0 + 4));
+    const float4 h0 = __ldg(reinterpret_cast<const float4*>(shift + k0)), h1 = __ldg(reinterpret_cast<const float4*>(shift + k0 + 4));
+    const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z), e = unpack_bf16x2(u.w);
+    const float wv[8] = {a.x, a.y, b.x, b.y, cc.x, cc.y, e.x, e.y};
+    const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+    const float hv[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int i = 0; i < 8; i += 2) {
+      const uint32_t pk = pack_bf16x2(wv[i] * (1.0f + sv[i]), wv[i + 1] * (1.0f + sv[i + 1]));
+      o[i >> 1] = pk;
+      const float2 r = unpack_bf16x2(pk);  // the rounded values are what the GEMM multiplies
+      c += r.x + r.y;
+      d = fmaf(hv[i], wv[i], d);
+      d = fmaf(hv[i + 1], wv[i + 1], d);
+    }
+    *reinterpret_cast<uint4*>(wf + k0) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+  c = warp_sum(c);
+  d = warp_sum(d);
+  if (lane == 0) {
+    job.c[n] = c;
+    job.d[n] = d + (job.bias ? job.bias[n] : 0.f);
+    const __nv_bfloat16 hi = __float2bfloat16(c);
+    const __nv_bfloat16 lo = __float2bfloat16(c - __bfloat162float(hi));
+    uint2 u;
+    u.x = (uint32_t)__bfloat16_as_ushort(hi) | ((uint32_t)__bfloat16_as_ushort(hi) << 16);
+    u.y = (uint32_t)__bfloat16_as_ushort(lo);
+    *reinterpret_cast<uint2*>(wf + D) = u;  // pairs with (-mu_hi, -mu_lo, -mu_hi): -(mu_hi c_hi + mu_lo c_hi + mu_hi c_lo)
+  }
+}
+
+int fold_ln_weights(cudaStream_t st, const FoldJob* jobs_dev, int n_jobs, int total_rows, int D, const float* mod) {
+  F5E_REQUIRE(jobs_dev && n_jobs > 0 && total_rows > 0 && D % 256 == 0, "fold_ln_weights: bad arguments");
+  LaunchScope ls(st, PROF_NORM, total_rows, D, 2);
+  fold_ln_weights_kernel<<<(total_rows + 7) / 8, 256, 0, st>>>(jobs_dev, n_jobs, total_rows, D, mod);
+  F5E_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
 // guided_euler: combine the flow predictions of the guidance branches, then one Euler step y += dt * v
 //   1 branch : v = p0
 //   2 branches (CFM.sample, reference model/cfm.py:431-447):        v = p0 + (p0 - p1) * c0

@@ -19,6 +19,8 @@ struct EpiParams {
   int gate_stride;                 // 0 = one gate vector shared by every sample
   const __nv_bfloat16* residual;   // [M, ldr] or null : v += residual
   int ldr;
+  const float* ln_rstd;            // [M] or null: folded LayerNorm (gemm_bf16 only): v = v * rstd[row] + bias[col]
+  const __nv_bfloat16* ln_a2;      // [M, 64] with ln_rstd: A operand of the LAST K block (K = dim + 64): -mean as (hi, lo, hi)
   const int* row_len;              // [M / n_pad] or null : rows with (row % n_pad) >= row_len[row / n_pad] -> 0
   int n_pad;                       // frames per sample (row -> (sample, frame)); needed by row_len / rope
   int rope_inner;                  // heads*64 (columns [0, 2*rope_inner) hold Q then K)

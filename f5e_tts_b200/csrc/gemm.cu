@@ -73,7 +73,8 @@ __device__ __forceinline__ uint4* staging_slot(uint8_t* stage, int r, int j) {
 template <int BN, int STAGES, int CG>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmC, int M, int N, int K, EpiParams ep, int accumulate) {
+                 const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmA2, int M, int N, int K,
+                 EpiParams ep, int accumulate) {
   using S = GemmSmem<BN, STAGES, CG>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -98,6 +99,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmC);
+    if (ep.ln_a2) tma_prefetch_desc(&tmA2);
     for (int i = 0; i < STAGES; ++i) {
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
@@ -128,13 +130,18 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * S::STAGE_BYTES;
           uint8_t* sb = sa + S::A_BYTES;
+          // folded LayerNorm: the LAST K block of A comes from the per-row statistics matrix (-mean split in bf16),
+          // against the column sums appended to the folded weight, so the tensor core does the mean correction
+          const bool from_a2 = ep.ln_a2 && kb == nkb - 1;
+          const CUtensorMap* ta = from_a2 ? &tmA2 : &tmA;
+          const int ka = from_a2 ? 0 : kb * GEMM_BK;
           if (CG == 2) {  // both CTAs' bytes complete on the leader's barrier
             if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * S::STAGE_BYTES);
-            tma_load_2d_2cta(sa, &tmA, &full_bar[stage], kb * GEMM_BK, m_blk * TILE_M + rank * GEMM_BM);
+            tma_load_2d_2cta(sa, ta, &full_bar[stage], ka, m_blk * TILE_M + rank * GEMM_BM);
             tma_load_2d_2cta(sb, &tmB, &full_bar[stage], kb * GEMM_BK, n_blk * BN + rank * (BN / 2));
           } else {
             mbar_expect_tx(&full_bar[stage], S::STAGE_BYTES);
-            tma_load_2d(sa, &tmA, &full_bar[stage], kb * GEMM_BK, m_blk * GEMM_BM);
+            tma_load_2d(sa, ta, &full_bar[stage], ka, m_blk * GEMM_BM);
             tma_load_2d(sb, &tmB, &full_bar[stage], kb * GEMM_BK, n_blk * BN);
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -158,8 +165,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const uint32_t sa = smem_u32(smem + stage * S::STAGE_BYTES);
           const uint64_t adesc = umma_desc_kmajor_sw128(sa);
           const uint64_t bdesc = umma_desc_kmajor_sw128(sa + S::A_BYTES);
+          const int ksteps = (ep.ln_a2 && kb == nkb - 1) ? 1 : GEMM_BK / 16;  // the statistics block is 16 columns deep
 #pragma unroll
           for (int k = 0; k < GEMM_BK / 16; ++k) {  // +32 bytes (2 x 16B units) per UMMA_K inside the swizzle atom
+            if (k >= ksteps) break;
             if (CG == 2) umma_f16_ss_2cta(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
             else umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
           }
@@ -226,7 +235,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           for (int i = 0; i < 32; ++i) { v[i] = __uint_as_float(r0[i]); v[32 + i] = __uint_as_float(r1[i]); }
         }
         const bool full = col0 + 64 <= N;
-        if (ep.bias) {
+        if (ep.ln_rstd) {  // folded LayerNorm: acc already holds x . W' - mean * colsum(W'); scale by rstd, add d (as bias)
+          const float rs = __ldg(ep.ln_rstd + rowc);
+#pragma unroll
+          for (int i = 0; i < 64; i += 4) {
+            if (col0 + i < N) {
+              const float4 b = __ldg(reinterpret_cast<const float4*>(ep.bias + col0 + i));
+              v[i] = fmaf(v[i], rs, b.x); v[i + 1] = fmaf(v[i + 1], rs, b.y);
+              v[i + 2] = fmaf(v[i + 2], rs, b.z); v[i + 3] = fmaf(v[i + 3], rs, b.w);
+            }
+          }
+        } else if (ep.bias) {
           if (full) {
 #pragma unroll
             for (int i = 0; i < 64; i += 4) {
@@ -389,8 +408,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 }
 
 template <int BN, int STAGES, int CG>
-static int launch_gemm(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, int M, int N,
-                       int K, const EpiParams& ep, int accumulate) {
+static int launch_gemm(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                       const CUtensorMap& tmA2, int M, int N, int K, const EpiParams& ep, int accumulate) {
   using S = GemmSmem<BN, STAGES, CG>;
   const int tiles = ((M + GEMM_BM * CG - 1) / (GEMM_BM * CG)) * ((N + BN - 1) / BN);
   const int slots = num_sms() / CG;  // CTAs (CG = 1) or CTA pairs (CG = 2) that can be resident
@@ -408,7 +427,7 @@ static int launch_gemm(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMa
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  F5E_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<BN, STAGES, CG>, tmA, tmB, tmC, M, N, K, ep, accumulate));
+  F5E_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<BN, STAGES, CG>, tmA, tmB, tmC, tmA2, M, N, K, ep, accumulate));
   return 0;
 }
 
@@ -428,14 +447,24 @@ int gemm_bf16(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloa
   F5E_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_bf16: empty problem (M=%d N=%d K=%d)", M, N, K);
   F5E_REQUIRE(ep.out != nullptr, "gemm_bf16: null output");
   F5E_REQUIRE(ep.n_pad > 0, "gemm_bf16: n_pad must be positive");
+  F5E_REQUIRE((ep.ln_rstd == nullptr) == (ep.ln_a2 == nullptr), "gemm_bf16: folded LayerNorm needs ln_rstd and ln_a2");
+  F5E_REQUIRE(!ep.ln_rstd || (ep.bias && N % 4 == 0 && K % GEMM_BK == 0 && K > GEMM_BK),
+              "gemm_bf16: folded LayerNorm needs a bias (d), N %% 4 == 0 and K = dim + 64");
   F5E_REQUIRE(!(ep.split3 > 0) || (N % 64 == 0 && !ep.out_f32), "gemm_bf16: split3 output needs N %% 64 == 0 and bf16");
   const bool wide = N > 128;
   // x += epilogue(...) with the residual aliasing the output: the read-modify-write is a TMA reduce-add
   const bool alias = ep.residual && (const void*)ep.residual == (const void*)ep.out && ep.ldr == ep.ldo &&
                      (ep.res_f32 != 0) == (ep.out_f32 != 0) && ep.split3 == 0;
-  CUtensorMap tmA, tmB, tmC;
-  int rc = make_tmap_2d(&tmA, A, 2, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, GEMM_BK, GEMM_BM);
+  CUtensorMap tmA, tmB, tmC, tmA2;
+  // folded LayerNorm: K counts the 64-column statistics block, which lives in its own [M, 64] matrix
+  int rc = make_tmap_2d(&tmA, A, 2, (uint64_t)(ep.ln_a2 ? K - GEMM_BK : K), (uint64_t)M, (uint64_t)lda * 2, GEMM_BK, GEMM_BM);
   if (rc) return rc;
+  if (ep.ln_a2) {
+    rc = make_tmap_2d(&tmA2, ep.ln_a2, 2, (uint64_t)GEMM_BK, (uint64_t)M, (uint64_t)GEMM_BK * 2, GEMM_BK, GEMM_BM);
+    if (rc) return rc;
+  } else {
+    tmA2 = tmA;
+  }
   // CTA pairs when there are enough 256-row tiles to fill the 74 pairs; each CTA then loads a 128-row half of the W tile
   const bool pair = wide && GEMM_PAIR && ((M + 255) / 256) * ((N + 255) / 256) >= num_sms() / 2;
   rc = make_tmap_2d(&tmB, W, 2, (uint64_t)K, (uint64_t)N, (uint64_t)ldw * 2, GEMM_BK, (wide && !pair) ? 256 : 128);
@@ -445,9 +474,9 @@ int gemm_bf16(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloa
   else
     rc = make_tmap_2d(&tmC, ep.out, 2, (uint64_t)(ep.split3 > 0 ? 3 * ep.split3 : N), (uint64_t)M, (uint64_t)ep.ldo * 2, 64, 32);
   if (rc) return rc;
-  if (pair) return launch_gemm<256, 5, 2>(st, tmA, tmB, tmC, M, N, K, ep, alias ? 1 : 0);
-  if (wide) return launch_gemm<256, 4, 1>(st, tmA, tmB, tmC, M, N, K, ep, alias ? 1 : 0);
-  return launch_gemm<128, 6, 1>(st, tmA, tmB, tmC, M, N, K, ep, alias ? 1 : 0);
+  if (pair) return launch_gemm<256, 5, 2>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
+  if (wide) return launch_gemm<256, 4, 1>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
+  return launch_gemm<128, 6, 1>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
 }
 
 }  // namespace f5e

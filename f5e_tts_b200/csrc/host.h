@@ -26,6 +26,17 @@ int gemm_bf16(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloa
 
 int norm_mod(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int M, int D, const float* mul,
              const float* add, int mod_stride, int n_pad, float plus_one, float eps, const int* row_info = nullptr);
+// LayerNorm folded into the next GEMM (elementwise.cu): per-row (mean, rstd) of x; per-step rewrite of the weights
+struct FoldJob {  // device-resident job list of fold_ln_weights; mirrors the public f5e_fold_job
+  const __nv_bfloat16* w;   // [N, D] original weight
+  const float* bias;        // [N] or null
+  __nv_bfloat16* wf;        // [N, D + 64] out: bf16(w * (1 + scale)) | column sum as (hi, hi, lo, 0 ...)
+  float* c;                 // [N] out: row sums of wf
+  float* d;                 // [N] out: bias + w . shift
+  int N, row0, scale_off, shift_off;  // rows of this job, first launch row, offsets of scale / shift in the step's mod vector
+};
+int row_stats(cudaStream_t st, const __nv_bfloat16* x, float* rstd, __nv_bfloat16* a2, int M, int D, float eps);
+int fold_ln_weights(cudaStream_t st, const FoldJob* jobs_dev, int n_jobs, int total_rows, int D, const float* mod);
 int guided_euler(cudaStream_t st, const float* pred, int ld_pred, float* y, __nv_bfloat16* x_cat, int ld_cat,
                  float* traj, int rows, int C, float dt, int branches, float c0, float c1, int round_bf16,
                  const int* row_map = nullptr, int rows_state = 0);

@@ -13,6 +13,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 
 import torch
 import torch.nn.functional as F
@@ -24,7 +25,13 @@ from ._lib import check, ptr, stream_ptr
 
 # ---- ctypes mirrors of include/f5e_b200.h ------------------------------------------------------------
 class _Layer(C.Structure):
-    _fields_ = [(n, C.c_void_p) for n in ("w_qkv", "b_qkv", "w_out", "b_out", "w_ff1", "b_ff1", "w_ff2", "b_ff2")]
+    _fields_ = [(n, C.c_void_p) for n in ("w_qkv", "b_qkv", "w_out", "b_out", "w_ff1", "b_ff1", "w_ff2", "b_ff2",
+                                          "wf_qkv", "c_qkv", "d_qkv", "wf_ff1", "c_ff1", "d_ff1")]
+
+
+class _FoldJob(C.Structure):  # f5e_fold_job
+    _fields_ = [("w", C.c_void_p), ("bias", C.c_void_p), ("wf", C.c_void_p), ("c", C.c_void_p), ("d", C.c_void_p),
+                ("N", C.c_int32), ("row0", C.c_int32), ("scale_off", C.c_int32), ("shift_off", C.c_int32)]
 
 
 class _Model(C.Structure):
@@ -32,11 +39,12 @@ class _Model(C.Structure):
                                          "conv_groups")] + [
         ("w_in", C.c_void_p), ("b_in", C.c_void_p), ("w_conv1", C.c_void_p), ("b_conv1", C.c_void_p),
         ("w_conv2", C.c_void_p), ("b_conv2", C.c_void_p), ("layers", C.POINTER(_Layer)),
-        ("w_proj", C.c_void_p), ("b_proj", C.c_void_p), ("rope_inv_freq", C.c_void_p), ("isolate_samples", C.c_int32)]
+        ("w_proj", C.c_void_p), ("b_proj", C.c_void_p), ("rope_inv_freq", C.c_void_p), ("fold_jobs", C.c_void_p), ("fold_n_jobs", C.c_int32), ("fold_rows", C.c_int32),
+        ("isolate_samples", C.c_int32)]
 
 
 class _Buffers(C.Structure):
-    _fields_ = [(n, C.c_void_p) for n in ("x_cat", "h0", "h1", "x", "xn", "qkv", "attn", "ff", "pred")]
+    _fields_ = [(n, C.c_void_p) for n in ("x_cat", "h0", "h1", "x", "xn", "qkv", "attn", "ff", "pred", "stats", "stats_a")]
 
 
 class _Packing(C.Structure):  # f5e_dit_packing
@@ -167,6 +175,8 @@ class DiT(nn.Module):
         self.text_cond = self.text_uncond = None
         self._plan = None
         self._ws = {}
+        # Euler loop only: fold the adaLN LayerNorms into the QKV / FF1 GEMMs (no normalised copy of the activations)
+        self.fold_layernorm = os.environ.get("F5E_FOLD_LN", "1") != "0"
         self.initialize_weights()
 
     def initialize_weights(self):  # backbones/dit.py:273-283
@@ -221,6 +231,24 @@ class DiT(nn.Module):
             layers[l].w_ff2, layers[l].b_ff2 = K(bf(blk.ff.ff["2"].weight)), K(f32(blk.ff.ff["2"].bias))
             mod_w.append(blk.attn_norm.linear.weight)
             mod_b.append(blk.attn_norm.linear.bias)
+        # folded-LayerNorm path of the Euler loop (include/f5e_b200.h: f5e_fold_job): per-step rewritten QKV / FF1 weights
+        jobs = (_FoldJob * (2 * self.depth))()
+        row0 = 0
+        for l in range(self.depth):
+            for which, (wk, bk, n_out, sc, sh) in enumerate((("w_qkv", "b_qkv", 3 * self.heads * 64, 1, 0),
+                                                             ("w_ff1", "b_ff1", D * self.ff_mult, 4, 3))):
+                wf = torch.zeros(n_out, D + 64, device=dev, dtype=torch.bfloat16)
+                cv, dv = torch.empty(n_out, device=dev), torch.empty(n_out, device=dev)
+                tag = "qkv" if which == 0 else "ff1"
+                setattr(layers[l], "wf_" + tag, K(wf))
+                setattr(layers[l], "c_" + tag, K(cv))
+                setattr(layers[l], "d_" + tag, K(dv))
+                j = jobs[2 * l + which]
+                j.w, j.bias, j.wf, j.c, j.d = getattr(layers[l], wk), getattr(layers[l], bk), wf.data_ptr(), cv.data_ptr(), dv.data_ptr()
+                j.N, j.row0, j.scale_off, j.shift_off = n_out, row0, (l * 6 + sc) * D, (l * 6 + sh) * D
+                row0 += n_out
+        P.fold_jobs = torch.frombuffer(bytearray(bytes(jobs)), dtype=torch.uint8).to(dev)
+        P.fold_n_jobs, P.fold_rows = 2 * self.depth, row0
         mod_w.append(self.norm_out.linear.weight)
         mod_b.append(self.norm_out.linear.bias)
         P.w_mod, P.b_mod = bf(torch.cat(mod_w, 0)), f32(torch.cat(mod_b, 0))
@@ -274,7 +302,8 @@ class DiT(nn.Module):
             mk = lambda c, dt=torch.bfloat16: torch.empty(rows, c, device=dev, dtype=dt)  # noqa: E731
             t = dict(x_cat=torch.zeros(rows, self.in_dim, device=dev, dtype=torch.bfloat16), h0=mk(D), h1=mk(D), x=mk(D),
                      xn=mk(D), qkv=mk(3 * inner), attn=torch.zeros(rows, inner, device=dev, dtype=torch.bfloat16),
-                     ff=mk(D * self.ff_mult), pred=mk(self.mel_dim, torch.float32))
+                     ff=mk(D * self.ff_mult), pred=mk(self.mel_dim, torch.float32), stats=mk(1, torch.float32),
+                     stats_a=torch.zeros(rows, 64, device=dev, dtype=torch.bfloat16))
             b = _Buffers(**{k: v.data_ptr() for k, v in t.items()})
             self._ws = {key: (t, b)}  # keep only the latest shape
         return self._ws[key]
@@ -541,6 +570,9 @@ class CFM(nn.Module):
         t_emb, p_emb = {}, {}  # the reference caches text_cond / text_uncond the same way (dit.py:433-441)
         isolate = bool(self.isolate_samples) and batch > 1
         P.model.isolate_samples = int(isolate)
+        fold = bool(getattr(dit, "fold_layernorm", False))
+        P.model.fold_jobs = P.fold_jobs.data_ptr() if fold else None
+        P.model.fold_n_jobs, P.model.fold_rows = (P.fold_n_jobs, P.fold_rows) if fold else (0, 0)
 
         def embed(fn, src, drop):  # isolate: every sample embedded alone at its own length, zeros beyond it
             if not isolate:

@@ -151,7 +151,28 @@ typedef struct f5e_dit_layer {     /* one DiTBlock (model/modules.py:610-641); w
   const void* w_out;  const float* b_out;   /* attn.to_out.0 : [dim, inner] */
   const void* w_ff1;  const float* b_ff1;   /* ff.ff.0.0     : [ff_dim, dim] */
   const void* w_ff2;  const float* b_ff2;   /* ff.ff.2       : [dim, ff_dim] */
+  /* Optional scratch of the folded-LayerNorm path of f5e_ode_solve (all NULL = off; see f5e_fold_job): per-step
+   * rewritten weights bf16 [3*inner, dim + 64] / [ff_dim, dim + 64] (ZERO-initialised by the caller; the 64 extra K
+   * columns carry the row sum) and their fp32 column vectors c (row sums) and d (bias). */
+  void* wf_qkv;  float* c_qkv;  float* d_qkv;
+  void* wf_ff1;  float* c_ff1;  float* d_ff1;
 } f5e_dit_layer;
+
+/* One entry of the DEVICE-resident job list of the folded-LayerNorm path.  In the Euler loop every sample shares the
+ * time step, so AdaLayerNorm's (1 + scale) is one vector per layer and step (model/modules.py:310-315, :636) and
+ *   (LN(x) * (1 + scale) + shift) @ W^T + b  ==  rstd_r * (x_r . W'_n - mean_r * c_n) + d_n,
+ *   W' = bf16(W * (1 + scale)),  c_n = sum_k W'_nk,  d_n = b_n + sum_k shift_k W_nk :
+ * the QKV / FF1 GEMMs read the residual stream itself and the normalised copy is never written; the mean term is one
+ * more UMMA_K step ((-mean) split in bf16 against c_n split in bf16), the epilogue is v * rstd + d.  Once per step ONE
+ * kernel rewrites W', c, d of every job from that step's modulation vector (scale_off / shift_off index into it). */
+typedef struct f5e_fold_job {
+  const void* w;      /* bf16 [N, dim] */
+  const float* bias;  /* [N] or NULL  */
+  void* wf;           /* bf16 [N, dim + 64] out: W' | (c_hi, c_hi, c_lo, 0 ...) */
+  float* c;           /* [N] out */
+  float* d;           /* [N] out */
+  int32_t N, row0, scale_off, shift_off;  /* row0 = first row of this job in the launch (prefix sum of N) */
+} f5e_fold_job;
 
 typedef struct f5e_dit_model {
   int32_t dim, depth, heads, ff_dim, in_dim, mel_dim, rope_heads, conv_groups;
@@ -161,6 +182,8 @@ typedef struct f5e_dit_model {
   const f5e_dit_layer* layers;                /* HOST array [depth] */
   const void* w_proj;  const float* b_proj;   /* proj_out [mel_dim, dim] */
   const float* rope_inv_freq;                 /* rotary_embed.inv_freq [32] fp32 (NULL only when rope_heads == 0) */
+  const f5e_fold_job* fold_jobs;              /* DEVICE array [fold_n_jobs] (2 per layer: QKV, FF1) or NULL = no folding */
+  int32_t fold_n_jobs, fold_rows;             /* fold_rows = sum of N over the jobs */
   int32_t isolate_samples;                    /* != 0 (needs klen): frames >= klen[s] are ZEROED at the inputs of both
                                                * ConvPositionEmbedding convs, so a sample's result does not depend on
                                                * what it is batched with (a padded batch then equals the per-sample
@@ -178,6 +201,8 @@ typedef struct f5e_dit_buffers {   /* caller-allocated scratch, rows = samples *
   void* attn;     /* bf16 [rows, heads*64]                                                         */
   void* ff;       /* bf16 [rows, ff_dim]                                                           */
   float* pred;    /* fp32 [rows, mel_dim]                                                          */
+  float* stats;   /* fp32 [rows] rstd of the folded-LayerNorm path; NULL when fold_jobs is NULL                    */
+  void* stats_a;  /* bf16 [rows, 64], ZERO-initialised by the caller: (-mean_hi, -mean_lo, -mean_hi, 0 ...) per row */
 } f5e_dit_buffers;
 
 /* Optional row packing: after the (unmasked, hence padded-layout) ConvPositionEmbedding nothing but the key-masked
