@@ -1,0 +1,75 @@
+"""Batched evaluation inference, sharded by batch across ranks: the loop of eval/eval_infer_batch.py:184-220
+(and its _tts / _vc siblings) over the prompts `pipeline.get_inference_prompt` produced.
+
+The reference splits the shuffled batch list contiguously between processes (`accelerator.split_between_processes`),
+decodes every utterance with its own Vocos call, copies each wave to the host and writes a file.  Here a rank solves its
+batches (LPT-balanced on the modelled cost by default, `split="reference"` keeps the contiguous split), decodes a whole
+batch with one `Vocos.decode_varlen`, applies the loudness gain on the device and hands (utt, wave) to a sink - writing
+files (torchaudio.save in the reference) stays with the caller.  The only exchange is the optional final gather."""
+from __future__ import annotations
+
+import torch
+
+from . import dist as fdist
+
+TARGET_SAMPLE_RATE, HOP_LENGTH = 24000, 256
+
+
+def split_batches(prompts_all, rank: int, world: int, split: str = "lpt") -> list:
+    """Indices of the batches rank `rank` solves.  "reference": contiguous chunks like accelerate's
+    split_between_processes (the first len % world ranks get one more); "lpt": longest-processing-time on the modelled
+    cost sum(a N + b N^2) of each batch (dist.utterance_cost), deterministic, identical on every rank."""
+    n = len(prompts_all)
+    if world <= 1:
+        return list(range(n))
+    if split == "reference":
+        base, extra = divmod(n, world)
+        start = rank * base + min(rank, extra)
+        return list(range(start, start + base + (1 if rank < extra else 0)))
+    if split != "lpt":
+        raise ValueError(f"split must be 'lpt' or 'reference', not {split!r}")
+    cost = [sum(fdist.utterance_cost(d) for d in p[4]) for p in prompts_all]
+    order = sorted(range(n), key=lambda i: (-cost[i], i))
+    load, mine = [0.0] * world, []
+    for i in order:
+        r = min(range(world), key=lambda k: (load[k], k))
+        load[r] += cost[i]
+        if r == rank:
+            mine.append(i)
+    return sorted(mine)
+
+
+@torch.no_grad()
+def infer_batches(model, vocoder, prompts_all, *, nfe_step=32, cfg_strength=2.0, sway_sampling_coef=-1.0,
+                  no_ref_audio=False, seed=None, target_rms=0.1, rank=0, world=1, split="lpt", sink=None, device=None,
+                  sampler="sample", sampler_kwargs=None):
+    """Solve this rank's batches.  Returns [(utt, wave fp32 [1, n] on the CPU)] (or whatever `sink(utt, wave, sr)`
+    returned, when a sink is given).  sampler: "sample" (eval_infer_batch.py), "sample_tts" (eval_infer_batch_tts.py:
+    alpha_spk / alpha_txt in sampler_kwargs instead of cfg_strength)."""
+    dev = torch.device(device) if device is not None else model.device
+    out = []
+    for bi in split_batches(prompts_all, rank, world, split):
+        utts, ref_rms_list, ref_mels, ref_mel_lens, total_mel_lens, final_text_list = prompts_all[bi]
+        ref_mels = ref_mels.to(dev)
+        ref_len = torch.tensor(ref_mel_lens, dtype=torch.long, device=dev)
+        total = torch.tensor(total_mel_lens, dtype=torch.long, device=dev)
+        if sampler == "sample":
+            generated, _ = model.sample(cond=ref_mels, text=final_text_list, duration=total, lens=ref_len, steps=nfe_step,
+                                        cfg_strength=cfg_strength, sway_sampling_coef=sway_sampling_coef,
+                                        no_ref_audio=no_ref_audio, seed=seed)
+        elif sampler == "sample_tts":
+            generated, _ = model.sample_tts(cond=ref_mels, text=final_text_list, duration=total, lens=ref_len, steps=nfe_step,
+                                            sway_sampling_coef=sway_sampling_coef, no_ref_audio=no_ref_audio, seed=seed,
+                                            **(sampler_kwargs or {}))
+        else:
+            raise ValueError(f"unknown sampler {sampler!r}")
+        n_frames = [t - r for t, r in zip(total_mel_lens, ref_mel_lens)]
+        waves = vocoder.decode_varlen(generated, ref_len, total, max_frames=max(n_frames))  # [B, (max - 1) * hop]
+        rms = torch.stack([torch.as_tensor(r, dtype=torch.float32) for r in ref_rms_list]).to(dev)
+        # `if ref_rms < target_rms: wave = wave * ref_rms / target_rms` (eval_infer_batch.py:214-215), per row
+        scaled = waves * rms[:, None] / target_rms
+        waves = torch.where((rms < target_rms)[:, None], scaled, waves).cpu()
+        for i, utt in enumerate(utts):
+            w = waves[i: i + 1, : (n_frames[i] - 1) * HOP_LENGTH]
+            out.append(sink(utt, w, TARGET_SAMPLE_RATE) if sink is not None else (utt, w))
+    return out

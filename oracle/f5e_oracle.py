@@ -634,3 +634,25 @@ def get_inference_prompt(metainfo, speed=1.0, target_sample_rate=24000, hop_leng
     random.seed(666)
     random.shuffle(prompts_all)
     return prompts_all
+
+
+def eval_infer(dit: OracleDiT, vocos_sd, prompts_all, *, steps, cfg_strength=2.0, sway=-1.0, seed=None, target_rms=0.1):
+    """The loop of eval/eval_infer_batch.py:187-216 (one `sample` per batch, one vocoder call per utterance, loudness
+    gain); text_list entries are token-id lists here (the tokenizer is not on the path).  Returns {utt: wave [1, n]}."""
+    res = {}
+    for utts, ref_rms_list, ref_mels, ref_mel_lens, total_mel_lens, texts in prompts_all:
+        nt = max(len(t) for t in texts)
+        text = torch.full((len(texts), nt), -1, dtype=torch.long, device=dit.device)
+        for i, t in enumerate(texts):
+            text[i, : len(t)] = torch.tensor(t, dtype=torch.long)
+        ref_len = torch.tensor(ref_mel_lens, dtype=torch.long, device=dit.device)
+        total = torch.tensor(total_mel_lens, dtype=torch.long, device=dit.device)
+        generated, _ = cfm_sample(dit, ref_mels.to(dit.device), text, total, lens=ref_len, steps=steps,
+                                  cfg_strength=cfg_strength, sway_sampling_coef=sway, seed=seed)
+        for i, gen in enumerate(generated):
+            gen = gen[ref_mel_lens[i]: total_mel_lens[i], :].unsqueeze(0)
+            wave = vocos_decode(vocos_sd, gen.permute(0, 2, 1).to(torch.float32)).cpu()
+            if ref_rms_list[i] < target_rms:
+                wave = wave * ref_rms_list[i] / target_rms
+            res[utts[i]] = wave
+    return res

@@ -51,3 +51,22 @@ def test_crossfade_chain_properties():
     assert np.array_equal(out[-(12000 - 3600):], waves[3][3600:].astype(np.float64))
     assert np.array_equal(O.crossfade_chain(waves, 0.0), np.concatenate(waves))
     del cf
+
+
+def test_split_batches_covers_every_batch_once():
+    from f5e_tts_b200.evaluate import split_batches
+    rng = np.random.default_rng(1)
+    prompts = [(None, None, None, None, list(rng.integers(300, 1400, size=int(rng.integers(1, 17)))), None) for _ in range(37)]
+    for split in ("lpt", "reference"):
+        for world in (1, 2, 4, 8):
+            parts = [split_batches(prompts, r, world, split) for r in range(world)]
+            assert sorted(i for p in parts for i in p) == list(range(37))
+            assert parts == [split_batches(prompts, r, world, split) for r in range(world)]  # deterministic
+    # accelerate's split_between_processes: contiguous, first ranks one longer
+    assert split_batches(prompts, 0, 4, "reference") == list(range(0, 10))
+    assert split_batches(prompts, 3, 4, "reference") == list(range(28, 37))
+    # LPT balances the modelled cost
+    from f5e_tts_b200.dist import utterance_cost
+    cost = [sum(utterance_cost(d) for d in p[4]) for p in prompts]
+    loads = [sum(cost[i] for i in split_batches(prompts, r, 4, "lpt")) for r in range(4)]
+    assert max(loads) / (sum(loads) / 4) < 1.1

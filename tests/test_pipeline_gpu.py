@@ -128,7 +128,7 @@ def test_infer_batch_process_vs_oracle_and_batch1(cuda_dev):
     ids = lambda s: list(s.encode("utf-8"))  # noqa: E731
     o32 = O.OracleDiT(cfg, sd, torch.float32, cuda_dev)
     o16 = O.OracleDiT(cfg, sd, torch.bfloat16, cuda_dev)
-    vsd = {k: v.to(cuda_dev) for k, v in O.make_vocos_state_dict(4321).items()}
+    vsd = voc.state_dict()  # the oracle decodes with the product vocoder's weights
     args = (vsd, ref_audio.to(cuda_dev), sr, ids(rt), [ids(c) for c in chunks], [len(ids(c)) for c in chunks], len(ids(rt)))
     w32, m32 = O.long_form(o32, *args, steps=4, seed=11)
     w16, m16 = O.long_form(o16, *args, steps=4, seed=11)
@@ -138,3 +138,41 @@ def test_infer_batch_process_vs_oracle_and_batch1(cuda_dev):
     e_ref = np.linalg.norm(m16c - m32c) / np.linalg.norm(m32c)
     print(f"long-form mel: product-vs-fp32 {e_got:.3e}  oracle-bf16-vs-fp32 {e_ref:.3e}")
     assert e_got <= 2.0 * e_ref + 5e-3
+    w_got, w_ref = np.linalg.norm(wave - w32) / np.linalg.norm(w32), np.linalg.norm(w16 - w32) / np.linalg.norm(w32)
+    print(f"long-form wave (gain + cross-fade included): product-vs-fp32 {w_got:.3e}  oracle-bf16-vs-fp32 {w_ref:.3e}")
+    assert w_got <= 2.0 * w_ref + 2e-2
+
+
+def test_eval_loop_vs_oracle(cuda_dev):
+    """evaluate.infer_batches (batched decode, device-side gain, rank sharding) against the reference loop's restatement."""
+    from f5e_tts_b200 import evaluate as E
+    from f5e_tts_b200 import pipeline as P
+    from f5e_tts_b200.model import CFM, DiT
+    from f5e_tts_b200.vocos import Vocos
+    cfg = O.DiTConfig(dim=256, depth=2, heads=4, text_dim=256, conv_layers=2, text_num_embeds=256)
+    sd = {k: v.to(torch.bfloat16).float() for k, v in O.make_state_dict(cfg, 41).items()}
+    dit = DiT(dim=cfg.dim, depth=cfg.depth, heads=cfg.heads, ff_mult=cfg.ff_mult, mel_dim=100, text_num_embeds=256,
+              text_dim=256, conv_layers=2)
+    dit.load_state_dict(sd, strict=False)
+    model = CFM(dit).to(cuda_dev).to(torch.bfloat16)
+    voc = Vocos(seed=4321).to(cuda_dev)
+    meta = _metainfo(7, 9)
+    prompts = P.get_inference_prompt(meta, device=cuda_dev, infer_batch_size=1500, num_buckets=10, min_secs=1, max_secs=40)
+    kw = dict(nfe_step=4, cfg_strength=2.0, sway_sampling_coef=-1.0, seed=5)
+    # two "ranks" in one process: together they cover every utterance exactly once
+    got = dict(E.infer_batches(model, voc, prompts, rank=0, world=2, **kw) + E.infer_batches(model, voc, prompts, rank=1, world=2, **kw))
+    assert sorted(got) == sorted(m[0] for m in meta)
+    # oracle: same prompts, texts as UTF-8 byte ids (vocab_char_map None), fp32 and bf16
+    oprompts = [(u, [float(r) for r in rms], mels.cpu(), rl, tl, [list(t.encode("utf-8")) for t in txt])
+                for u, rms, mels, rl, tl, txt in prompts]
+    vsd = voc.state_dict()
+    r32 = O.eval_infer(O.OracleDiT(cfg, sd, torch.float32, cuda_dev), vsd, oprompts, steps=4, seed=5)
+    r16 = O.eval_infer(O.OracleDiT(cfg, sd, torch.bfloat16, cuda_dev), vsd, oprompts, steps=4, seed=5)
+    worst = []
+    for utt, w in got.items():
+        assert w.shape == r32[utt].shape and w.dtype == torch.float32  # lengths: exact
+        e_got, e_ref = rel_l2(w, r32[utt]), rel_l2(r16[utt], r32[utt])
+        print(f"{utt}: wave product-vs-fp32 {e_got:.3e}  oracle-bf16-vs-fp32 {e_ref:.3e}")
+        worst.append((e_got, e_ref, utt))
+    for e_got, e_ref, utt in worst:
+        assert e_got <= 2.0 * e_ref + 2e-2, utt

@@ -18,6 +18,7 @@ def main():
     ap.add_argument("--prompts", type=int, default=1088)
     ap.add_argument("--chunks", type=int, default=8)
     ap.add_argument("--cpu-sample", type=int, default=48)
+    ap.add_argument("--eval-batches", type=int, default=1000)
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     g = torch.Generator().manual_seed(0)
@@ -27,6 +28,11 @@ def main():
         wave = 0.05 * torch.randn(1, int(secs * 16000), generator=g)
         meta.append((f"u{i}", "reference transcript of the prompt audio.", (wave, 16000),
                      " " + "some generated words " * int(1 + 4 * torch.rand(1, generator=g).item()), None))
+    from bench import build_model
+    from f5e_tts_b200.vocos import Vocos
+    model, _ = build_model(dev)
+    model.store_trajectory = False
+    voc = Vocos(seed=4321).to(dev)
     kw = dict(infer_batch_size=16 * 1031, num_buckets=200, min_secs=3, max_secs=40)
     P.get_inference_prompt(meta[:64], device=dev, **kw)
     torch.cuda.synchronize()
@@ -43,12 +49,6 @@ def main():
                           cores=torch.get_num_threads(), note="host wall clock incl. H2D of the prompts and batching logic")))
 
     # long-form: chunks batched in one solve vs the reference's chunk-by-chunk loop (both through the product)
-    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)) + "/..")
-    from bench import build_model
-    from f5e_tts_b200.vocos import Vocos
-    model, _ = build_model(dev)
-    model.store_trajectory = False
-    voc = Vocos(seed=4321).to(dev)
     ref = (0.05 * torch.randn(1, 5 * 24000, generator=g), 24000)
     ref_text = "a reference transcript of about five seconds of speech, more or less."
     chunks = ["this is a chunk of generated text that is about as long as the chunker allows, one hundred and thirty bytes, "
@@ -62,6 +62,20 @@ def main():
         r = fn()
         torch.cuda.synchronize()
         return time.perf_counter() - t0, r
+
+    # evaluation set end to end on this GPU (BASELINE configs[3] shape: nfe 16), prompts from above
+    from f5e_tts_b200 import evaluate as E
+    sub = out[: a.eval_batches]
+    E.infer_batches(model, voc, sub[:1], nfe_step=16, seed=0)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    res = E.infer_batches(model, voc, sub, nfe_step=16, seed=0)
+    torch.cuda.synchronize()
+    t_e = time.perf_counter() - t0
+    gen_s = sum(w.shape[-1] for _, w in res) / 24000
+    print(json.dumps(dict(row="evaluate.infer_batches", batches=len(sub), utterances=len(res), nfe=16,
+                          generated_audio_s=round(gen_s, 1), seconds=round(t_e, 3), audio_s_per_s=round(gen_s / t_e, 1),
+                          note="host wall clock incl. per-batch D2H of the waveforms")))
 
     t_b, rb = timed(lambda: next(P.infer_batch_process(ref, ref_text, chunks, model, voc, **kwi)))
     t_s, _ = timed(lambda: [next(P.infer_batch_process(ref, ref_text, [c], model, voc, **kwi)) for c in chunks])
