@@ -148,14 +148,24 @@ class DiT(nn.Module):
         self.time_embed = _Holder(time_mlp=_seq({0: nn.Linear(256, dim), 2: nn.Linear(dim, dim)}))
         self.text_embed = _TextEmbedding(text_num_embeds, text_dim, conv_layers)
         in_dim = mel_dim * 2 + text_dim * (2 if self.use_ppg else 1)
+        self.ppg_transformer = False
         if self.use_ppg:
-            if ppg_config.get("use_transformer", False):
-                raise NotImplementedError("f5e_tts_b200: PPGEmbedding(use_transformer=True) is not implemented")
             P = self.ppg_dim = ppg_config["ppg_dim"]
-            self.ppg_embed = _Holder(ppg_proj=_seq({0: nn.Linear(P, P), 2: nn.Conv1d(P, P, 5, padding="same"),
-                                                    3: nn.BatchNorm1d(P), 6: nn.Conv1d(P, P, 5, padding="same"),
-                                                    7: nn.BatchNorm1d(P), 10: nn.Conv1d(P, P, 5, padding="same"),
-                                                    11: nn.BatchNorm1d(P), 15: nn.Linear(P, text_dim)}))
+            self.ppg_transformer = bool(ppg_config.get("use_transformer", False))
+            if self.ppg_transformer:  # dit.py:105-119; torch's modules are used as parameter containers only (same keys)
+                tc = ppg_config["transformer_config"]
+                if P % tc["nhead"] or P // tc["nhead"] != 64 or P % 256:
+                    raise NotImplementedError("f5e_tts_b200: the transformer PPG embedder needs ppg_dim % 256 == 0 and "
+                                              "ppg_dim / nhead == 64 (the attention kernel's head width)")
+                layer = nn.TransformerEncoderLayer(d_model=P, nhead=tc["nhead"], dim_feedforward=tc["dim_feedforward"],
+                                                   dropout=tc["dropout"], activation=F.gelu, batch_first=True)
+                self.ppg_embed = _Holder(ppg_proj=_seq({0: nn.TransformerEncoder(layer, num_layers=tc["num_layers"]),
+                                                        1: nn.Linear(P, text_dim)}))
+            else:
+                self.ppg_embed = _Holder(ppg_proj=_seq({0: nn.Linear(P, P), 2: nn.Conv1d(P, P, 5, padding="same"),
+                                                        3: nn.BatchNorm1d(P), 6: nn.Conv1d(P, P, 5, padding="same"),
+                                                        7: nn.BatchNorm1d(P), 10: nn.Conv1d(P, P, 5, padding="same"),
+                                                        11: nn.BatchNorm1d(P), 15: nn.Linear(P, text_dim)}))
         if self.use_codebook:
             from .quantizer import GumbelVectorQuantizer
             self.quantizer = GumbelVectorQuantizer(
@@ -283,7 +293,17 @@ class DiT(nn.Module):
                                           w2=bf(b.pwconv2.weight), b2=f32(b.pwconv2.bias)))
         else:
             P.pos = None
-        if self.use_ppg:
+        if self.use_ppg and self.ppg_transformer:
+            pp = self.ppg_embed.ppg_proj
+            P.ppg = dict(w1=bf(pp["1"].weight), b1=f32(pp["1"].bias), heads=pp["0"].layers[0].self_attn.num_heads, layers=[])
+            for ly in pp["0"].layers:
+                sa = ly.self_attn
+                P.ppg["layers"].append(dict(
+                    w_in=bf(sa.in_proj_weight), b_in=f32(sa.in_proj_bias), w_out=bf(sa.out_proj.weight), b_out=f32(sa.out_proj.bias),
+                    w_l1=bf(ly.linear1.weight), b_l1=f32(ly.linear1.bias), w_l2=bf(ly.linear2.weight), b_l2=f32(ly.linear2.bias),
+                    n1w=f32(ly.norm1.weight), n1b=f32(ly.norm1.bias), n2w=f32(ly.norm2.weight), n2b=f32(ly.norm2.bias),
+                    eps=ly.norm1.eps))
+        elif self.use_ppg:
             pp = self.ppg_embed.ppg_proj
             P.ppg = dict(w0=bf(pp["0"].weight), b0=f32(pp["0"].bias), w15=bf(pp["15"].weight), b15=f32(pp["15"].bias), convs=[])
             for ci, bi in (("2", "3"), ("6", "7"), ("10", "11")):
@@ -350,6 +370,17 @@ class DiT(nn.Module):
             ops.pack_cols(x.view(batch * seq_len, Pd).view(batch, seq_len * Pd)[:, : n * Pd], 0,
                           ppg[:, :n].reshape(batch, n * Pd).to(dev))
         rows = batch * seq_len
+        if self.ppg_transformer:  # post-norm nn.TransformerEncoderLayer, exact GELU, no padding mask (dit.py:105-119)
+            h = x.view(rows, Pd)
+            for ly in P.ppg["layers"]:
+                qkv = ops.gemm(h, ly["w_in"], bias=ly["b_in"])
+                a = ops.attention(qkv, P.ppg["heads"], n_pad=seq_len)
+                h = ops.gemm(a, ly["w_out"], bias=ly["b_out"], residual=h)
+                h = ops.norm_mod(h, ly["n1w"], ly["n1b"], plus_one=0.0, eps=ly["eps"])
+                f = ops.gemm(h, ly["w_l1"], bias=ly["b_l1"], act=_lib.ACT_GELU_ERF)
+                h = ops.gemm(f, ly["w_l2"], bias=ly["b_l2"], residual=h)
+                h = ops.norm_mod(h, ly["n2w"], ly["n2b"], plus_one=0.0, eps=ly["eps"])
+            return ops.gemm(h, P.ppg["w1"], bias=P.ppg["b1"]).view(batch, seq_len, self.text_dim)
         h = ops.gemm(x.view(rows, Pd), P.ppg["w0"], bias=P.ppg["b0"])
         for w, b in P.ppg["convs"]:
             u = ops.unfold_frames(h.view(batch, seq_len, Pd), 5)

@@ -44,6 +44,11 @@ class DiTConfig:
     use_codebook: bool = False
     cb_num_vars: int = 100
     cb_groups: int = 2
+    # PPGEmbedding(use_transformer=True) (dit.py:105-119): nn.TransformerEncoder over ppg_dim, then Linear -> text_dim
+    ppg_transformer: bool = False
+    ppg_nhead: int = 4
+    ppg_ff: int = 1024
+    ppg_layers: int = 2
 
     @property
     def in_dim(self) -> int:
@@ -93,7 +98,20 @@ def make_state_dict(cfg: DiTConfig, seed: int = 1234, device="cpu", zero_init_st
         sd[p + ".grn.gamma"] = 0.1 * torch.randn(1, 1, TD * 2, generator=g)  # reference inits zeros
         sd[p + ".grn.beta"] = 0.1 * torch.randn(1, 1, TD * 2, generator=g)
         lin(p + ".pwconv2", TD, TD * 2)
-    if cfg.use_ppg:
+    if cfg.use_ppg and cfg.ppg_transformer:
+        P = cfg.ppg_dim
+        for i in range(cfg.ppg_layers):
+            p = f"ppg_embed.ppg_proj.0.layers.{i}"
+            uni(p + ".self_attn.in_proj_weight", (3 * P, P), P)
+            uni(p + ".self_attn.in_proj_bias", (3 * P,), P)
+            lin(p + ".self_attn.out_proj", P, P)
+            lin(p + ".linear1", cfg.ppg_ff, P)
+            lin(p + ".linear2", P, cfg.ppg_ff)
+            for nm in ("norm1", "norm2"):
+                sd[p + f".{nm}.weight"] = 1 + 0.1 * torch.randn(P, generator=g)
+                sd[p + f".{nm}.bias"] = 0.1 * torch.randn(P, generator=g)
+        lin("ppg_embed.ppg_proj.1", TD, P)
+    elif cfg.use_ppg:
         P = cfg.ppg_dim
         lin("ppg_embed.ppg_proj.0", P, P)
         for ci, bi in ((2, 3), (6, 7), (10, 11)):
@@ -258,6 +276,18 @@ class OracleDiT:
             ppg = F.pad(ppg, (0, 0, 0, seq_len - ppg.shape[1]), value=0).to(self.dtype)
             if drop_ppg:
                 ppg = torch.zeros_like(ppg)
+        if cfg.ppg_transformer:  # nn.TransformerEncoderLayer, post-norm, exact GELU, eval mode, no padding mask (dit.py:105-119)
+            x, P, H = ppg, cfg.ppg_dim, cfg.ppg_nhead
+            B, N = x.shape[:2]
+            for i in range(cfg.ppg_layers):
+                p = f"ppg_embed.ppg_proj.0.layers.{i}"
+                qkv = F.linear(x, sd[p + ".self_attn.in_proj_weight"], sd[p + ".self_attn.in_proj_bias"])
+                q, k, v = (t.reshape(B, N, H, P // H).transpose(1, 2) for t in qkv.chunk(3, dim=-1))
+                a = F.scaled_dot_product_attention(q, k, v).transpose(1, 2).reshape(B, N, P)
+                x = F.layer_norm(x + _lin(sd, p + ".self_attn.out_proj", a), (P,), sd[p + ".norm1.weight"], sd[p + ".norm1.bias"], 1e-5)
+                f = _lin(sd, p + ".linear2", F.gelu(_lin(sd, p + ".linear1", x)))
+                x = F.layer_norm(x + f, (P,), sd[p + ".norm2.weight"], sd[p + ".norm2.bias"], 1e-5)
+            return _lin(sd, "ppg_embed.ppg_proj.1", x)
         h = _lin(sd, "ppg_embed.ppg_proj.0", ppg).transpose(1, 2)
         for ci, bi in ((2, 3), (6, 7), (10, 11)):
             h = F.conv1d(h, sd[f"ppg_embed.ppg_proj.{ci}.weight"], sd[f"ppg_embed.ppg_proj.{ci}.bias"], padding=2)

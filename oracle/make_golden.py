@@ -27,8 +27,9 @@ SMALL_PPG = O.DiTConfig(dim=256, depth=2, heads=4, text_dim=64, conv_layers=2, t
 
 
 def build_reference(cfg: O.DiTConfig, seed: int):
-    ppg_config = dict(use_ppg=cfg.use_ppg, ppg_dim=cfg.ppg_dim, use_transformer=False, transformer_config={},
-                      combined_cond_drop_prob=0.1)
+    ppg_config = dict(use_ppg=cfg.use_ppg, ppg_dim=cfg.ppg_dim, use_transformer=cfg.ppg_transformer,
+                      transformer_config=dict(nhead=cfg.ppg_nhead, dim_feedforward=cfg.ppg_ff, dropout=0.1,
+                                              num_layers=cfg.ppg_layers), combined_cond_drop_prob=0.1)
     cb_config = dict(use_codebook=cfg.use_codebook, num_vars=cfg.cb_num_vars, temp_start=2.0, temp_stop=0.5,
                      temp_decay=0.999, groups=cfg.cb_groups, combine_groups=False, weight_proj_depth=1,
                      weight_proj_factor=1)
@@ -199,5 +200,9 @@ if __name__ == "__main__":
     case_sample("sample_b2_ppg", SMALL_PPG, 2, 202, with_ppg=True)
     case_sample3("sample_tts_b2", SMALL_PPG, 2, 203, "tts")
     case_sample3("sample_vc_b2", SMALL_PPG, 2, 204, "vc")
+    SMALL_PPG_TR = O.DiTConfig(dim=256, depth=2, heads=4, text_dim=64, conv_layers=2, text_num_embeds=50,
+                               text_mask_padding=False, pe_attn_head=1, use_ppg=True, ppg_dim=32, ppg_transformer=True,
+                               ppg_nhead=2, ppg_ff=48, ppg_layers=2)
+    case_single_eval("dit_eval_small_ppg_transformer", SMALL_PPG_TR, 102)
     case_resample("resample")
     case_chunk_text("chunk_text")

@@ -4,6 +4,7 @@ import os
 import subprocess
 import sys
 
+import pytest
 import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -60,6 +61,24 @@ def test_state_dict_keys_match_reference_layout():
     assert all("num_batches_tracked" in k or "inv_freq" in k for k in missing), missing
     for k, v in sd.items():
         assert dit.state_dict()[k].shape == v.shape, k
+
+
+def test_state_dict_keys_transformer_ppg_embedder():
+    """PPGEmbedding(use_transformer=True) (dit.py:105-119): same keys as the reference's nn.TransformerEncoder; the oracle's
+    key layout is pinned by tests/golden/dit_eval_small_ppg_transformer.pt (loaded into the reference with strict keys)."""
+    from f5e_tts_b200.model import DiT
+    from oracle import f5e_oracle as O
+    cfg = O.DiTConfig(dim=512, depth=1, heads=8, text_dim=256, conv_layers=1, text_num_embeds=50, use_ppg=True, ppg_dim=256,
+                      ppg_transformer=True, ppg_nhead=4, ppg_ff=512, ppg_layers=2)
+    ppg = dict(use_ppg=True, ppg_dim=256, use_transformer=True,
+               transformer_config=dict(nhead=4, dim_feedforward=512, dropout=0.1, num_layers=2))
+    dit = DiT(dim=512, depth=1, heads=8, ff_mult=2, text_dim=256, conv_layers=1, text_num_embeds=50, ppg_config=ppg)
+    sd = O.make_state_dict(cfg, 1)
+    missing, unexpected = dit.load_state_dict(sd, strict=False)
+    assert not unexpected and all("inv_freq" in k for k in missing), (missing, unexpected)
+    with pytest.raises(NotImplementedError):  # head width other than 64 is not supported by the attention kernel
+        DiT(dim=512, depth=1, heads=8, ppg_config=dict(use_ppg=True, ppg_dim=256, use_transformer=True,
+                                                       transformer_config=dict(nhead=8, dim_feedforward=512, dropout=0.1, num_layers=1)))
 
 
 def test_vocos_state_dict_layout():

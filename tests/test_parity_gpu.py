@@ -23,7 +23,8 @@ def build(cfg, seed, dev):
     from f5e_tts_b200.model import CFM, DiT
     sd = O.make_state_dict(cfg, seed)
     sd = {k: v.to(torch.bfloat16).float() for k, v in sd.items()}  # bf16-representable weights on both sides
-    ppg_config = dict(use_ppg=cfg.use_ppg, ppg_dim=cfg.ppg_dim, use_transformer=False, transformer_config={})
+    ppg_config = dict(use_ppg=cfg.use_ppg, ppg_dim=cfg.ppg_dim, use_transformer=cfg.ppg_transformer,
+                      transformer_config=dict(nhead=cfg.ppg_nhead, dim_feedforward=cfg.ppg_ff, dropout=0.1, num_layers=cfg.ppg_layers))
     cb_config = dict(use_codebook=cfg.use_codebook, num_vars=cfg.cb_num_vars, temp_start=2.0, temp_stop=0.5,
                      temp_decay=0.999, groups=cfg.cb_groups, combine_groups=False, weight_proj_depth=1, weight_proj_factor=1)
     dit = DiT(dim=cfg.dim, depth=cfg.depth, heads=cfg.heads, ff_mult=cfg.ff_mult, mel_dim=cfg.mel_dim,
@@ -50,10 +51,14 @@ SMALL = O.DiTConfig(dim=256, depth=2, heads=4, text_dim=256, conv_layers=2, text
 SMALL_PPG = O.DiTConfig(dim=768, depth=2, heads=12, text_dim=256, conv_layers=2, text_num_embeds=50, text_mask_padding=False,
                         pe_attn_head=1, use_ppg=True, ppg_dim=64)
 BASE2 = O.DiTConfig(depth=2)  # F5TTS_v1_Base widths, 2 layers
+# PPGEmbedding(use_transformer=True) (reference dit.py:105-119): nn.TransformerEncoder over the PPG stream
+PPG_TR = O.DiTConfig(dim=512, depth=2, heads=8, text_dim=256, conv_layers=2, text_num_embeds=50, text_mask_padding=False,
+                     pe_attn_head=1, use_ppg=True, ppg_dim=256, ppg_transformer=True, ppg_nhead=4, ppg_ff=512, ppg_layers=2)
 
 
 @pytest.mark.parametrize("cfg,B,N,lens", [(SMALL, 1, 200, None), (SMALL, 3, 333, [333, 150, 290]),
-                                           (SMALL_PPG, 2, 260, [260, 131]), (BASE2, 2, 300, [300, 177])])
+                                           (SMALL_PPG, 2, 260, [260, 131]), (BASE2, 2, 300, [300, 177]),
+                                           (PPG_TR, 2, 260, [260, 131])])
 def test_dit_eval_vs_oracle(cuda_dev, cfg, B, N, lens):
     model, sd = build(cfg, 7, cuda_dev)
     x, cond, text, ppg = inputs(cfg, B, N, 8, cuda_dev, cfg.use_ppg)
@@ -73,7 +78,7 @@ def test_dit_eval_vs_oracle(cuda_dev, cfg, B, N, lens):
             assert e_got <= K_TOL * e_ref + 5e-3, (i, e_got, e_ref)
 
 
-@pytest.mark.parametrize("cfg,B", [(SMALL, 1), (SMALL, 3), (SMALL_PPG, 2)])
+@pytest.mark.parametrize("cfg,B", [(SMALL, 1), (SMALL, 3), (SMALL_PPG, 2), (PPG_TR, 2)])
 def test_cfm_sample_vs_oracle(cuda_dev, cfg, B):
     model, sd = build(cfg, 17, cuda_dev)
     g = torch.Generator().manual_seed(18)
