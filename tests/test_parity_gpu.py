@@ -58,7 +58,8 @@ PPG_TR = O.DiTConfig(dim=512, depth=2, heads=8, text_dim=256, conv_layers=2, tex
 
 @pytest.mark.parametrize("cfg,B,N,lens", [(SMALL, 1, 200, None), (SMALL, 3, 333, [333, 150, 290]),
                                            (SMALL_PPG, 2, 260, [260, 131]), (BASE2, 2, 300, [300, 177]),
-                                           (PPG_TR, 2, 260, [260, 131])])
+                                           (PPG_TR, 2, 260, [260, 131]),
+                                           (BASE2, 2, 2812, [2812, 1903])])  # BASELINE configs[4] length (30 s utterances)
 def test_dit_eval_vs_oracle(cuda_dev, cfg, B, N, lens):
     model, sd = build(cfg, 7, cuda_dev)
     x, cond, text, ppg = inputs(cfg, B, N, 8, cuda_dev, cfg.use_ppg)
