@@ -191,3 +191,37 @@ def test_sample_vc_needs_unmasked_text_embedder(cuda_dev):
     model, _ = build(SMALL, 7, cuda_dev)  # text_mask_padding=True: the reference raises on text=None
     with pytest.raises(ValueError):
         model.sample_vc(torch.randn(1, 30, 100, device=cuda_dev), None, 80)
+
+
+def test_config3_f5e_small_ppg_batch32(cuda_dev):
+    """BASELINE configs[2]: the PPG-conditioned + VQ-codebook F5E "Small" variant (configs/example.yaml: dim 768, depth 18,
+    12 heads, pe_attn_head 1, text_mask_padding off, ppg 256, codebook 2 x 100), nfe 16, batch 32: `sample_vc` against the
+    oracle under the bf16 bar, and the codebook indices of the model's own text / PPG embeddings bit-exact."""
+    cfg = O.F5E_SMALL_PPG
+    model, sd = build(cfg, 77, cuda_dev)
+    g = torch.Generator().manual_seed(78)
+    B = 32
+    ref_len = torch.randint(90, 200, (B,), generator=g).to(cuda_dev)
+    dur = torch.randint(300, 620, (B,), generator=g).to(cuda_dev)
+    cond = torch.randn(B, int(ref_len.max()), cfg.mel_dim, generator=g).to(cuda_dev)
+    ppg = torch.randn(B, 640, cfg.ppg_dim, generator=g).to(cuda_dev)
+    kw = dict(steps=16, sway_sampling_coef=-1.0)
+    o32 = O.OracleDiT(cfg, sd, torch.float32, cuda_dev)
+    o16 = O.OracleDiT(cfg, sd, torch.bfloat16, cuda_dev)
+    okw = dict(mode="vc", alpha_spk=2.5, alpha_cont=3.0, **kw)
+    out16, traj16, aux = O.cfm_sample(o16, cond, None, dur, ppg=ppg, lens=ref_len, seed=3, return_aux=True, **okw)
+    out32, traj32 = O.cfm_sample(o32, cond.bfloat16().float(), None, dur, ppg=ppg, lens=ref_len, y0=aux["y0"].float(), **okw)
+    got, traj = model.sample_vc(cond, ppg, dur, lens=ref_len, seed=3, alpha_spk=2.5, alpha_ppg=3.0, **kw)
+    assert torch.equal(traj[0], aux["y0"]) and torch.equal(aux["duration"], dur)
+    worst = 0.0
+    for i in range(B):
+        L = int(dur[i])
+        e_got, e_ref = rel_l2(traj[-1][i, :L], traj32[-1][i, :L]), rel_l2(traj16[-1][i, :L], traj32[-1][i, :L])
+        worst = max(worst, e_got / (K_TOL * e_ref + 5e-3))
+        assert e_got <= K_TOL * e_ref + 5e-3, (i, e_got, e_ref)
+    print(f"config 3: worst product error / allowed = {worst:.2f}")
+    # codebook: indices of the PPG embeddings the oracle computes in fp32, quantised by the product's kernel: bit exact
+    emb = o32.ppg_embed(ppg, 640, False, B)  # [B, 640, 512] fp32
+    ref = O.vq_forward(sd, emb.cpu(), groups=cfg.cb_groups, num_vars=cfg.cb_num_vars)
+    xq, tg = model.transformer.quantizer.forward_idx(emb)
+    assert torch.equal(tg.cpu(), ref["targets"])
