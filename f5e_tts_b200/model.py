@@ -14,6 +14,7 @@ from __future__ import annotations
 import ctypes as C
 import math
 import os
+import threading
 
 import torch
 import torch.nn.functional as F
@@ -21,6 +22,8 @@ from torch import nn
 
 from . import _lib, ops
 from ._lib import check, ptr, stream_ptr
+
+_SOLVE_LOCK = threading.RLock()
 
 
 # ---- ctypes mirrors of include/f5e_b200.h ------------------------------------------------------------
@@ -530,8 +533,14 @@ class CFM(nn.Module):
                            sway_sampling_coef=sway_sampling_coef, seed=seed, max_duration=max_duration, vocoder=vocoder,
                            no_ref_audio=no_ref_audio, duplicate_test=duplicate_test, t_inter=t_inter, edit_mask=edit_mask)
 
-    def _solve(self, cond, text, ppg, duration, branches, guidance, *, lens, steps, sway_sampling_coef, seed,
-               max_duration, vocoder, no_ref_audio, duplicate_test, t_inter, edit_mask):
+    def _solve(self, cond, text, ppg, duration, branches, guidance, **kw):
+        # The reference's long-form caller runs `model.sample` from a ThreadPoolExecutor (utils_infer.py:503-515); the
+        # DiT workspace (plan, caches, CUDA graph) is one per model, so concurrent callers take turns here.
+        with _SOLVE_LOCK:
+            return self._solve_locked(cond, text, ppg, duration, branches, guidance, **kw)
+
+    def _solve_locked(self, cond, text, ppg, duration, branches, guidance, *, lens, steps, sway_sampling_coef, seed,
+                      max_duration, vocoder, no_ref_audio, duplicate_test, t_inter, edit_mask):
         """The part the three samplers of the reference share line for line (cfm.py:119-164 + 187-223, 250-296 + 319-346,
         374-428 + 449-482).  `branches` = (drop_audio_cond, drop_text, drop_ppg) of every stacked evaluation."""
         self.eval()

@@ -225,3 +225,29 @@ def test_config3_f5e_small_ppg_batch32(cuda_dev):
     ref = O.vq_forward(sd, emb.cpu(), groups=cfg.cb_groups, num_vars=cfg.cb_num_vars)
     xq, tg = model.transformer.quantizer.forward_idx(emb)
     assert torch.equal(tg.cpu(), ref["targets"])
+
+
+def test_concurrent_callers_take_turns(cuda_dev):
+    """The reference's long-form loop calls model.sample from a ThreadPoolExecutor (utils_infer.py:503-515): concurrent
+    callers of ONE model must each get the bits a lone caller gets (different shapes, so a shared workspace would show)."""
+    from concurrent.futures import ThreadPoolExecutor
+    model, _ = build(SMALL, 17, cuda_dev)
+    g = torch.Generator().manual_seed(44)
+    jobs = []
+    for i in range(6):
+        n_ref, dur = 40 + 7 * i, 150 + 31 * i
+        cond = torch.randn(1, n_ref, SMALL.mel_dim, generator=g).to(cuda_dev)
+        text = torch.randint(0, SMALL.text_num_embeds, (1, 20 + i), generator=g).to(cuda_dev)
+        jobs.append((cond, text, dur))
+
+    def run(j):
+        torch.cuda.set_device(cuda_dev)
+        out, _ = model.sample(j[0], j[1], None, j[2], steps=4, cfg_strength=2.0, sway_sampling_coef=-1.0, seed=5)
+        torch.cuda.synchronize()
+        return out
+
+    alone = [run(j) for j in jobs]
+    with ThreadPoolExecutor(max_workers=4) as ex:
+        together = list(ex.map(run, jobs))
+    for a, b in zip(alone, together):
+        assert torch.equal(a, b)
