@@ -286,6 +286,20 @@ int f5e_melspec(const float* wav, int64_t ld_wav, int32_t batch, int32_t n_sampl
                 const float* twiddles, const float* fb_t, const int32_t* fb_lo, const int32_t* fb_hi, int32_t n_mels,
                 float* out, void* stream);
 
+/* Front end of the PPG extractor: kaldiFbank.forward (ppg/wenet/dataset/feats.py:49-83) = wave * 2^15 ->
+ * torchaudio.compliance.kaldi.fbank(num_mel_bins 80, frame_length 25, frame_shift 10, dither 0, energy_floor 0) and,
+ * optionally fused, GlobalCMVN (ppg/wenet/transformer/cmvn.py:9-47; encoder.py:171-172): (x - mean) * istd.
+ * wav fp32 [batch, n_max] (row stride ld_wav), lens[b] valid samples (NULL: n_max).  Per utterance
+ * T = 1 + (len - win) / shift frames (snip_edges; 0 if len < win): DC removal, pre-emphasis, window[win] (povey, built
+ * by the caller), zero pad to 512, |rFFT|^2, fb_t [n_mels, 257] mel banks (non-zero bins [fb_lo, fb_hi) per bank),
+ * log(max(., FLT_EPSILON)).  twiddles: float2[256] = exp(-2 pi i j / 512).  out fp32 [batch, t_max, n_mels] (utterance
+ * stride ld_out); frames >= T are zeros.  cmvn_mean / cmvn_istd: [n_mels] or both NULL. */
+int f5e_kaldi_fbank(const float* wav, int64_t ld_wav, const int32_t* lens, int32_t batch, int32_t n_max, float scale,
+                    float preemph, int32_t win, int32_t shift, const float* window, const float* twiddles,
+                    const float* fb_t, const int32_t* fb_lo, const int32_t* fb_hi, int32_t n_mels,
+                    const float* cmvn_mean, const float* cmvn_istd, float* out, int64_t ld_out, int32_t t_max,
+                    void* stream);
+
 /* Vocos ISTFTHead after its Linear (published vocos architecture; in-tree corroboration
  * runtime/triton_trtllm/scripts/export_vocoder_to_onnx.py:45-59, scripts/conv_stft.py:193-234):
  * spec fp32 [batch, t_pad, ld_spec] rows = (log-magnitude[513] | phase[513]); frames >= n_frames[b] ignored (NULL: all).
