@@ -190,6 +190,38 @@ def case_chunk_text(name):
     print(f"[{name}] {len(rows)} cases")
 
 
+def case_ppg_conformer(name):
+    """The reference's own wenet ConformerEncoder (ppg/wenet/transformer/encoder.py:403-495) + the content Linear of
+    ASRModel (asr_model.py:78-79, 241), built the way init_asr_model does (asr_model.py:814-836; the decoder / CTC heads
+    are not on the extract path) with random weights, on the reference's kaldiFbank features of seeded noise."""
+    from f5_tts.ppg.wenet.dataset.feats import kaldiFbank
+    from f5_tts.ppg.wenet.transformer.cmvn import GlobalCMVN
+    from f5_tts.ppg.wenet.transformer.encoder import ConformerEncoder
+    from oracle import ppg_oracle as PO
+    cfg = PO.ConformerConfig(blocks=3)
+    sd = PO.make_conformer_state_dict(cfg, seed=99)
+    enc = ConformerEncoder(cfg.input_dim, global_cmvn=GlobalCMVN(sd["encoder.global_cmvn.mean"], sd["encoder.global_cmvn.istd"]),
+                           output_size=cfg.dim, attention_heads=cfg.heads, linear_units=cfg.ffn, num_blocks=cfg.blocks,
+                           input_layer="conv2d", cnn_module_kernel=cfg.kernel).eval()
+    esd = {k[len("encoder."):]: v for k, v in sd.items() if k.startswith("encoder.")}
+    missing, unexpected = enc.load_state_dict(esd, strict=False)
+    missing = [k for k in missing if "num_batches_tracked" not in k and "linear_xs_embs" not in k and "concat_linear" not in k]
+    assert not missing and not unexpected, (missing, unexpected)
+    linear = torch.nn.Linear(cfg.dim, cfg.dim)
+    linear.load_state_dict({"weight": sd["linear.weight"], "bias": sd["linear.bias"]})
+    g = torch.Generator().manual_seed(31)
+    wave = 0.1 * torch.randn(1, 20000, generator=g) * torch.linspace(0.2, 1.0, 20000)
+    with torch.no_grad():
+        feats, feats_len = kaldiFbank().eval()(wave)
+        out, mask = enc(feats, feats_len, embs=None, decoding_chunk_size=-1)
+        ref = linear(out)[0]
+    got_feats = PO.kaldi_fbank(wave[0])
+    got = PO.conformer_extract(cfg, sd, got_feats)
+    print(f"{name}: fbank max abs {float((got_feats - feats[0]).abs().max()):.2e}; extract rel-L2 {rel(got, ref):.2e} "
+          f"shape {tuple(ref.shape)} mask frames {int(mask.sum())}")
+    torch.save(dict(blocks=cfg.blocks, seed=99, wave=wave[0], feats=feats[0], ppg=ref), os.path.join(OUT, name + ".pt"))
+
+
 if __name__ == "__main__":
     case_mel("melspec")
     case_vq("vq")
@@ -206,3 +238,4 @@ if __name__ == "__main__":
     case_single_eval("dit_eval_small_ppg_transformer", SMALL_PPG_TR, 102)
     case_resample("resample")
     case_chunk_text("chunk_text")
+    case_ppg_conformer("ppg_conformer")

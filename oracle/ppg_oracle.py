@@ -65,3 +65,145 @@ def kaldi_fbank(wave: torch.Tensor, sample_rate=16000, n_mels=80, frame_length_m
 def global_cmvn(x: torch.Tensor, mean: torch.Tensor, istd: torch.Tensor) -> torch.Tensor:
     """cmvn.py:34-47."""
     return (x - mean) * istd
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Conformer encoder (non-streaming, eval) + content head: ASRModel.extract (asr_model.py:222-244)
+# ---------------------------------------------------------------------------------------------------------------
+from dataclasses import dataclass  # noqa: E402
+
+
+@dataclass
+class ConformerConfig:
+    """encoder_conf of the PPG model.  train.yaml is not in the tree: these are the constructor defaults of
+    ConformerEncoder (encoder.py:405-433) with input_layer "conv2d" (= Conv2dSubsampling2, the 20 ms PPG frame of
+    ppg_model.py:12, 66) and 12 blocks."""
+    input_dim: int = 80
+    dim: int = 256
+    heads: int = 4
+    ffn: int = 2048
+    blocks: int = 12
+    kernel: int = 15
+    cmvn: bool = True
+
+
+def make_conformer_state_dict(cfg: ConformerConfig, seed: int = 99) -> dict:
+    """Random weights under the reference's own state_dict keys (ASRModel: `encoder.*`, `linear.*`)."""
+    g = torch.Generator().manual_seed(seed)
+    r = lambda *s, std=1.0: torch.randn(*s, generator=g) * std
+    d, f, sd = cfg.dim, cfg.ffn, {}
+    fdim = (cfg.input_dim - 1) // 2
+
+    def lin(name, o, i, bias=True):
+        sd[name + ".weight"] = r(o, i, std=i ** -0.5)
+        if bias:
+            sd[name + ".bias"] = r(o, std=0.1)
+
+    def ln(name):
+        sd[name + ".weight"] = 1.0 + r(d, std=0.1)
+        sd[name + ".bias"] = r(d, std=0.1)
+
+    if cfg.cmvn:
+        sd["encoder.global_cmvn.mean"] = 10.0 + r(cfg.input_dim)
+        sd["encoder.global_cmvn.istd"] = 0.3 + 0.1 * torch.rand(cfg.input_dim, generator=g)
+    sd["encoder.embed.conv.0.weight"] = r(d, 1, 3, 3, std=1.0 / 3.0)
+    sd["encoder.embed.conv.0.bias"] = r(d, std=0.1)
+    lin("encoder.embed.out.0", d, d * fdim)
+    for i in range(cfg.blocks):
+        p = f"encoder.encoders.{i}."
+        for ff in ("feed_forward_macaron", "feed_forward"):
+            lin(p + ff + ".w_1", f, d)
+            lin(p + ff + ".w_2", d, f)
+        for nm in ("linear_q", "linear_k", "linear_v", "linear_out"):
+            lin(p + "self_attn." + nm, d, d)
+        lin(p + "self_attn.linear_pos", d, d, bias=False)
+        sd[p + "self_attn.pos_bias_u"] = r(cfg.heads, d // cfg.heads, std=0.3)
+        sd[p + "self_attn.pos_bias_v"] = r(cfg.heads, d // cfg.heads, std=0.3)
+        sd[p + "conv_module.pointwise_conv1.weight"] = r(2 * d, d, 1, std=d ** -0.5)
+        sd[p + "conv_module.pointwise_conv1.bias"] = r(2 * d, std=0.1)
+        sd[p + "conv_module.depthwise_conv.weight"] = r(d, 1, cfg.kernel, std=cfg.kernel ** -0.5)
+        sd[p + "conv_module.depthwise_conv.bias"] = r(d, std=0.1)
+        sd[p + "conv_module.norm.weight"] = 1.0 + r(d, std=0.1)
+        sd[p + "conv_module.norm.bias"] = r(d, std=0.1)
+        sd[p + "conv_module.norm.running_mean"] = r(d, std=0.1)
+        sd[p + "conv_module.norm.running_var"] = 0.5 + torch.rand(d, generator=g)
+        sd[p + "conv_module.pointwise_conv2.weight"] = r(d, d, 1, std=d ** -0.5)
+        sd[p + "conv_module.pointwise_conv2.bias"] = r(d, std=0.1)
+        for nm in ("norm_ff", "norm_mha", "norm_ff_macaron", "norm_conv", "norm_final"):
+            ln(p + nm)
+    ln("encoder.after_norm")
+    lin("linear", d, d)
+    return sd
+
+
+def rel_pos_table(n: int, d: int) -> torch.Tensor:
+    """embedding.py:37-43: pe[pos, 2i] = sin(pos * w_i), pe[pos, 2i+1] = cos(pos * w_i) in fp32."""
+    pos = torch.arange(0, n, dtype=torch.float32).unsqueeze(1)
+    div = torch.exp(torch.arange(0, d, 2, dtype=torch.float32) * -(math.log(10000.0) / d))
+    pe = torch.zeros(n, d)
+    pe[:, 0::2], pe[:, 1::2] = torch.sin(pos * div), torch.cos(pos * div)
+    return pe
+
+
+def conformer_extract(cfg: ConformerConfig, sd: dict, feats: torch.Tensor, dtype=torch.float32) -> torch.Tensor:
+    """ONE utterance: feats [T, input_dim] fp32 (kaldi fbank, before CMVN) -> content embedding [T', dim], T' = (T - 1) // 2.
+    Every Linear / conv / LayerNorm runs in `dtype` (fp32: the reference; bf16: the precision class of the product)."""
+    W = lambda k: sd[k].to(device=feats.device, dtype=dtype)
+    d, H = cfg.dim, cfg.heads
+    dk = d // H
+    x = feats.float()
+    if cfg.cmvn:
+        x = (x - sd["encoder.global_cmvn.mean"].to(x.device)) * sd["encoder.global_cmvn.istd"].to(x.device)  # cmvn.py:34-47
+    # Conv2dSubsampling2 (subsampling.py:81-119): Conv2d(1, d, 3, stride 2) + ReLU over (time, freq), Linear over (channel, freq)
+    x = x.to(dtype)[None, None]
+    x = F.relu(F.conv2d(x, W("encoder.embed.conv.0.weight"), W("encoder.embed.conv.0.bias"), stride=2))
+    _, c, t, f = x.shape
+    x = F.linear(x.transpose(1, 2).reshape(1, t, c * f), W("encoder.embed.out.0.weight"), W("encoder.embed.out.0.bias"))[0]
+    x = x * math.sqrt(d)  # RelPositionalEncoding.forward (embedding.py:107-111); dropout off
+    pos = rel_pos_table(t, d).to(device=x.device, dtype=dtype)
+    ln = lambda v, name: F.layer_norm(v, (d,), W(name + ".weight"), W(name + ".bias"), 1e-5)
+    swish = lambda v: v * torch.sigmoid(v)
+    for i in range(cfg.blocks):
+        p = f"encoder.encoders.{i}."
+        # encoder_layer.py:206-213 macaron feed-forward, ff_scale 0.5
+        h = ln(x, p + "norm_ff_macaron")
+        h = F.linear(swish(F.linear(h, W(p + "feed_forward_macaron.w_1.weight"), W(p + "feed_forward_macaron.w_1.bias"))),
+                     W(p + "feed_forward_macaron.w_2.weight"), W(p + "feed_forward_macaron.w_2.bias"))
+        x = x + 0.5 * h
+        # :216-236 rel-pos self attention (attention.py:179-222: no rel_shift; scores = ((q+u) k^T + (q+v) p^T) / sqrt(dk))
+        h = ln(x, p + "norm_mha")
+        q = F.linear(h, W(p + "self_attn.linear_q.weight"), W(p + "self_attn.linear_q.bias")).view(t, H, dk)
+        k = F.linear(h, W(p + "self_attn.linear_k.weight"), W(p + "self_attn.linear_k.bias")).view(t, H, dk)
+        v = F.linear(h, W(p + "self_attn.linear_v.weight"), W(p + "self_attn.linear_v.bias")).view(t, H, dk)
+        pp = F.linear(pos, W(p + "self_attn.linear_pos.weight")).view(t, H, dk)
+        qu = (q + W(p + "self_attn.pos_bias_u")).transpose(0, 1)
+        qv = (q + W(p + "self_attn.pos_bias_v")).transpose(0, 1)
+        scores = (qu @ k.permute(1, 2, 0) + qv @ pp.permute(1, 2, 0)) / math.sqrt(dk)
+        a = torch.softmax(scores.float(), dim=-1).to(dtype) @ v.transpose(0, 1)
+        a = a.transpose(0, 1).reshape(t, d)
+        x = x + F.linear(a, W(p + "self_attn.linear_out.weight"), W(p + "self_attn.linear_out.bias"))
+        # :243-248 convolution module (convolution.py:99-134): pointwise -> GLU -> depthwise k -> BatchNorm(eval) -> swish -> pointwise
+        h = ln(x, p + "norm_conv").t()[None]
+        h = F.glu(F.conv1d(h, W(p + "conv_module.pointwise_conv1.weight"), W(p + "conv_module.pointwise_conv1.bias")), dim=1)
+        h = F.conv1d(h, W(p + "conv_module.depthwise_conv.weight"), W(p + "conv_module.depthwise_conv.bias"),
+                     padding=(cfg.kernel - 1) // 2, groups=d)
+        h = F.batch_norm(h, W(p + "conv_module.norm.running_mean"), W(p + "conv_module.norm.running_var"),
+                         W(p + "conv_module.norm.weight"), W(p + "conv_module.norm.bias"), False, 0.0, 1e-5)
+        h = F.conv1d(swish(h), W(p + "conv_module.pointwise_conv2.weight"), W(p + "conv_module.pointwise_conv2.bias"))
+        x = x + h[0].t()
+        # :254-263 feed-forward, final norm
+        h = ln(x, p + "norm_ff")
+        h = F.linear(swish(F.linear(h, W(p + "feed_forward.w_1.weight"), W(p + "feed_forward.w_1.bias"))),
+                     W(p + "feed_forward.w_2.weight"), W(p + "feed_forward.w_2.bias"))
+        x = ln(x + 0.5 * h, p + "norm_final")
+    x = ln(x, "encoder.after_norm")  # encoder.py:203-204
+    return F.linear(x, W("linear.weight"), W("linear.bias")).float()  # asr_model.py:241
+
+
+def audio_to_ppg(cfg: ConformerConfig, sd: dict, wave16k: torch.Tensor, dtype=torch.float32):
+    """ppg_model.py:147-168 (output_type "ppg") for one 16 kHz utterance: -> (ppg [T', dim], true_len)."""
+    feats = kaldi_fbank(wave16k)
+    ppg = conformer_extract(cfg, sd, feats, dtype)
+    true_len = min(int(feats.shape[0] / 2), ppg.shape[0])  # :139-141 (ppg_frame_length 20 / mel_f_shift 10)
+    ppg[true_len:] = 0.0
+    return ppg, true_len

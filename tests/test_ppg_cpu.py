@@ -45,3 +45,19 @@ def test_lengths_and_mask():
     lens = torch.tensor([5, 3, 2])
     assert make_pad_mask(lens).tolist() == [[False] * 5, [False] * 3 + [True] * 2, [False] * 2 + [True] * 3]
     assert ppg_true_len(torch.tensor([98, 99, 301]), 120).tolist() == [49, 49, 120]
+
+
+def test_oracle_conformer_matches_reference_golden():
+    """tests/golden/ppg_conformer.pt: the reference's kaldiFbank + wenet ConformerEncoder + content Linear, run in the
+    build container by oracle/make_golden.py (case_ppg_conformer) with the same seeded weights."""
+    fx = torch.load(os.path.join(os.path.dirname(__file__), "golden", "ppg_conformer.pt"))
+    cfg = PO.ConformerConfig(blocks=fx["blocks"])
+    sd = PO.make_conformer_state_dict(cfg, seed=fx["seed"])
+    feats = PO.kaldi_fbank(fx["wave"])
+    assert (feats - fx["feats"]).abs().max().item() < 1e-4
+    got = PO.conformer_extract(cfg, sd, fx["feats"])
+    assert got.shape == fx["ppg"].shape == ((feats.shape[0] - 1) // 2, cfg.dim)
+    rel = ((got - fx["ppg"]).norm() / fx["ppg"].norm()).item()
+    assert rel < 1e-5, rel
+    ppg, n = PO.audio_to_ppg(cfg, sd, fx["wave"])
+    assert n == got.shape[0] and ppg.shape == got.shape
