@@ -65,10 +65,13 @@ __device__ __forceinline__ bool att_decode(int w, int qtiles, int heads, const i
   return it.q0 < it.klen;
 }
 
+// KEY_BIAS: scores get key_bias[(sample * heads + head) * ld_bias + key] added BEFORE the scale (the position term of the
+// Conformer's rel-pos attention, see conformer.cu); ld_bias covers whole 128-key blocks.
+template <bool KEY_BIAS>
 __global__ void __launch_bounds__(ATT_THREADS, 2)
 attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __restrict__ out, int ldo,
                  const int* __restrict__ klen_ptr, const int* __restrict__ row_start, int n_pad, int inner, int heads,
-                 int qtiles, int total_items, float scale_log2) {
+                 int qtiles, int total_items, float scale_log2, const float* __restrict__ key_bias, int ld_bias) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + ATT_SMEM_BAR);
@@ -213,6 +216,18 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __res
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(s_free);  // S_b is in registers: the next QK may overwrite the TMEM columns now
+        if constexpr (KEY_BIAS) {
+          const float4* kb = reinterpret_cast<const float4*>(key_bias + ((size_t)it.sample * heads + it.head) * ld_bias +
+                                                             (size_t)j * ATT_BN);
+#pragma unroll
+          for (int i = 0; i < ATT_BN / 4; ++i) {
+            const float4 v4 = __ldg(kb + i);
+            s[4 * i] += v4.x;
+            s[4 * i + 1] += v4.y;
+            s[4 * i + 2] += v4.z;
+            s[4 * i + 3] += v4.w;
+          }
+        }
         if (kvalid < ATT_BN) {  // last key block of the sample only; kept a real (warp-uniform) branch
 #pragma unroll
           for (int i = 0; i < ATT_BN; ++i)
@@ -311,16 +326,21 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __res
 }
 
 int attention_configure() {
-  F5E_CUDA_CHECK(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM_TOTAL));
+  F5E_CUDA_CHECK(cudaFuncSetAttribute(attention_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM_TOTAL));
+  F5E_CUDA_CHECK(cudaFuncSetAttribute(attention_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM_TOTAL));
   return 0;
 }
 
 int attention(cudaStream_t st, const __nv_bfloat16* qkv, int ld_qkv, __nv_bfloat16* out, int ldo, const int* klen,
-              int samples, int n_pad, int heads, float scale, const int* row_start, int total_rows) {
+              int samples, int n_pad, int heads, float scale, const int* row_start, int total_rows, const float* key_bias,
+              int ld_bias) {
   { int rc0 = ensure_configured(); if (rc0) return rc0; }
   F5E_REQUIRE(samples > 0 && n_pad > 0 && heads > 0, "attention: empty problem");
   F5E_REQUIRE(ldo % 8 == 0, "attention: ldo must be a multiple of 8");
   F5E_REQUIRE(row_start == nullptr || (klen != nullptr && total_rows > 0), "attention: packed rows need klen and total_rows");
+  F5E_REQUIRE(key_bias == nullptr || (row_start == nullptr && ld_bias % 4 == 0 && ld_bias >= (n_pad + ATT_BN - 1) / ATT_BN * ATT_BN &&
+                                      (reinterpret_cast<uintptr_t>(key_bias) & 15) == 0),
+              "attention: key_bias needs padded rows and a 16-byte aligned stride covering whole 128-key blocks");
   const int inner = heads * ATT_DH;
   CUtensorMap tm;
   int rc = make_tmap_2d(&tm, qkv, 2, (uint64_t)3 * inner, (uint64_t)(row_start ? total_rows : samples * n_pad), (uint64_t)ld_qkv * 2,
@@ -331,9 +351,14 @@ int attention(cudaStream_t st, const __nv_bfloat16* qkv, int ld_qkv, __nv_bfloat
   F5E_REQUIRE(total < (1ll << 30), "attention: too many work items");
   const int grid = (int)(total < 2 * num_sms() ? total : 2 * num_sms());
   LaunchScope ls(st, PROF_ATTN, samples, n_pad, heads);
-  attention_kernel<<<grid, ATT_THREADS, ATT_SMEM_TOTAL, st>>>(tm, out, ldo, klen, row_start, n_pad, inner, heads, qtiles,
-                                                              (int)total,
-                                                              scale * 1.4426950408889634f);
+  if (key_bias)
+    attention_kernel<true><<<grid, ATT_THREADS, ATT_SMEM_TOTAL, st>>>(tm, out, ldo, klen, row_start, n_pad, inner, heads,
+                                                                      qtiles, (int)total, scale * 1.4426950408889634f,
+                                                                      key_bias, ld_bias);
+  else
+    attention_kernel<false><<<grid, ATT_THREADS, ATT_SMEM_TOTAL, st>>>(tm, out, ldo, klen, row_start, n_pad, inner, heads,
+                                                                       qtiles, (int)total, scale * 1.4426950408889634f,
+                                                                       nullptr, 0);
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

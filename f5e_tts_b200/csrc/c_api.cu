@@ -73,6 +73,13 @@ int f5e_attention(const void* qkv, int32_t ld_qkv, void* out, int32_t ldo, const
                    n_pad, heads, scale);
 }
 
+int f5e_attention_bias(const void* qkv, int32_t ld_qkv, void* out, int32_t ldo, const int32_t* klen, const float* key_bias,
+                       int32_t ld_bias, int32_t samples, int32_t n_pad, int32_t heads, float scale, void* stream) {
+  F5E_REQUIRE(qkv && out && key_bias, "f5e_attention_bias: null argument");
+  return attention((cudaStream_t)stream, (const __nv_bfloat16*)qkv, ld_qkv, (__nv_bfloat16*)out, ldo, klen, samples,
+                   n_pad, heads, scale, nullptr, 0, key_bias, ld_bias);
+}
+
 int f5e_conv_pos(const void* x, const void* w_packed, int32_t samples, int32_t n_pad, int32_t dim, int32_t groups,
                  const f5e_epilogue* ep, void* stream) {
   F5E_REQUIRE(x && w_packed && ep && ep->out, "f5e_conv_pos: null argument");

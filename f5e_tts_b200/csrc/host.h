@@ -44,7 +44,8 @@ int gather_rows(cudaStream_t st, const __nv_bfloat16* src, __nv_bfloat16* dst, c
 // o[rows, inner] = softmax(q k^T * scale, keys < klen[sample]) v over qkv[rows, 3*inner] (Q|K|V column blocks)
 // row_start (optional): first row of every sample when the rows are PACKED (valid frames only); total_rows = rows of qkv
 int attention(cudaStream_t st, const __nv_bfloat16* qkv, int ld_qkv, __nv_bfloat16* out, int ldo, const int* klen,
-              int samples, int n_pad, int heads, float scale, const int* row_start = nullptr, int total_rows = 0);
+              int samples, int n_pad, int heads, float scale, const int* row_start = nullptr, int total_rows = 0,
+              const float* key_bias = nullptr, int ld_bias = 0);
 // grouped conv k=31 as implicit GEMM; wp = packed weights [31*dim, 64]
 int conv_pos(cudaStream_t st, const __nv_bfloat16* x, const __nv_bfloat16* wp, int samples, int n_pad, int dim,
              int groups, const EpiParams& ep);

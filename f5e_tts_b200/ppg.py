@@ -126,3 +126,240 @@ def make_pad_mask(lengths: torch.Tensor, max_len: int = 0) -> torch.Tensor:
 def ppg_true_len(mel_lens: torch.Tensor, ppg_len: int, ppg_frame_length=20, mel_f_shift=10) -> torch.Tensor:
     """ppg/ppg_model.py:139-141: frames of the (sub-sampled) PPG that belong to each utterance."""
     return (mel_lens / (ppg_frame_length / mel_f_shift)).long().clamp(max=ppg_len)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Conformer encoder + content head (ASRModel.extract, ppg/asr_model.py:222-244) and the wrapper (ppg/ppg_model.py:59-168)
+# ---------------------------------------------------------------------------------------------------------------
+from . import ops  # noqa: E402
+
+_ENCODER_DEFAULTS = dict(output_size=256, attention_heads=4, linear_units=2048, num_blocks=6, input_layer="conv2d",
+                         pos_enc_layer_type="rel_pos", normalize_before=True, concat_after=False, macaron_style=True,
+                         activation_type="swish", use_cnn_module=True, cnn_module_kernel=15, causal=False,
+                         cnn_module_norm="batch_norm", use_emb=False)
+
+
+class ASRModel:
+    """The part of the reference's ASRModel that `extract` runs (asr_model.py:222-244, non-streaming): GlobalCMVN,
+    Conv2dSubsampling2, RelPositionalEncoding, `num_blocks` ConformerEncoderLayers, after_norm and the content Linear.
+    `load_state_dict` takes the reference checkpoint's keys (`encoder.*`, `linear.*`; decoder / CTC / CE heads are not on
+    this path and are ignored).  Activations bf16, statistics and accumulation fp32; no CPU path."""
+
+    def __init__(self, input_dim: int = 80, **encoder_conf):
+        conf = dict(_ENCODER_DEFAULTS)
+        unknown = set(encoder_conf) - set(conf) - {"dropout_rate", "positional_dropout_rate", "attention_dropout_rate",
+                                                    "static_chunk_size", "use_dynamic_chunk", "use_dynamic_left_chunk",
+                                                    "selfattention_layer_type", "positionwise_conv_kernel_size", "emb_dim"}
+        if unknown:
+            raise TypeError(f"ASRModel: unknown encoder_conf keys {sorted(unknown)}")
+        conf.update({k: v for k, v in encoder_conf.items() if k in conf})
+        for key, want in (("input_layer", "conv2d"), ("pos_enc_layer_type", "rel_pos"), ("normalize_before", True),
+                          ("concat_after", False), ("macaron_style", True), ("activation_type", "swish"),
+                          ("use_cnn_module", True), ("cnn_module_norm", "batch_norm"), ("use_emb", False)):
+            if conf[key] != want:
+                raise NotImplementedError(f"f5e_tts_b200.ASRModel: {key}={conf[key]!r} is not implemented (only {want!r})")
+        self.conf, self.input_dim = conf, input_dim
+        self.dim, self.heads = conf["output_size"], conf["attention_heads"]
+        if self.dim % self.heads or self.dim // self.heads != 64 or self.dim % 256:
+            raise NotImplementedError("f5e_tts_b200.ASRModel: the attention kernel needs output_size / attention_heads == 64 "
+                                      "and the norm kernel output_size % 256 == 0")
+        self.sd: dict | None = None
+        self.device = None
+        self._plan = None
+        self._pos: dict = {}
+
+    def load_state_dict(self, state_dict: dict, strict: bool = False):
+        need = ["encoder.embed.conv.0.weight", "encoder.embed.out.0.weight", "encoder.after_norm.weight", "linear.weight"]
+        need += [f"encoder.encoders.{self.conf['num_blocks'] - 1}.norm_final.weight"]
+        missing = [k for k in need if k not in state_dict]
+        if missing:
+            raise KeyError(f"ASRModel.load_state_dict: missing {missing}")
+        self.sd = {k: v.detach().float() for k, v in state_dict.items() if k.startswith("encoder.") or k.startswith("linear.")}
+        self._plan, self._pos = None, {}
+        return self
+
+    def to(self, device):
+        self.device = torch.device(device)
+        self._plan, self._pos = None, {}
+        return self
+
+    def eval(self):
+        return self
+
+    @property
+    def global_cmvn(self) -> GlobalCMVN | None:
+        if self.sd is None or "encoder.global_cmvn.mean" not in self.sd:
+            return None
+        return GlobalCMVN(self.sd["encoder.global_cmvn.mean"], self.sd["encoder.global_cmvn.istd"])
+
+    # ---- plan: device copies of the weights in the layouts the kernels take -------------------------------------
+    def _get_plan(self):
+        if self._plan is not None:
+            return self._plan
+        if self.sd is None or self.device is None or self.device.type != "cuda":
+            raise RuntimeError("f5e_tts_b200.ASRModel: load_state_dict() and .to(<cuda device>) first; there is no CPU path")
+        _lib.require_device()
+        sd, dev, d = self.sd, self.device, self.dim
+        f32 = lambda t: t.to(dev, torch.float32).contiguous()
+        b16 = lambda t: t.to(dev, torch.bfloat16).contiguous()
+        fo = (self.input_dim - 3) // 2 + 1
+        xs = math.sqrt(d)  # RelPositionalEncoding.xscale, folded into the sub-sampling Linear
+        w_out = sd["encoder.embed.out.0.weight"].view(d, d, fo).permute(0, 2, 1).reshape(d, fo * d)  # (c, f) -> (f, c) columns
+        P = dict(fo=fo, conv_w=f32(sd["encoder.embed.conv.0.weight"].view(d, 9)), conv_b=f32(sd["encoder.embed.conv.0.bias"]),
+                 w_out=b16(w_out * xs), b_out=f32(sd["encoder.embed.out.0.bias"] * xs),
+                 an_w=f32(sd["encoder.after_norm.weight"]), an_b=f32(sd["encoder.after_norm.bias"]),
+                 w_lin=b16(sd["linear.weight"]), b_lin=f32(sd["linear.bias"]), layers=[])
+        taps = self.conf["cnn_module_kernel"]
+        for i in range(self.conf["num_blocks"]):
+            p = f"encoder.encoders.{i}."
+            g = lambda k: sd[p + k]
+            ly = {}
+            for nm in ("norm_ff_macaron", "norm_mha", "norm_conv", "norm_ff", "norm_final"):
+                ly[nm] = (f32(g(nm + ".weight")), f32(g(nm + ".bias")))
+            for nm, tag in (("feed_forward_macaron", "m"), ("feed_forward", "f")):
+                ly[tag + "w1"], ly[tag + "b1"] = b16(g(nm + ".w_1.weight")), f32(g(nm + ".w_1.bias"))
+                ly[tag + "w2"], ly[tag + "b2"] = b16(0.5 * g(nm + ".w_2.weight")), f32(0.5 * g(nm + ".w_2.bias"))  # ff_scale
+            ly["wqkv"] = b16(torch.cat([g("self_attn.linear_q.weight"), g("self_attn.linear_k.weight"), g("self_attn.linear_v.weight")]))
+            ly["bqkv"] = f32(torch.cat([g("self_attn.linear_q.bias"), g("self_attn.linear_k.bias"), g("self_attn.linear_v.bias")]))
+            ly["wo"], ly["bo"] = b16(g("self_attn.linear_out.weight")), f32(g("self_attn.linear_out.bias"))
+            ly["wpos"] = g("self_attn.linear_pos.weight")
+            ly["u"], ly["v"] = f32(g("self_attn.pos_bias_u")), f32(g("self_attn.pos_bias_v"))
+            ly["wpw1"], ly["bpw1"] = b16(g("conv_module.pointwise_conv1.weight").view(2 * d, d)), f32(g("conv_module.pointwise_conv1.bias"))
+            s = g("conv_module.norm.weight") / torch.sqrt(g("conv_module.norm.running_var") + 1e-5)  # eval BatchNorm1d, folded
+            ly["wdw"] = f32(g("conv_module.depthwise_conv.weight").view(d, taps) * s[:, None])
+            ly["bdw"] = f32((g("conv_module.depthwise_conv.bias") - g("conv_module.norm.running_mean")) * s + g("conv_module.norm.bias"))
+            ly["wpw2"], ly["bpw2"] = b16(g("conv_module.pointwise_conv2.weight").view(d, d)), f32(g("conv_module.pointwise_conv2.bias"))
+            P["layers"].append(ly)
+        self._plan = P
+        return P
+
+    def _pos_tables(self, n_pad: int):
+        """linear_pos(pos_emb[:n_pad]) of every layer (attention.py:199-200): input independent, fp32 [n_pad, dim]."""
+        if n_pad not in self._pos:
+            pos = torch.arange(0, n_pad, dtype=torch.float32).unsqueeze(1)
+            div = torch.exp(torch.arange(0, self.dim, 2, dtype=torch.float32) * -(math.log(10000.0) / self.dim))
+            pe = torch.zeros(n_pad, self.dim)
+            pe[:, 0::2], pe[:, 1::2] = torch.sin(pos * div), torch.cos(pos * div)  # embedding.py:37-43
+            pe = pe.to(self.device)
+            self._pos[n_pad] = [(pe @ ly["wpos"].to(self.device).t()).contiguous() for ly in self._get_plan()["layers"]]
+        return self._pos[n_pad]
+
+    @torch.no_grad()
+    def extract(self, speech: torch.Tensor, speech_lengths: torch.Tensor, stream: bool = False, *, cmvn_applied: bool = False):
+        """asr_model.py:222-244.  speech fp32 [B, T, input_dim] fbank features, speech_lengths [B] (or [1] for all) frames.
+        -> (content embedding fp32 [B, T', dim], None); every utterance is processed as a batch-1 call would process it,
+        rows beyond its own (len - 1) // 2 frames are zeros.  The CE logits of the reference are not on the PPG path."""
+        if stream:
+            raise NotImplementedError("f5e_tts_b200.ASRModel.extract: chunk-by-chunk streaming is not implemented")
+        P = self._get_plan()
+        lib, dev, d, H = _lib.load(), self.device, self.dim, self.heads
+        i64, f32c = _lib.C.c_int64, _lib.C.c_float
+        if not speech.is_cuda:
+            raise RuntimeError("f5e_tts_b200.ASRModel has no CPU path: pass CUDA tensors")
+        B, T, Fdim = speech.shape
+        assert Fdim == self.input_dim
+        lens = speech_lengths.to(dev).to(torch.int32).flatten()
+        if lens.numel() == 1 and B > 1:
+            lens = lens.expand(B)
+        lens = lens.clamp(max=T).contiguous()
+        cm = None if cmvn_applied else self.global_cmvn
+        feats = speech.float()
+        if cm is not None:  # unfused GlobalCMVN (kaldiFbank.forward(cmvn=...) fuses it)
+            feats = (feats - cm.mean.to(dev)) * cm.istd.to(dev)
+        feats = feats.contiguous()
+        t_out = torch.where(lens >= 3, (lens - 3) // 2 + 1, torch.zeros_like(lens)).to(torch.int32).contiguous()
+        t_max = int(t_out.max())
+        if t_max == 0:
+            return torch.zeros(B, 0, d, device=dev), None
+        n_pad = (t_max + 7) // 8 * 8
+        rows = B * n_pad
+        st = stream_ptr()
+        a0 = torch.empty(rows, P["fo"] * d, device=dev, dtype=torch.bfloat16)
+        check(lib.f5e_subsample_conv(ptr(feats), i64(feats.stride(0)), ptr(lens), B, T, Fdim, ptr(P["conv_w"]), ptr(P["conv_b"]), d,
+                                     ptr(a0), n_pad, st), "f5e_subsample_conv")
+        x = ops.gemm(a0, P["w_out"], bias=P["b_out"])
+        del a0
+        pos = self._pos_tables(n_pad)
+        ld_bias = (n_pad + 127) // 128 * 128
+        key_bias = torch.zeros(B * H, ld_bias, device=dev, dtype=torch.float32)
+        att = torch.zeros(rows, d, device=dev, dtype=torch.bfloat16)
+        conv = torch.empty(rows, d, device=dev, dtype=torch.bfloat16)
+        taps = self.conf["cnn_module_kernel"]
+        lpad = taps - 1 if self.conf["causal"] else (taps - 1) // 2
+        ln = lambda v, wb: ops.norm_mod(v, wb[0], wb[1], plus_one=0.0, eps=1e-5)
+        for ly, pl in zip(P["layers"], pos):
+            h = ln(x, ly["norm_ff_macaron"])  # encoder_layer.py:206-213
+            x = ops.gemm(ops.gemm(h, ly["mw1"], bias=ly["mb1"], act=_lib.ACT_SILU), ly["mw2"], bias=ly["mb2"], residual=x)
+            h = ln(x, ly["norm_mha"])  # :216-236
+            qkv = ops.gemm(h, ly["wqkv"], bias=ly["bqkv"])
+            check(lib.f5e_relpos_prepare(ptr(qkv), qkv.stride(0), ptr(pl), ptr(ly["u"]), ptr(ly["v"]), ptr(key_bias), ld_bias, B,
+                                         n_pad, H, st), "f5e_relpos_prepare")
+            check(lib.f5e_attention_bias(ptr(qkv), qkv.stride(0), ptr(att), att.stride(0), ptr(t_out), ptr(key_bias), ld_bias, B,
+                                         n_pad, H, f32c(1.0 / math.sqrt(d // H)), st), "f5e_attention_bias")
+            x = ops.gemm(att, ly["wo"], bias=ly["bo"], residual=x)
+            h = ln(x, ly["norm_conv"])  # :243-248
+            g = ops.gemm(h, ly["wpw1"], bias=ly["bpw1"])
+            check(lib.f5e_glu_dwconv(ptr(g), ptr(ly["wdw"]), ptr(ly["bdw"]), ptr(t_out), ptr(conv), B, n_pad, d, taps, lpad, st),
+                  "f5e_glu_dwconv")
+            x = ops.gemm(conv, ly["wpw2"], bias=ly["bpw2"], residual=x)
+            h = ln(x, ly["norm_ff"])  # :254-263
+            x = ops.gemm(ops.gemm(h, ly["fw1"], bias=ly["fb1"], act=_lib.ACT_SILU), ly["fw2"], bias=ly["fb2"], residual=x)
+            x = ln(x, ly["norm_final"])
+        x = ln(x, (P["an_w"], P["an_b"]))  # encoder.py:203-204
+        out = ops.gemm(x, P["w_lin"], bias=P["b_lin"], out_f32=True).view(B, n_pad, d)[:, :t_max]  # asr_model.py:241
+        valid = torch.arange(t_max, device=dev).unsqueeze(0) < t_out.unsqueeze(1)
+        return out * valid.unsqueeze(-1), None
+
+
+class PPGModelWapper(object):
+    """ppg/ppg_model.py:59-168 (output_type "ppg"; the "map" variant needs phone-centre tables that live outside the tree).
+    Pass either the reference's `ppg_model_path` + `ppg_config` (train.yaml + checkpoint) or a ready `model`."""
+
+    def __init__(self, ppg_model_path=None, ppg_config=None, device="cuda", output_type="ppg", map_mix_ratio=1.0,
+                 ppg_frame_length=20, mel_f_shift=10, model: ASRModel | None = None, **_unused):
+        if output_type != "ppg":
+            raise NotImplementedError("f5e_tts_b200.PPGModelWapper: only output_type='ppg' (the 'map' tables are not in the tree)")
+        if model is None:
+            import yaml
+            with open(ppg_config, "r") as fin:
+                conf = yaml.load(fin, Loader=yaml.FullLoader)
+            model = ASRModel(conf["input_dim"], **conf.get("encoder_conf", {}))
+            model.load_state_dict(torch.load(ppg_model_path, map_location="cpu"))
+        self.ppg_model = model.to(device).eval()
+        self.device = torch.device(device)
+        self.output_type, self.map_mix_ratio = output_type, map_mix_ratio
+        self.ppg_frame_length, self.mel_f_shift = ppg_frame_length, mel_f_shift
+        self.featCal = kaldiFbank().eval()
+
+    @torch.no_grad()
+    def audio_to_mel(self, audio, sr=None, lens=None):
+        """ppg_model.py:147-160: -> (CMVN-normalised fbank [B, T, 80], frames).  `lens` (samples at 16 kHz) makes the batch ragged."""
+        if isinstance(audio, str):
+            raise NotImplementedError("f5e_tts_b200.PPGModelWapper: pass a waveform tensor (file decoding is outside the hot path)")
+        if audio.dim() == 1:
+            audio = audio.unsqueeze(0)
+        audio = audio.to(self.device)
+        if sr is not None and sr != 16000:
+            from .pipeline import resample
+            audio, new_lens = resample(audio, sr, 16000, lens)
+            if lens is not None:
+                lens = new_lens.to(self.device)
+        feats, feats_len = self.featCal(audio, lens=lens, cmvn=self.ppg_model.global_cmvn)
+        return feats, feats_len.to(self.device)
+
+    @torch.no_grad()
+    def mel_to_ppg(self, mel, mel_lens):
+        """ppg_model.py:134-145; `mel` as returned by audio_to_mel (CMVN already applied)."""
+        ppg, _ = self.ppg_model.extract(mel, mel_lens, stream=False, cmvn_applied=True)
+        lens = mel_lens.to(self.device).flatten()
+        if lens.numel() == 1 and ppg.shape[0] > 1:
+            lens = lens.expand(ppg.shape[0])
+        own = torch.where(lens >= 3, (lens - 3) // 2 + 1, torch.zeros_like(lens))
+        true_len = torch.minimum(ppg_true_len(lens, ppg.shape[1], self.ppg_frame_length, self.mel_f_shift), own)
+        ppg = ppg * (~make_pad_mask(true_len, ppg.shape[1]))[:, :, None]
+        return ppg, true_len
+
+    @torch.no_grad()
+    def audio_to_ppg(self, audio, sr=None, lens=None):
+        feats, feats_len = self.audio_to_mel(audio, sr, lens)
+        return self.mel_to_ppg(feats, feats_len)

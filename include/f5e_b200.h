@@ -111,6 +111,36 @@ int f5e_guided_euler(const float* pred, int32_t ld_pred, float* y, void* x_cat, 
 int f5e_attention(const void* qkv, int32_t ld_qkv, void* out, int32_t ldo, const int32_t* klen, int32_t samples,
                   int32_t n_pad, int32_t heads, float scale, void* stream);
 
+/* f5e_attention with a per-key additive term: scores = q.k_j + key_bias[(sample * heads + head) * ld_bias + j], then * scale.
+ * key_bias fp32, 16-byte aligned, ld_bias a multiple of 4 covering whole 128-key blocks (>= ceil(n_pad / 128) * 128).
+ * With f5e_relpos_prepare this is RelPositionMultiHeadedAttention.forward of the PPG Conformer
+ * (ppg/wenet/transformer/attention.py:179-222; this wenet version applies no rel_shift). */
+int f5e_attention_bias(const void* qkv, int32_t ld_qkv, void* out, int32_t ldo, const int32_t* klen, const float* key_bias,
+                       int32_t ld_bias, int32_t samples, int32_t n_pad, int32_t heads, float scale, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * PPG extractor: streaming kernels of the Conformer encoder (ppg/wenet/transformer/)
+ * ------------------------------------------------------------------------------------------------- */
+/* Conv2dSubsampling2.conv (subsampling.py:81-84, 114-117): Conv2d(1, C, 3, stride 2) + ReLU over (frames, mel bins).
+ * feats fp32 [batch, T, F] (utterance stride ld_feats), n_frames[b] valid frames (NULL: T); w fp32 [C, 9], bias [C].
+ * out bf16 [batch * t_pad, Fo * C], Fo = (F - 3) / 2 + 1, column f * C + c (the Linear that follows takes its weight
+ * columns in that order); rows >= (n_frames[b] - 3) / 2 + 1 of an utterance are zeros. */
+int f5e_subsample_conv(const float* feats, int64_t ld_feats, const int32_t* n_frames, int32_t batch, int32_t T, int32_t F,
+                       const float* w, const float* bias, int32_t C, void* out, int32_t t_pad, void* stream);
+
+/* Rel-pos attention, rewritten: (q+u).k_j + (q+v).p_j = q.(k_j + p_j) + (u.k_j + v.p_j).  In place on the K block of
+ * qkv (bf16 [samples * n_pad, 3 * heads * 64]): k_j += pos[j]; key_bias[(s * heads + h) * ld_bias + j] = u_h.k_j + v_h.pos_j.
+ * pos fp32 [n_pad, heads * 64] = linear_pos(pos_emb) (input independent, built once per layer); u, v fp32 [heads, 64]. */
+int f5e_relpos_prepare(void* qkv, int32_t ld_qkv, const float* pos, const float* u, const float* v, float* key_bias,
+                       int32_t ld_bias, int32_t samples, int32_t n_pad, int32_t heads, void* stream);
+
+/* ConvolutionModule between its two pointwise convs (convolution.py:116-127): GLU over channels, depthwise Conv1d(taps)
+ * with left_pad zeros on the left (symmetric: (taps - 1) / 2; causal: taps - 1), eval BatchNorm1d folded into w / b by
+ * the caller, swish.  g bf16 [samples * n_pad, 2 C] (value | gate) -> out bf16 [samples * n_pad, C]; frames outside
+ * [0, len[s]) read as zero (what a batch-1 call sees), rows >= len[s] are written as zeros. */
+int f5e_glu_dwconv(const void* g, const float* w, const float* b, const int32_t* len, void* out, int32_t samples,
+                   int32_t n_pad, int32_t C, int32_t taps, int32_t left_pad, void* stream);
+
 /* Grouped Conv1d(dim, dim, k=31, groups, padding=15) over frames, per sample, as a tcgen05 implicit GEMM with the
  * fused epilogue (bias, Mish, residual).  x: bf16 [samples*n_pad, dim] contiguous; w_packed: bf16 [31*dim, 64]
  * with w_packed[tap*dim + co, ci] = weight[co, ci, tap] (ci >= dim/groups zero).  Frames outside [0, n_pad) of a

@@ -68,3 +68,129 @@ def test_fbank_rejects_cpu_and_short(cuda_dev):
         kaldiFbank()(torch.zeros(1, 1600))
     with pytest.raises(ValueError):
         kaldiFbank()(torch.zeros(1, 399, device=cuda_dev))
+
+
+# ---- Conformer encoder + content head -------------------------------------------------------------------------------
+K_TOL = 2.0  # same bar as the DiT: err(product vs fp32 oracle) <= K_TOL * err(bf16 oracle vs fp32 oracle) + 5e-3 (rel-L2)
+
+
+def rel_l2(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).norm() / b.norm().clamp_min(1e-12)).item()
+
+
+def make_model(cfg, sd, dev):
+    from f5e_tts_b200.ppg import ASRModel
+    sd16 = {k: (v.to(torch.bfloat16).float() if v.dim() >= 2 and "global_cmvn" not in k else v) for k, v in sd.items()}
+    m = ASRModel(cfg.input_dim, output_size=cfg.dim, attention_heads=cfg.heads, linear_units=cfg.ffn, num_blocks=cfg.blocks,
+                 cnn_module_kernel=cfg.kernel)
+    return m.load_state_dict(sd16).to(dev), sd16
+
+
+def test_conformer_vs_reference_golden(cuda_dev):
+    """The product against the output of the reference's own wenet modules (tests/golden/ppg_conformer.pt)."""
+    from f5e_tts_b200.ppg import PPGModelWapper
+    fx = torch.load(os.path.join(os.path.dirname(__file__), "golden", "ppg_conformer.pt"))
+    cfg = PO.ConformerConfig(blocks=fx["blocks"])
+    sd = PO.make_conformer_state_dict(cfg, seed=fx["seed"])
+    model, sd16 = make_model(cfg, sd, cuda_dev)
+    wrap = PPGModelWapper(model=model, device=cuda_dev)
+    ppg, true_len = wrap.audio_to_ppg(fx["wave"].to(cuda_dev), sr=16000)
+    assert ppg.shape == (1,) + tuple(fx["ppg"].shape) and true_len.tolist() == [fx["ppg"].shape[0]]
+    o16 = PO.conformer_extract(cfg, sd16, fx["feats"].to(cuda_dev), torch.bfloat16).cpu()
+    o32 = PO.conformer_extract(cfg, sd16, fx["feats"].to(cuda_dev)).cpu()
+    e_got, e_ref, e_w = rel_l2(ppg[0].cpu(), o32), rel_l2(o16, o32), rel_l2(o32, fx["ppg"])
+    print(f"golden: product-vs-fp32 {e_got:.3e}  oracle-bf16-vs-fp32 {e_ref:.3e}  (bf16 weights vs reference fp32 weights {e_w:.3e})")
+    assert e_got <= K_TOL * e_ref + 5e-3
+    assert rel_l2(ppg[0].cpu(), fx["ppg"]) <= K_TOL * rel_l2(o16, fx["ppg"]) + 5e-3
+
+
+@pytest.mark.parametrize("blocks", [1, 12])
+def test_conformer_ragged_batch_vs_oracle(cuda_dev, blocks):
+    from f5e_tts_b200.ppg import PPGModelWapper
+    cfg = PO.ConformerConfig(blocks=blocks)
+    sd = PO.make_conformer_state_dict(cfg, seed=5)
+    model, sd16 = make_model(cfg, sd, cuda_dev)
+    wrap = PPGModelWapper(model=model, device=cuda_dev)
+    g = torch.Generator().manual_seed(3)
+    lens = torch.tensor([48000, 17000, 33333, 1000])
+    wave = 0.1 * torch.randn(4, 48000, generator=g)
+    ppg, true_len = wrap.audio_to_ppg(wave.to(cuda_dev), sr=16000, lens=lens.to(cuda_dev))
+    worst = 0.0
+    for b in range(4):
+        w = wave[b, :int(lens[b])]
+        want32, n = PO.audio_to_ppg(cfg, sd16, w.to(cuda_dev))
+        want16, _ = PO.audio_to_ppg(cfg, sd16, w.to(cuda_dev), torch.bfloat16)
+        assert int(true_len[b]) == n
+        assert float(ppg[b, n:].abs().max()) == 0.0 if n < ppg.shape[1] else True
+        e_got, e_ref = rel_l2(ppg[b, :n], want32), rel_l2(want16, want32)
+        print(f"blocks={blocks} utt {b} ({n} frames): product-vs-fp32 {e_got:.3e}  oracle-bf16-vs-fp32 {e_ref:.3e}")
+        assert e_got <= K_TOL * e_ref + 5e-3
+        worst = max(worst, e_got / (K_TOL * e_ref + 5e-3))
+        alone, n1 = wrap.audio_to_ppg(w.to(cuda_dev)[None], sr=16000)  # ragged batch == batch-1 call, bit for bit
+        assert int(n1[0]) == n and torch.equal(alone[0, :n], ppg[b, :n])
+    print(f"blocks={blocks}: worst product error / allowed = {worst:.2f}")
+
+
+def test_kernels_of_the_conformer(cuda_dev):
+    """subsample conv, rel-pos key bias + attention, GLU/depthwise conv: each against plain torch on random data."""
+    import math
+    import torch.nn.functional as F
+    from f5e_tts_b200 import _lib
+    from f5e_tts_b200._lib import check, ptr, stream_ptr
+    lib, C = _lib.load(), _lib.C
+    g = torch.Generator().manual_seed(1)
+    # 1. Conv2d(1, C, 3, 2) + ReLU
+    B, T, Fd, Cc = 2, 21, 80, 256
+    feats = torch.randn(B, T, Fd, generator=g).to(cuda_dev)
+    w, b = torch.randn(Cc, 1, 3, 3, generator=g).to(cuda_dev) / 3, torch.randn(Cc, generator=g).to(cuda_dev)
+    nfr = torch.tensor([21, 10], dtype=torch.int32, device=cuda_dev)
+    t_pad, Fo = 16, 39
+    out = torch.empty(B * t_pad, Fo * Cc, device=cuda_dev, dtype=torch.bfloat16)
+    check(lib.f5e_subsample_conv(ptr(feats), C.c_int64(feats.stride(0)), ptr(nfr), B, T, Fd, ptr(w.view(Cc, 9).contiguous()), ptr(b), Cc,
+                                 ptr(out), t_pad, stream_ptr()), "f5e_subsample_conv")
+    want = F.relu(F.conv2d(feats[:, None], w, b, stride=2)).permute(0, 2, 3, 1)  # [B, t, f, c]
+    got = out.view(B, t_pad, Fo, Cc).float()
+    assert torch.equal(got[0, :10], want[0].bfloat16().float()) or (got[0, :10] - want[0]).abs().max() < 2e-2
+    assert (got[1, :4] - want[1, :4]).abs().max() < 2e-2 and float(got[1, 4:].abs().max()) == 0.0 and float(got[0, 10:].abs().max()) == 0.0
+    # 2. rel-pos attention = q.(k+p) + (u.k + v.p)
+    S, n_pad, H = 2, 200, 4
+    d = H * 64
+    qkv = (torch.randn(S * n_pad, 3 * d, generator=g) * 0.5).to(cuda_dev).bfloat16()
+    pos = (torch.randn(n_pad, d, generator=g) * 0.5).to(cuda_dev)
+    u, v = (torch.randn(H, 64, generator=g) * 0.3).to(cuda_dev), (torch.randn(H, 64, generator=g) * 0.3).to(cuda_dev)
+    klen = torch.tensor([200, 77], dtype=torch.int32, device=cuda_dev)
+    q, k, vv = [t.float().view(S, n_pad, H, 64).transpose(1, 2) for t in qkv.split(d, dim=1)]
+    p = pos.view(n_pad, H, 64).transpose(0, 1)
+    scores = ((q + u[None, :, None]) @ k.transpose(-1, -2) + (q + v[None, :, None]) @ p.transpose(-1, -2)[None]) / 8.0
+    scores = scores.masked_fill(torch.arange(n_pad, device=cuda_dev)[None, None, None] >= klen[:, None, None, None], float("-inf"))
+    want = (torch.softmax(scores, -1) @ vv).transpose(1, 2).reshape(S, n_pad, d)
+    ld_bias = 256
+    kb = torch.zeros(S * H, ld_bias, device=cuda_dev)
+    work = qkv.clone()
+    check(lib.f5e_relpos_prepare(ptr(work), work.stride(0), ptr(pos), ptr(u), ptr(v), ptr(kb), ld_bias, S, n_pad, H, stream_ptr()),
+          "f5e_relpos_prepare")
+    att = torch.zeros(S * n_pad, d, device=cuda_dev, dtype=torch.bfloat16)
+    check(lib.f5e_attention_bias(ptr(work), work.stride(0), ptr(att), att.stride(0), ptr(klen), ptr(kb), ld_bias, S, n_pad, H,
+                                 C.c_float(0.125), stream_ptr()), "f5e_attention_bias")
+    got = att.view(S, n_pad, d).float()
+    for s_ in range(S):
+        n = int(klen[s_])
+        e = rel_l2(got[s_, :n], want[s_, :n])
+        print(f"rel-pos attention sample {s_}: rel-L2 {e:.3e}")
+        assert e < 2e-2
+    # 3. GLU + depthwise conv + swish
+    S, n_pad, Cc, taps = 2, 50, 256, 15
+    gin = torch.randn(S * n_pad, 2 * Cc, generator=g).to(cuda_dev).bfloat16()
+    wd, bd = (torch.randn(Cc, taps, generator=g) / 4).to(cuda_dev), torch.randn(Cc, generator=g).to(cuda_dev)
+    ln_ = torch.tensor([50, 23], dtype=torch.int32, device=cuda_dev)
+    out = torch.empty(S * n_pad, Cc, device=cuda_dev, dtype=torch.bfloat16)
+    for lpad in (7, 14):
+        check(lib.f5e_glu_dwconv(ptr(gin), ptr(wd), ptr(bd), ptr(ln_), ptr(out), S, n_pad, Cc, taps, lpad, stream_ptr()), "f5e_glu_dwconv")
+        for s_ in range(S):
+            n = int(ln_[s_])
+            x = F.glu(gin.view(S, n_pad, 2 * Cc)[s_, :n].float(), dim=-1).t()[None]
+            y = F.conv1d(F.pad(x, (lpad, taps - 1 - lpad)), wd[:, None], bd, groups=Cc)
+            y = (y * torch.sigmoid(y))[0].t()
+            got = out.view(S, n_pad, Cc)[s_].float()
+            assert rel_l2(got[:n], y) < 1e-2 and (float(got[n:].abs().max()) == 0.0 if n < n_pad else True)
