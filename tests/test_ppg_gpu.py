@@ -194,3 +194,43 @@ def test_kernels_of_the_conformer(cuda_dev):
             y = (y * torch.sigmoid(y))[0].t()
             got = out.view(S, n_pad, Cc)[s_].float()
             assert rel_l2(got[:n], y) < 1e-2 and (float(got[n:].abs().max()) == 0.0 if n < n_pad else True)
+
+
+def test_voice_conversion_end_to_end(cuda_dev):
+    """Source audio -> kaldi fbank -> Conformer PPG -> CFM.sample_vc (eval_infer_batch_vc.py:215-225), product chain against the
+    oracle chain under the bf16 bar."""
+    import f5e_oracle as O
+    from test_parity_gpu import build
+    from f5e_tts_b200.ppg import PPGModelWapper
+    cfg = O.DiTConfig(dim=512, depth=2, heads=8, text_dim=256, conv_layers=2, text_num_embeds=50, text_mask_padding=False,
+                      pe_attn_head=1, use_ppg=True, ppg_dim=256)
+    model, sd = build(cfg, 41, cuda_dev)
+    pcfg = PO.ConformerConfig(blocks=2)
+    psd = PO.make_conformer_state_dict(pcfg, seed=6)
+    pmodel, psd16 = make_model(pcfg, psd, cuda_dev)
+    wrap = PPGModelWapper(model=pmodel, device=cuda_dev)
+    g = torch.Generator().manual_seed(42)
+    B = 2
+    src_len = torch.tensor([40000, 29000])
+    src = 0.1 * torch.randn(B, 40000, generator=g)
+    ref_len = torch.tensor([60, 45], device=cuda_dev)
+    dur = torch.tensor([290, 230], device=cuda_dev)
+    cond = torch.randn(B, 60, cfg.mel_dim, generator=g).to(cuda_dev)
+    ppg, true_len = wrap.audio_to_ppg(src.to(cuda_dev), sr=16000, lens=src_len.to(cuda_dev))
+    o_ppg = {}
+    for dt in (torch.float32, torch.bfloat16):
+        rows = [PO.audio_to_ppg(pcfg, psd16, src[b, :int(src_len[b])].to(cuda_dev), dt)[0] for b in range(B)]
+        o_ppg[dt] = torch.nn.utils.rnn.pad_sequence(rows, batch_first=True)
+    assert o_ppg[torch.float32].shape == ppg.shape
+    kw = dict(steps=6, sway_sampling_coef=-1.0)
+    okw = dict(mode="vc", alpha_spk=2.5, alpha_cont=3.0, **kw)
+    o32 = O.OracleDiT(cfg, sd, torch.float32, cuda_dev)
+    o16 = O.OracleDiT(cfg, sd, torch.bfloat16, cuda_dev)
+    out16, traj16, aux = O.cfm_sample(o16, cond, None, dur, ppg=o_ppg[torch.bfloat16], lens=ref_len, seed=3, return_aux=True, **okw)
+    out32, traj32 = O.cfm_sample(o32, cond.bfloat16().float(), None, dur, ppg=o_ppg[torch.float32], lens=ref_len, y0=aux["y0"].float(), **okw)
+    got, traj = model.sample_vc(cond, ppg, dur, lens=ref_len, seed=3, alpha_spk=2.5, alpha_ppg=3.0, **kw)
+    for i in range(B):
+        L = int(aux["duration"][i])
+        e_got, e_ref = rel_l2(traj[-1][i, :L], traj32[-1][i, :L]), rel_l2(traj16[-1][i, :L], traj32[-1][i, :L])
+        print(f"vc end to end sample {i}: product-vs-fp32 {e_got:.3e}  oracle-bf16-vs-fp32 {e_ref:.3e}")
+        assert e_got <= K_TOL * e_ref + 5e-3
