@@ -67,7 +67,8 @@ def full():
     raw = subprocess.run(["ncu", "-i", p, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
     h, units = rows[0], rows[1]
-    out = [f"# {tag}: `ncu --set full --clock-control none` of the top kernels (one DiT evaluation, BASELINE config 2 shape)", "",
+    what = "one DiT evaluation, BASELINE config 2 shape" if re.fullmatch(r"r\d+", tag) else "see the capture command in DESIGN.md"
+    out = [f"# {tag}: `ncu --set full --clock-control none` of the top kernels ({what})", "",
            "Numbers taken under the profiler explain the kernels; they are never bench values.", ""]
     traffic = defaultdict(list)
     for v in rows[2:]:
@@ -81,12 +82,17 @@ def full():
         try:
             rd, wr = float(d["dram__bytes_read.sum"].replace(",", "")), float(d["dram__bytes_write.sum"].replace(",", ""))
             scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u.get("dram__bytes_read.sum", "Mbyte"), 1e6)
-            traffic[name.split("<")[0]].append((rd + wr) * scale)
+            traffic[name.split("<")[0] if re.fullmatch(r"r\d+", tag) else name].append((rd + wr) * scale)
         except (KeyError, ValueError):
             pass
         out.append("")
     open(os.path.join(ROOT, "profiles", f"{tag}_kernels.md"), "w").write("\n".join(out) + "\n")
     tj = {k: sum(v) / len(v) for k, v in traffic.items()}
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp) and not re.fullmatch(r"r\d+", tag):  # side captures (e.g. r01ppg) add to the table, never replace it
+        old = json.load(open(tp))
+        old.update(tj)
+        tj = old
     tj["_note"] = f"mean dram__bytes_read.sum + dram__bytes_write.sum per launch, bytes, from gpurun_out/{tag}_full.ncu-rep"
     json.dump(tj, open(os.path.join(ROOT, "profiles", "traffic.json"), "w"), indent=1)
     print(json.dumps(tj, indent=1))
