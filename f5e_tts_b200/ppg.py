@@ -167,6 +167,8 @@ class ASRModel:
         self.device = None
         self._plan = None
         self._pos: dict = {}
+        self._graphs: dict = {}
+        self.use_cuda_graph = False  # extension: replay one captured graph per (batch, frames) shape
 
     def load_state_dict(self, state_dict: dict, strict: bool = False):
         need = ["encoder.embed.conv.0.weight", "encoder.embed.out.0.weight", "encoder.after_norm.weight", "linear.weight"]
@@ -175,12 +177,12 @@ class ASRModel:
         if missing:
             raise KeyError(f"ASRModel.load_state_dict: missing {missing}")
         self.sd = {k: v.detach().float() for k, v in state_dict.items() if k.startswith("encoder.") or k.startswith("linear.")}
-        self._plan, self._pos = None, {}
+        self._plan, self._pos, self._graphs = None, {}, {}
         return self
 
     def to(self, device):
         self.device = torch.device(device)
-        self._plan, self._pos = None, {}
+        self._plan, self._pos, self._graphs = None, {}, {}
         return self
 
     def eval(self):
@@ -267,10 +269,37 @@ class ASRModel:
         if cm is not None:  # unfused GlobalCMVN (kaldiFbank.forward(cmvn=...) fuses it)
             feats = (feats - cm.mean.to(dev)) * cm.istd.to(dev)
         feats = feats.contiguous()
-        t_out = torch.where(lens >= 3, (lens - 3) // 2 + 1, torch.zeros_like(lens)).to(torch.int32).contiguous()
-        t_max = int(t_out.max())
-        if t_max == 0:
+        if T < 3:
             return torch.zeros(B, 0, d, device=dev), None
+        if not self.use_cuda_graph:
+            return self._encode(feats, lens), None
+        # one CUDA graph per (batch, frames): the encoder is ~200 small launches, host-launch-bound when issued one by one
+        key = (B, T)
+        if key not in self._graphs:
+            sf, sl = feats.clone(), lens.clone()
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                self._encode(sf, sl)  # warm-up: position tables, kernel attributes, allocator
+            torch.cuda.current_stream().wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                so = self._encode(sf, sl)
+            self._graphs[key] = (graph, sf, sl, so)
+        graph, sf, sl, so = self._graphs[key]
+        sf.copy_(feats)
+        sl.copy_(lens)
+        graph.replay()
+        return so.clone(), None
+
+    def _encode(self, feats: torch.Tensor, lens: torch.Tensor) -> torch.Tensor:
+        """Device work of `extract`: no host synchronisation (the padded length comes from T, not from the lengths)."""
+        P = self._get_plan()
+        lib, dev, d, H = _lib.load(), self.device, self.dim, self.heads
+        i64, f32c = _lib.C.c_int64, _lib.C.c_float
+        B, T, Fdim = feats.shape
+        t_out = torch.where(lens >= 3, (lens - 3) // 2 + 1, torch.zeros_like(lens)).to(torch.int32).contiguous()
+        t_max = (T - 3) // 2 + 1  # = (T - 1) // 2: the length the reference returns for a T-frame batch
         n_pad = (t_max + 7) // 8 * 8
         rows = B * n_pad
         st = stream_ptr()
@@ -308,7 +337,7 @@ class ASRModel:
         x = ln(x, (P["an_w"], P["an_b"]))  # encoder.py:203-204
         out = ops.gemm(x, P["w_lin"], bias=P["b_lin"], out_f32=True).view(B, n_pad, d)[:, :t_max]  # asr_model.py:241
         valid = torch.arange(t_max, device=dev).unsqueeze(0) < t_out.unsqueeze(1)
-        return out * valid.unsqueeze(-1), None
+        return out * valid.unsqueeze(-1)
 
 
 class PPGModelWapper(object):

@@ -130,6 +130,13 @@ def test_conformer_ragged_batch_vs_oracle(cuda_dev, blocks):
         alone, n1 = wrap.audio_to_ppg(w.to(cuda_dev)[None], sr=16000)  # ragged batch == batch-1 call, bit for bit
         assert int(n1[0]) == n and torch.equal(alone[0, :n], ppg[b, :n])
     print(f"blocks={blocks}: worst product error / allowed = {worst:.2f}")
+    # the CUDA-graph path replays the same kernels: same bits, also on new data of the same shape
+    wave2, lens2 = wave.flip(0).contiguous(), torch.tensor([20000, 48000, 999, 31000])
+    want2, _ = wrap.audio_to_ppg(wave2.to(cuda_dev), sr=16000, lens=lens2.to(cuda_dev))
+    model.use_cuda_graph = True
+    g1, n1 = wrap.audio_to_ppg(wave.to(cuda_dev), sr=16000, lens=lens.to(cuda_dev))
+    g2, _ = wrap.audio_to_ppg(wave2.to(cuda_dev), sr=16000, lens=lens2.to(cuda_dev))
+    assert torch.equal(g1, ppg) and torch.equal(n1, true_len) and torch.equal(g2, want2)
 
 
 def test_kernels_of_the_conformer(cuda_dev):
