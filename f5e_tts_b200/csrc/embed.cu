@@ -135,8 +135,9 @@ int dwconv7(cudaStream_t st, const __nv_bfloat16* x, const float* w, const float
 // ---------------------------------------------------------------------------------------------
 // GRN (model/modules.py:225-234):  Gx[s,c] = ||x[s,:,c]||_2 over ALL n_pad frames;
 //   Nx = Gx / (mean_c Gx + 1e-6);  out = gamma * (x * Nx) + beta + x
-// grn_sumsq accumulates sum of squares per (sample, channel) with one atomicAdd per thread per
-// 64-frame slab; grn_apply recomputes the tiny per-sample mean in shared memory and applies.
+// grn_sumsq writes the sum of squares of every 64-frame slab per (sample, slab, channel); grn_apply adds the slabs in a
+// FIXED order (no atomics: the result must not depend on where the allocator put the buffers - float atomics arrive in an
+// address-dependent order), recomputes the tiny per-sample mean in shared memory and applies.
 // ---------------------------------------------------------------------------------------------
 constexpr int GRN_SLAB = 64;
 __global__ void __launch_bounds__(256)
@@ -151,8 +152,9 @@ grn_sumsq_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sumsq,
     a0 = fmaf(v.x, v.x, a0);
     a1 = fmaf(v.y, v.y, a1);
   }
-  atomicAdd(sumsq + (size_t)s * C + c, a0);
-  atomicAdd(sumsq + (size_t)s * C + c + 1, a1);
+  float* dst = sumsq + ((size_t)s * gridDim.y + blockIdx.y) * C + c;
+  dst[0] = a0;
+  dst[1] = a1;
 }
 
 __global__ void __launch_bounds__(256)
@@ -163,8 +165,11 @@ grn_apply_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ 
   float* part = sh + C;
   const int s = blockIdx.z, n0 = blockIdx.y * GRN_SLAB;
   float loc = 0.f;
+  const int slabs = gridDim.y;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    const float g = sqrtf(sumsq[(size_t)s * C + c]);
+    float tot_c = 0.f;
+    for (int k = 0; k < slabs; ++k) tot_c += sumsq[((size_t)s * slabs + k) * C + c];
+    const float g = sqrtf(tot_c);
     scale[c] = g;
     loc += g;
   }
@@ -186,11 +191,10 @@ grn_apply_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ 
   }
 }
 
-// scratch: fp32 [samples, C], zeroed here (cudaMemsetAsync) before accumulation.
+// scratch: fp32 [samples, ceil(n_pad / 64), C] slab partials, fully written by grn_sumsq.
 int grn(cudaStream_t st, const __nv_bfloat16* x, const float* gamma, const float* beta, __nv_bfloat16* out,
         float* scratch, int samples, int n_pad, int C) {
   F5E_REQUIRE(samples > 0 && n_pad > 0 && C % 2 == 0 && C <= 8192, "grn: bad shape");
-  F5E_CUDA_CHECK(cudaMemsetAsync(scratch, 0, (size_t)samples * C * sizeof(float), st));
   dim3 g1((C / 2 + 255) / 256, (n_pad + GRN_SLAB - 1) / GRN_SLAB, samples);
   {
     LaunchScope ls(st, PROF_ELEM, samples, n_pad, 4);

@@ -45,11 +45,12 @@ def infer_batches(model, vocoder, prompts_all, *, nfe_step=32, cfg_strength=2.0,
                   sampler="sample", sampler_kwargs=None):
     """Solve this rank's batches.  Returns [(utt, wave fp32 [1, n] on the CPU)] (or whatever `sink(utt, wave, sr)`
     returned, when a sink is given).  sampler: "sample" (eval_infer_batch.py), "sample_tts" (eval_infer_batch_tts.py:
-    alpha_spk / alpha_txt in sampler_kwargs instead of cfg_strength)."""
+    alpha_spk / alpha_txt in sampler_kwargs instead of cfg_strength), "sample_vc" (eval_infer_batch_vc.py: batches from
+    pipeline.get_vc_inference_prompt carry the padded PPG where the text list is; alpha_spk / alpha_ppg in sampler_kwargs)."""
     dev = torch.device(device) if device is not None else model.device
     out = []
     for bi in split_batches(prompts_all, rank, world, split):
-        utts, ref_rms_list, ref_mels, ref_mel_lens, total_mel_lens, final_text_list = prompts_all[bi]
+        utts, ref_rms_list, ref_mels, ref_mel_lens, total_mel_lens, final_text_list = prompts_all[bi]  # [5]: PPG for sample_vc
         ref_mels = ref_mels.to(dev)
         ref_len = torch.tensor(ref_mel_lens, dtype=torch.long, device=dev)
         total = torch.tensor(total_mel_lens, dtype=torch.long, device=dev)
@@ -61,6 +62,10 @@ def infer_batches(model, vocoder, prompts_all, *, nfe_step=32, cfg_strength=2.0,
             generated, _ = model.sample_tts(cond=ref_mels, text=final_text_list, duration=total, lens=ref_len, steps=nfe_step,
                                             sway_sampling_coef=sway_sampling_coef, no_ref_audio=no_ref_audio, seed=seed,
                                             **(sampler_kwargs or {}))
+        elif sampler == "sample_vc":  # eval_infer_batch_vc.py:215-225 over pipeline.get_vc_inference_prompt batches
+            generated, _ = model.sample_vc(cond=ref_mels, ppg=final_text_list.to(dev), duration=total, lens=ref_len, steps=nfe_step,
+                                           sway_sampling_coef=sway_sampling_coef, no_ref_audio=no_ref_audio, seed=seed,
+                                           **(sampler_kwargs or {}))
         else:
             raise ValueError(f"unknown sampler {sampler!r}")
         n_frames = [t - r for t, r in zip(total_mel_lens, ref_mel_lens)]

@@ -166,7 +166,7 @@ def grn(x, gamma, beta):
     _cuda_bf16(x, "x")
     B, N, Cc = x.shape
     out = torch.empty_like(x)
-    scratch = torch.empty(B, Cc, device=x.device, dtype=torch.float32)
+    scratch = torch.empty(B, (N + 63) // 64, Cc, device=x.device, dtype=torch.float32)  # slab partials
     check(_lib.load().f5e_grn(ptr(x), ptr(gamma), ptr(beta), ptr(out), ptr(scratch), B, N, Cc, stream_ptr()), "f5e_grn")
     return out
 

@@ -104,25 +104,17 @@ def prepare_reference(audio: torch.Tensor, sr: int, target_rms: float = TARGET_R
 # ---------------------------------------------------------------------------------------------------------------------
 # evaluation prompts (eval/utils_eval.py:77-219)
 # ---------------------------------------------------------------------------------------------------------------------
-def get_inference_prompt(metainfo, speed=1.0, text_converter=None, target_sample_rate=TARGET_SAMPLE_RATE, n_fft=1024,
-                         win_length=1024, n_mel_channels=100, hop_length=HOP_LENGTH, mel_spec_type="vocos",
-                         target_rms=TARGET_RMS, use_truth_duration=False, infer_batch_size=1, num_buckets=200, min_secs=3,
-                         max_secs=40, device="cuda", slab=128):
-    """Same bucketing / batching / shuffling as the reference, same return tuples
-    (utts, ref_rms_list, padded ref mels [B, T, n_mel], ref_mel_lens, total_mel_lens, final_text_list) per batch.
-    metainfo rows: (utt, prompt_text, (prompt_wave [1, n] or [n], sr), gt_text, gt) where `gt` is (wave, sr) when
-    use_truth_duration else ignored - waveforms instead of file names: decoding audio files stays with the caller.
-    text_converter: the tokenizer front end (`convert_char_to_pinyin` in the reference); default keeps the raw strings.
-    The loudness floor, resampling and MelSpec of `slab` prompts at a time run as batched kernels on `device`."""
+def _prepare_references(metainfo, dev, slab, target_sample_rate, n_fft, win_length, n_mel_channels, hop_length,
+                        mel_spec_type, target_rms):
+    """The audio half of get_inference_prompt / get_vc_inference_prompt (utils_eval.py:118-134, 286-299): loudness floor,
+    resampling and MelSpec of the prompts, batched per sample rate, `slab` prompts at a time.
+    -> (ref_rms [n], device-resident ref mels [n_mel, frames], ref_mel_len [n])."""
     from .frontend import MelSpec
 
     if mel_spec_type != "vocos":
         raise NotImplementedError("f5e_tts_b200: only the vocos mel variant is implemented")
-    dev = torch.device(device)
     mel_spectrogram = MelSpec(n_fft=n_fft, hop_length=hop_length, win_length=win_length, n_mel_channels=n_mel_channels,
                               target_sample_rate=target_sample_rate, mel_spec_type=mel_spec_type).to(dev)
-    metainfo = list(metainfo)
-    # ---- audio: batched per sample rate, `slab` prompts at a time ----
     ref_rms_all, ref_mel_all, ref_len_all = [None] * len(metainfo), [None] * len(metainfo), [0] * len(metainfo)
     by_sr: dict = {}
     for i, row in enumerate(metainfo):
@@ -146,6 +138,31 @@ def get_inference_prompt(metainfo, speed=1.0, text_converter=None, target_sample
                 ref_rms_all[i] = rms[r]
                 ref_len_all[i] = n // hop_length
                 ref_mel_all[i] = mel_spectrogram(wav[r:r + 1, :n]).squeeze(0)  # [n_mel, n // hop + 1], device resident
+    return ref_rms_all, ref_mel_all, ref_len_all
+
+
+def _resampled_length(n: int, sr: int, new_sr: int) -> int:
+    """Length torchaudio's resampler returns: ceil(new * n / old) on the reduced rates."""
+    if int(sr) == int(new_sr):
+        return n
+    g = math.gcd(int(sr), int(new_sr))
+    return -(-(int(new_sr) // g) * n // (int(sr) // g))
+
+
+def get_inference_prompt(metainfo, speed=1.0, text_converter=None, target_sample_rate=TARGET_SAMPLE_RATE, n_fft=1024,
+                         win_length=1024, n_mel_channels=100, hop_length=HOP_LENGTH, mel_spec_type="vocos",
+                         target_rms=TARGET_RMS, use_truth_duration=False, infer_batch_size=1, num_buckets=200, min_secs=3,
+                         max_secs=40, device="cuda", slab=128):
+    """Same bucketing / batching / shuffling as the reference, same return tuples
+    (utts, ref_rms_list, padded ref mels [B, T, n_mel], ref_mel_lens, total_mel_lens, final_text_list) per batch.
+    metainfo rows: (utt, prompt_text, (prompt_wave [1, n] or [n], sr), gt_text, gt) where `gt` is (wave, sr) when
+    use_truth_duration else ignored - waveforms instead of file names: decoding audio files stays with the caller.
+    text_converter: the tokenizer front end (`convert_char_to_pinyin` in the reference); default keeps the raw strings.
+    The loudness floor, resampling and MelSpec of `slab` prompts at a time run as batched kernels on `device`."""
+    dev = torch.device(device)
+    metainfo = list(metainfo)
+    ref_rms_all, ref_mel_all, ref_len_all = _prepare_references(metainfo, dev, slab, target_sample_rate, n_fft, win_length,
+                                                               n_mel_channels, hop_length, mel_spec_type, target_rms)
     # ---- text, durations, buckets: host integer logic, identical to the reference ----
     prompts_all = []
     min_tokens = min_secs * target_sample_rate // hop_length
@@ -167,10 +184,7 @@ def get_inference_prompt(metainfo, speed=1.0, text_converter=None, target_sample
         ref_mel_len = ref_len_all[i]
         if use_truth_duration:
             gt_wave, gt_sr = row[4]
-            n_gt = gt_wave.shape[-1]
-            if int(gt_sr) != target_sample_rate:
-                g = math.gcd(int(gt_sr), target_sample_rate)
-                n_gt = -(-(target_sample_rate // g) * n_gt // (int(gt_sr) // g))  # length torchaudio's resampler returns
+            n_gt = _resampled_length(gt_wave.shape[-1], gt_sr, target_sample_rate)
             total_mel_len = ref_mel_len + int(n_gt / hop_length / speed)
         else:
             ref_text_len = len(prompt_text.encode("utf-8"))
@@ -195,6 +209,95 @@ def get_inference_prompt(metainfo, speed=1.0, text_converter=None, target_sample
         if frames > 0:
             flush(b)
     random.seed(666)  # "not only leave easy work for last workers" (utils_eval.py:214-216)
+    random.shuffle(prompts_all)
+    return prompts_all
+
+
+def get_vc_inference_prompt(metainfo, ppg_model, speed=1.0, target_sample_rate=TARGET_SAMPLE_RATE, n_fft=1024, win_length=1024,
+                            n_mel_channels=100, hop_length=HOP_LENGTH, mel_spec_type="vocos", target_rms=TARGET_RMS,
+                            use_truth_duration=False, infer_batch_size=1, num_buckets=200, min_secs=3, max_secs=40,
+                            device="cuda", slab=64):
+    """eval/utils_eval.py:245-397 with waveforms instead of file names: rows (utt, prompt_text, (prompt_wave, sr), gt_text,
+    (gt_wave, gt_sr)).  Same return tuples (utts, ref_rms_list, padded ref mels [B, T, n_mel], ref_mel_lens, total_mel_lens,
+    padded PPG [B, T_ppg, dim]), same bucketing and shuffle.  As in the reference (:301-320) the PPG is extracted from the
+    SOURCE audio concatenated with itself (the "prompt" half is loaded from gt_wav there too), resampled to 16 kHz, multi-channel
+    sources averaged.  `slab` sources at a time go through the resampler, kaldi fbank and the Conformer as one ragged batch."""
+    dev = torch.device(device)
+    metainfo = list(metainfo)
+    ref_rms_all, ref_mel_all, ref_len_all = _prepare_references(metainfo, dev, slab, target_sample_rate, n_fft, win_length,
+                                                               n_mel_channels, hop_length, mel_spec_type, target_rms)
+    # ---- PPG of the doubled source, batched per sample rate ----
+    ppg_all, ppg_len_all = [None] * len(metainfo), [0] * len(metainfo)
+    by_sr: dict = {}
+    for i, row in enumerate(metainfo):
+        wave, sr = row[4]
+        wave = wave.reshape(1, -1) if wave.ndim == 1 else wave
+        by_sr.setdefault((int(sr), wave.shape[0]), []).append((i, wave))
+    for (sr, ch), items in by_sr.items():
+        for s0 in range(0, len(items), slab):
+            part = items[s0:s0 + slab]
+            lens = torch.tensor([w.shape[-1] for _, w in part])
+            n_max = int(lens.max())
+            batch = torch.zeros(len(part) * ch, n_max, dtype=torch.float32).pin_memory()
+            for r, (_, w) in enumerate(part):
+                batch[r * ch:(r + 1) * ch, : w.shape[-1]] = w
+            wav, out_lens = resample(batch.to(dev, non_blocking=True), sr, 16000, lens.repeat_interleave(ch))
+            if ch > 1:  # resample every channel, then average (:301-308)
+                wav, out_lens = wav.view(len(part), ch, -1).mean(dim=1), out_lens[::ch]
+            n16 = out_lens.to(dev)
+            m = wav.shape[1]
+            idx = torch.arange(2 * m, device=dev).unsqueeze(0)
+            src = torch.where(idx < n16[:, None], idx, idx - n16[:, None]).clamp(0, m - 1)
+            full = torch.gather(wav, 1, src) * (idx < 2 * n16[:, None])  # [source | source], ragged
+            ppg, true_len = ppg_model.audio_to_ppg(full, 16000, lens=2 * n16)
+            true_len = true_len.cpu()
+            for r, (i, _) in enumerate(part):
+                t = (int(1 + (2 * int(out_lens[r]) - 400) // 160) - 1) // 2  # frames the batch-1 call of the reference returns
+                ppg_all[i], ppg_len_all[i] = ppg[r, :t], int(true_len[r])
+    # ---- durations, buckets: host integer logic, identical to the reference ----
+    prompts_all = []
+    min_tokens = min_secs * target_sample_rate // hop_length
+    max_tokens = max_secs * target_sample_rate // hop_length
+    batch_accum = [0] * num_buckets
+    utts, ref_rms_list, ref_mels, ref_mel_lens, total_mel_lens, ppg_list, ppg_lens = ([[] for _ in range(num_buckets)] for _ in range(7))
+
+    def flush(b):
+        T = max(m.shape[-1] for m in ref_mels[b])
+        padded = torch.stack([torch.nn.functional.pad(m, (0, T - m.shape[-1]), value=0) for m in ref_mels[b]]).permute(0, 2, 1)
+        P = max(ppg_lens[b])  # padded_ppg_batch (:226-242): truncate / pad every PPG to the longest ppg_length of the batch
+        pp = torch.stack([torch.nn.functional.pad(p[:P], (0, 0, 0, P - min(p.shape[0], P)), value=0) for p in ppg_list[b]])
+        prompts_all.append((utts[b], ref_rms_list[b], padded, ref_mel_lens[b], total_mel_lens[b], pp))
+
+    for i, row in enumerate(metainfo):
+        utt, prompt_text, gt_text = row[0], row[1], row[3]
+        ref_mel_len = ref_len_all[i]
+        if use_truth_duration:
+            gt_wave, gt_sr = row[4]
+            total_mel_len = ref_mel_len + int(_resampled_length(gt_wave.shape[-1], gt_sr, target_sample_rate) / hop_length / speed)
+        else:
+            ref_text_len = len(prompt_text.encode("utf-8"))
+            gen_text_len = len(gt_text.encode("utf-8"))
+            total_mel_len = ref_mel_len + int(ref_mel_len / ref_text_len * gen_text_len / speed)
+        assert infer_batch_size > 0, "infer_batch_size should be greater than 0."
+        assert min_tokens <= total_mel_len <= max_tokens, (
+            f"Audio {utt} has duration {total_mel_len * hop_length // target_sample_rate}s out of range [{min_secs}, {max_secs}].")
+        b = math.floor((total_mel_len - min_tokens) / (max_tokens - min_tokens + 1) * num_buckets)
+        utts[b].append(utt)
+        ref_rms_list[b].append(ref_rms_all[i])
+        ref_mels[b].append(ref_mel_all[i])
+        ref_mel_lens[b].append(ref_mel_len)
+        total_mel_lens[b].append(total_mel_len)
+        ppg_list[b].append(ppg_all[i])
+        ppg_lens[b].append(ppg_len_all[i])
+        batch_accum[b] += total_mel_len
+        if batch_accum[b] >= infer_batch_size:
+            flush(b)
+            batch_accum[b] = 0
+            utts[b], ref_rms_list[b], ref_mels[b], ref_mel_lens[b], total_mel_lens[b], ppg_list[b], ppg_lens[b] = [], [], [], [], [], [], []
+    for b, frames in enumerate(batch_accum):
+        if frames > 0:
+            flush(b)
+    random.seed(666)
     random.shuffle(prompts_all)
     return prompts_all
 

@@ -361,8 +361,9 @@ class PPGModelWapper(object):
         self.featCal = kaldiFbank().eval()
 
     @torch.no_grad()
-    def audio_to_mel(self, audio, sr=None, lens=None):
-        """ppg_model.py:147-160: -> (CMVN-normalised fbank [B, T, 80], frames).  `lens` (samples at 16 kHz) makes the batch ragged."""
+    def audio_to_mel(self, audio, sr=None, lens=None, *, fuse_cmvn: bool = False):
+        """ppg_model.py:147-160: -> (kaldi fbank [B, T, 80], frames).  `lens` (samples) makes the batch ragged; fuse_cmvn applies
+        the encoder's GlobalCMVN in the same kernel (then call mel_to_ppg(..., cmvn_applied=True))."""
         if isinstance(audio, str):
             raise NotImplementedError("f5e_tts_b200.PPGModelWapper: pass a waveform tensor (file decoding is outside the hot path)")
         if audio.dim() == 1:
@@ -373,13 +374,13 @@ class PPGModelWapper(object):
             audio, new_lens = resample(audio, sr, 16000, lens)
             if lens is not None:
                 lens = new_lens.to(self.device)
-        feats, feats_len = self.featCal(audio, lens=lens, cmvn=self.ppg_model.global_cmvn)
+        feats, feats_len = self.featCal(audio, lens=lens, cmvn=self.ppg_model.global_cmvn if fuse_cmvn else None)
         return feats, feats_len.to(self.device)
 
     @torch.no_grad()
-    def mel_to_ppg(self, mel, mel_lens):
-        """ppg_model.py:134-145; `mel` as returned by audio_to_mel (CMVN already applied)."""
-        ppg, _ = self.ppg_model.extract(mel, mel_lens, stream=False, cmvn_applied=True)
+    def mel_to_ppg(self, mel, mel_lens, *, cmvn_applied: bool = False):
+        """ppg_model.py:134-145: fbank features (as audio_to_mel returns them) -> (ppg [B, T', dim] zero beyond true_len, true_len)."""
+        ppg, _ = self.ppg_model.extract(mel, mel_lens, stream=False, cmvn_applied=cmvn_applied)
         lens = mel_lens.to(self.device).flatten()
         if lens.numel() == 1 and ppg.shape[0] > 1:
             lens = lens.expand(ppg.shape[0])
@@ -390,5 +391,5 @@ class PPGModelWapper(object):
 
     @torch.no_grad()
     def audio_to_ppg(self, audio, sr=None, lens=None):
-        feats, feats_len = self.audio_to_mel(audio, sr, lens)
-        return self.mel_to_ppg(feats, feats_len)
+        feats, feats_len = self.audio_to_mel(audio, sr, lens, fuse_cmvn=True)
+        return self.mel_to_ppg(feats, feats_len, cmvn_applied=True)

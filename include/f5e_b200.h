@@ -164,7 +164,8 @@ int f5e_text_gather(const int64_t* text, int32_t samples, int32_t nt, const void
 /* Depthwise Conv1d(C, C, k=7, padding=3) + bias over frames per sample (model/modules.py:250-252). */
 int f5e_dwconv7(const void* x_bf16, const float* w, const float* b, void* out_bf16, int32_t samples, int32_t n_pad,
                 int32_t C, void* stream);
-/* GRN (model/modules.py:225-234) over all n_pad frames of each sample; scratch: fp32 [samples, C]. */
+/* GRN (model/modules.py:225-234) over all n_pad frames of each sample; scratch: fp32 [samples, ceil(n_pad / 64), C]
+ * (slab partial sums, added in a fixed order: bit-reproducible wherever the buffers live). */
 int f5e_grn(const void* x_bf16, const float* gamma, const float* beta, void* out_bf16, float* scratch, int32_t samples,
             int32_t n_pad, int32_t C, void* stream);
 

@@ -207,3 +207,55 @@ def audio_to_ppg(cfg: ConformerConfig, sd: dict, wave16k: torch.Tensor, dtype=to
     true_len = min(int(feats.shape[0] / 2), ppg.shape[0])  # :139-141 (ppg_frame_length 20 / mel_f_shift 10)
     ppg[true_len:] = 0.0
     return ppg, true_len
+
+
+def get_vc_inference_prompt(metainfo, cfg: ConformerConfig, sd: dict, speed=1.0, target_sample_rate=24000, hop_length=256,
+                            target_rms=0.1, infer_batch_size=1, num_buckets=200, min_secs=3, max_secs=40, dtype=torch.float32):
+    """eval/utils_eval.py:245-397 with waveforms in place of file names, one utterance at a time like the reference:
+    rows (utt, prompt_text, (prompt_wave, sr), gt_text, (gt_wave, gt_sr)).  The PPG comes from the 16 kHz source concatenated
+    with itself (:301-320: the "prompt" half is loaded from gt_wav as well), multi-channel sources averaged after resampling."""
+    import random
+    import f5e_oracle as O
+    prompts_all = []
+    min_tokens = min_secs * target_sample_rate // hop_length
+    max_tokens = max_secs * target_sample_rate // hop_length
+    acc = [0] * num_buckets
+    cols = [[[] for _ in range(num_buckets)] for _ in range(7)]
+
+    def emit(b):
+        mels = cols[2][b]
+        T = max(m.shape[-1] for m in mels)
+        padded = torch.stack([F.pad(m, (0, T - m.shape[-1]), value=0) for m in mels]).permute(0, 2, 1)
+        P = max(cols[6][b])
+        pp = torch.stack([F.pad(p, (0, 0, 0, P - p.shape[0]), value=0) for p in cols[5][b]])  # padded_ppg_batch (:226-242)
+        prompts_all.append((cols[0][b], cols[1][b], padded, cols[3][b], cols[4][b], pp))
+
+    for utt, prompt_text, (ref_audio, ref_sr), gt_text, (gt_audio, gt_sr) in metainfo:
+        ref_audio = ref_audio.reshape(1, -1)
+        ref_audio, ref_rms = O.rms_floor(ref_audio, target_rms)
+        ref_audio = O.resample(ref_audio, ref_sr, target_sample_rate)
+        ref_mel = O.mel_spectrogram(ref_audio).squeeze(0)
+        ref_mel_len = ref_audio.shape[-1] // hop_length
+        gt = gt_audio.reshape(1, -1) if gt_audio.ndim == 1 else gt_audio
+        gt16 = O.resample(gt, gt_sr, 16000)
+        if gt16.shape[0] > 1:
+            gt16 = gt16.mean(dim=0, keepdim=True)
+        full = torch.cat([gt16, gt16], dim=1)
+        ppg, ppg_len = audio_to_ppg(cfg, sd, full[0], dtype)
+        total = ref_mel_len + int(ref_mel_len / len(prompt_text.encode("utf-8")) * len(gt_text.encode("utf-8")) / speed)
+        assert min_tokens <= total <= max_tokens
+        b = math.floor((total - min_tokens) / (max_tokens - min_tokens + 1) * num_buckets)
+        for c, v in zip(cols, (utt, ref_rms, ref_mel, ref_mel_len, total, ppg, ppg_len)):
+            c[b].append(v)
+        acc[b] += total
+        if acc[b] >= infer_batch_size:
+            emit(b)
+            acc[b] = 0
+            for c in cols:
+                c[b] = []
+    for b, frames in enumerate(acc):
+        if frames > 0:
+            emit(b)
+    random.seed(666)
+    random.shuffle(prompts_all)
+    return prompts_all

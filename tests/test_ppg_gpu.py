@@ -241,3 +241,57 @@ def test_voice_conversion_end_to_end(cuda_dev):
         e_got, e_ref = rel_l2(traj[-1][i, :L], traj32[-1][i, :L]), rel_l2(traj16[-1][i, :L], traj32[-1][i, :L])
         print(f"vc end to end sample {i}: product-vs-fp32 {e_got:.3e}  oracle-bf16-vs-fp32 {e_ref:.3e}")
         assert e_got <= K_TOL * e_ref + 5e-3
+
+
+def test_get_vc_inference_prompt_and_eval_loop(cuda_dev):
+    """pipeline.get_vc_inference_prompt (eval/utils_eval.py:245-397) against the oracle's one-utterance-at-a-time restatement,
+    then the sample_vc evaluation loop (eval_infer_batch_vc.py:203-232) over its batches."""
+    import f5e_oracle as O
+    from test_parity_gpu import build
+    from f5e_tts_b200.evaluate import infer_batches
+    from f5e_tts_b200.pipeline import get_vc_inference_prompt
+    from f5e_tts_b200.ppg import PPGModelWapper
+    from f5e_tts_b200.vocos import Vocos
+    pcfg = PO.ConformerConfig(blocks=2)
+    psd = PO.make_conformer_state_dict(pcfg, seed=8)
+    pmodel, psd16 = make_model(pcfg, psd, cuda_dev)
+    wrap = PPGModelWapper(model=pmodel, device=cuda_dev)
+    g = torch.Generator().manual_seed(77)
+    meta = []
+    for i, (psr, gsr, ch) in enumerate([(24000, 16000, 1), (16000, 24000, 1), (24000, 16000, 2), (24000, 24000, 1), (16000, 16000, 1)]):
+        pw = 0.05 * torch.randn(1, int(psr * (3.0 + 0.3 * i)), generator=g)
+        gw = 0.1 * torch.randn(ch, int(gsr * (2.0 + 0.5 * i)), generator=g)
+        meta.append((f"utt{i}", "some prompt text here.", (pw, psr), "words to say " * (2 + i), (gw, gsr)))
+    got = get_vc_inference_prompt(meta, wrap, infer_batch_size=1500, device=cuda_dev)
+    want32 = PO.get_vc_inference_prompt(meta, pcfg, psd16, infer_batch_size=1500)
+    want16 = PO.get_vc_inference_prompt(meta, pcfg, psd16, infer_batch_size=1500, dtype=torch.bfloat16)
+    assert len(got) == len(want32) and sum(len(b[0]) for b in got) == len(meta)
+    for gb, w32, w16 in zip(got, want32, want16):
+        assert gb[0] == w32[0] and gb[3] == w32[3] and gb[4] == w32[4]  # utterances, ref_mel_lens, total_mel_lens: exact
+        assert gb[2].shape == w32[2].shape and (gb[2].cpu() - w32[2]).abs().max() < 3e-4
+        assert gb[5].shape == w32[5].shape
+        for r in range(gb[5].shape[0]):
+            e_got, e_ref = rel_l2(gb[5][r].cpu(), w32[5][r]), rel_l2(w16[5][r], w32[5][r])
+            print(f"{gb[0][r]}: ppg {tuple(gb[5][r].shape)} product-vs-fp32 {e_got:.3e}  oracle-bf16-vs-fp32 {e_ref:.3e}")
+            assert e_got <= K_TOL * e_ref + 5e-3
+    cfg = O.DiTConfig(dim=512, depth=2, heads=8, text_dim=256, conv_layers=2, text_num_embeds=50, text_mask_padding=False,
+                      pe_attn_head=1, use_ppg=True, ppg_dim=256)
+    model, _ = build(cfg, 43, cuda_dev)
+    voc = Vocos(seed=4321).to(cuda_dev)
+    kw = dict(nfe_step=4, sway_sampling_coef=-1.0, seed=5, sampler="sample_vc", sampler_kwargs=dict(alpha_spk=2.5, alpha_ppg=3.0))
+    out = infer_batches(model, voc, got, device=cuda_dev, **kw)
+    assert sorted(u for u, _ in out) == sorted(m[0] for m in meta)
+    by_utt = dict(out)
+    # the loop's waves are what a direct sample_vc + decode of the same batch gives
+    utts, rms, mels, ref_lens, tot_lens, ppg = got[0]
+    rl, tl = torch.tensor(ref_lens, device=cuda_dev), torch.tensor(tot_lens, device=cuda_dev)
+    gen, _ = model.sample_vc(cond=mels.to(cuda_dev), ppg=ppg, duration=tl, lens=rl, steps=4, sway_sampling_coef=-1.0, seed=5,
+                             alpha_spk=2.5, alpha_ppg=3.0)
+    wav = voc.decode_varlen(gen, rl, tl, max_frames=max(t - r for t, r in zip(tot_lens, ref_lens)))
+    n0 = (tot_lens[0] - ref_lens[0] - 1) * 256
+    w0 = wav[0, :n0].cpu()
+    if float(rms[0]) < 0.1:
+        w0 = w0 * float(rms[0]) / 0.1
+    assert by_utt[utts[0]].shape == (1, n0) and torch.allclose(by_utt[utts[0]][0], w0, atol=1e-6)
+    two = infer_batches(model, voc, got, device=cuda_dev, rank=0, world=2, **kw) + infer_batches(model, voc, got, device=cuda_dev, rank=1, world=2, **kw)
+    assert sorted(u for u, _ in two) == sorted(by_utt) and all(torch.equal(w, by_utt[u]) for u, w in two)
