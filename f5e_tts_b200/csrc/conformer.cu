@@ -67,22 +67,51 @@ relpos_prepare_kernel(__nv_bfloat16* __restrict__ qkv, int ld_qkv, const float* 
 }
 
 // g bf16 [samples * n_pad, 2 C] (value | gate) -> out bf16 [samples * n_pad, C]:
-//   y[t, c] = swish(b[c] + sum_k w[c, k] * glu[t + k - lpad, c]),  glu = value * sigmoid(gate), zero outside [0, len[s])
-// w fp32 [C, taps] / b fp32 [C] already carry the eval BatchNorm.  Rows t >= len[s] are written as zeros.
+//   y[t, c] = swish(norm(b[c] + sum_k w[c, k] * glu[t + k - lpad, c])),  glu = value * sigmoid(gate)
+// glu reads as zero at t >= len[s] and as pad_val[c] at t < 0 (NULL: zero).  The reference pads the causal left context BEFORE
+// its biased pointwise conv (convolution.py:104-113), so that context is glu(bias) - pad_val carries it; the symmetric module
+// pads the depthwise conv itself with zeros.  norm: eval BatchNorm1d arrives folded into w / b; LayerNorm over the C channels
+// of a frame (ln_w != NULL; needs C <= blockDim.x, one block per frame tile) is applied here.  Rows t >= len[s] are zeros.
 constexpr int DW_TT = 16;
+
+__device__ __forceinline__ void block_sum_tt(float (&v)[DW_TT], float* red) {  // red: [8][DW_TT]; all threads take part
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+#pragma unroll
+  for (int i = 0; i < DW_TT; ++i) v[i] = warp_sum(v[i]);
+  if (lane == 0) {
+#pragma unroll
+    for (int i = 0; i < DW_TT; ++i) red[warp * DW_TT + i] = v[i];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < DW_TT; ++i) {
+    float t = 0.f;
+    for (int w = 0; w < nw; ++w) t += red[w * DW_TT + i];
+    v[i] = t;
+  }
+  __syncthreads();
+}
+
 __global__ void __launch_bounds__(256)
 glu_dwconv_kernel(const __nv_bfloat16* __restrict__ g, const float* __restrict__ w, const float* __restrict__ b,
-                  const int* __restrict__ len, __nv_bfloat16* __restrict__ out, int n_pad, int C, int taps, int lpad) {
-  extern __shared__ float tile[];  // [DW_TT + taps - 1][cw]
+                  const int* __restrict__ len, __nv_bfloat16* __restrict__ out, int n_pad, int C, int taps, int lpad,
+                  const float* __restrict__ pad_val, const float* __restrict__ ln_w, const float* __restrict__ ln_b, float ln_eps) {
+  extern __shared__ float tile[];  // [DW_TT + taps - 1][blockDim.x]
+  __shared__ float red[8 * DW_TT];
   const int s = blockIdx.y, t0 = blockIdx.x * DW_TT, c0 = blockIdx.z * blockDim.x;
   const int cw = min((int)blockDim.x, C - c0);
   const int n = len ? min(len[s], n_pad) : n_pad;
   const int span = DW_TT + taps - 1;
   const int c = threadIdx.x;
-  if (c < cw) {
+  const bool active = c < cw;
+  float acc[DW_TT];
+#pragma unroll
+  for (int i = 0; i < DW_TT; ++i) acc[i] = 0.f;
+  if (active) {
+    const float pv = pad_val ? __ldg(pad_val + c0 + c) : 0.f;
     for (int r = 0; r < span; ++r) {
       const int t = t0 + r - lpad;
-      float val = 0.f;
+      float val = t < 0 ? pv : 0.f;
       if (t >= 0 && t < n) {
         const __nv_bfloat16* row = g + ((size_t)s * n_pad + t) * (2 * (size_t)C) + c0 + c;
         const float a = __bfloat162float(row[0]), gt = __bfloat162float(row[C]);
@@ -91,7 +120,6 @@ glu_dwconv_kernel(const __nv_bfloat16* __restrict__ g, const float* __restrict__
       tile[r * blockDim.x + c] = val;
     }
     // a thread only reads the column it wrote: no barrier needed
-    float acc[DW_TT];
     const float bc = __ldg(b + c0 + c);
 #pragma unroll
     for (int i = 0; i < DW_TT; ++i) acc[i] = bc;
@@ -100,6 +128,27 @@ glu_dwconv_kernel(const __nv_bfloat16* __restrict__ g, const float* __restrict__
 #pragma unroll
       for (int i = 0; i < DW_TT; ++i) acc[i] = fmaf(wk, tile[(i + k) * blockDim.x + c], acc[i]);
     }
+  }
+  if (ln_w) {  // LayerNorm over the channels of each frame (two-pass, fp32); the launcher guarantees gridDim.z == 1
+    float m[DW_TT];
+#pragma unroll
+    for (int i = 0; i < DW_TT; ++i) m[i] = acc[i];  // inactive threads hold zeros
+    block_sum_tt(m, red);
+    float q[DW_TT];
+#pragma unroll
+    for (int i = 0; i < DW_TT; ++i) {
+      m[i] /= (float)C;
+      const float d = active ? acc[i] - m[i] : 0.f;
+      q[i] = d * d;
+    }
+    block_sum_tt(q, red);
+    if (active) {
+      const float lw = __ldg(ln_w + c), lb = __ldg(ln_b + c);
+#pragma unroll
+      for (int i = 0; i < DW_TT; ++i) acc[i] = (acc[i] - m[i]) * rsqrtf(q[i] / (float)C + ln_eps) * lw + lb;
+    }
+  }
+  if (active) {
 #pragma unroll
     for (int i = 0; i < DW_TT; ++i) {
       const int t = t0 + i;
@@ -143,9 +192,12 @@ int f5e_relpos_prepare(void* qkv, int32_t ld_qkv, const float* pos, const float*
 }
 
 int f5e_glu_dwconv(const void* g, const float* w, const float* b, const int32_t* len, void* out, int32_t samples,
-                   int32_t n_pad, int32_t C, int32_t taps, int32_t left_pad, void* stream) {
+                   int32_t n_pad, int32_t C, int32_t taps, int32_t left_pad, const float* pad_val, const float* ln_w,
+                   const float* ln_b, float ln_eps, void* stream) {
   F5E_REQUIRE(g && w && b && out && samples > 0 && n_pad > 0 && C > 0, "f5e_glu_dwconv: bad arguments");
   F5E_REQUIRE(taps >= 1 && taps <= 64 && left_pad >= 0 && left_pad < taps, "f5e_glu_dwconv: taps must be in [1, 64]");
+  F5E_REQUIRE((ln_w == nullptr) == (ln_b == nullptr), "f5e_glu_dwconv: LayerNorm weight and bias go together");
+  F5E_REQUIRE(ln_w == nullptr || C <= 256, "f5e_glu_dwconv: the LayerNorm variant needs C <= 256 (one block per frame tile), C=%d", C);
   const int threads = C < 256 ? ((C + 31) / 32) * 32 : 256;
   const size_t smem = (size_t)(DW_TT + taps - 1) * threads * sizeof(float);
   if (smem > 48 * 1024)
@@ -153,7 +205,7 @@ int f5e_glu_dwconv(const void* g, const float* w, const float* b, const int32_t*
   cudaStream_t st = (cudaStream_t)stream;
   LaunchScope ls(st, PROF_CONV, samples, n_pad, C);
   glu_dwconv_kernel<<<dim3((n_pad + DW_TT - 1) / DW_TT, samples, (C + threads - 1) / threads), threads, smem, st>>>(
-      (const __nv_bfloat16*)g, w, b, len, (__nv_bfloat16*)out, n_pad, C, taps, left_pad);
+      (const __nv_bfloat16*)g, w, b, len, (__nv_bfloat16*)out, n_pad, C, taps, left_pad, pad_val, ln_w, ln_b, ln_eps);
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

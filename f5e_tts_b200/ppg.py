@@ -155,9 +155,11 @@ class ASRModel:
         conf.update({k: v for k, v in encoder_conf.items() if k in conf})
         for key, want in (("input_layer", "conv2d"), ("pos_enc_layer_type", "rel_pos"), ("normalize_before", True),
                           ("concat_after", False), ("macaron_style", True), ("activation_type", "swish"),
-                          ("use_cnn_module", True), ("cnn_module_norm", "batch_norm"), ("use_emb", False)):
+                          ("use_cnn_module", True), ("use_emb", False)):
             if conf[key] != want:
                 raise NotImplementedError(f"f5e_tts_b200.ASRModel: {key}={conf[key]!r} is not implemented (only {want!r})")
+        if conf["cnn_module_norm"] not in ("batch_norm", "layer_norm"):
+            raise ValueError(f"cnn_module_norm must be 'batch_norm' or 'layer_norm', not {conf['cnn_module_norm']!r}")
         self.conf, self.input_dim = conf, input_dim
         self.dim, self.heads = conf["output_size"], conf["attention_heads"]
         if self.dim % self.heads or self.dim // self.heads != 64 or self.dim % 256:
@@ -227,9 +229,18 @@ class ASRModel:
             ly["wpos"] = g("self_attn.linear_pos.weight")
             ly["u"], ly["v"] = f32(g("self_attn.pos_bias_u")), f32(g("self_attn.pos_bias_v"))
             ly["wpw1"], ly["bpw1"] = b16(g("conv_module.pointwise_conv1.weight").view(2 * d, d)), f32(g("conv_module.pointwise_conv1.bias"))
-            s = g("conv_module.norm.weight") / torch.sqrt(g("conv_module.norm.running_var") + 1e-5)  # eval BatchNorm1d, folded
-            ly["wdw"] = f32(g("conv_module.depthwise_conv.weight").view(d, taps) * s[:, None])
-            ly["bdw"] = f32((g("conv_module.depthwise_conv.bias") - g("conv_module.norm.running_mean")) * s + g("conv_module.norm.bias"))
+            wd, bd = g("conv_module.depthwise_conv.weight").view(d, taps), g("conv_module.depthwise_conv.bias")
+            if self.conf["cnn_module_norm"] == "batch_norm":  # eval BatchNorm1d is affine per channel: folded into the conv
+                s = g("conv_module.norm.weight") / torch.sqrt(g("conv_module.norm.running_var") + 1e-5)
+                wd, bd = wd * s[:, None], (bd - g("conv_module.norm.running_mean")) * s + g("conv_module.norm.bias")
+                ly["ln_w"] = ly["ln_b"] = None
+            else:  # LayerNorm over channels: applied inside glu_dwconv
+                ly["ln_w"], ly["ln_b"] = f32(g("conv_module.norm.weight")), f32(g("conv_module.norm.bias"))
+            ly["wdw"], ly["bdw"] = f32(wd), f32(bd)
+            ly["pad"] = None
+            if self.conf["causal"]:  # convolution.py:104-113: the left context passes the biased pointwise conv and the GLU
+                bq = g("conv_module.pointwise_conv1.bias").to(torch.bfloat16).float()  # what the GEMM writes for a zero input row
+                ly["pad"] = f32(bq[:d] * torch.sigmoid(bq[d:]))
             ly["wpw2"], ly["bpw2"] = b16(g("conv_module.pointwise_conv2.weight").view(d, d)), f32(g("conv_module.pointwise_conv2.bias"))
             P["layers"].append(ly)
         self._plan = P
@@ -328,8 +339,8 @@ class ASRModel:
             x = ops.gemm(att, ly["wo"], bias=ly["bo"], residual=x)
             h = ln(x, ly["norm_conv"])  # :243-248
             g = ops.gemm(h, ly["wpw1"], bias=ly["bpw1"])
-            check(lib.f5e_glu_dwconv(ptr(g), ptr(ly["wdw"]), ptr(ly["bdw"]), ptr(t_out), ptr(conv), B, n_pad, d, taps, lpad, st),
-                  "f5e_glu_dwconv")
+            check(lib.f5e_glu_dwconv(ptr(g), ptr(ly["wdw"]), ptr(ly["bdw"]), ptr(t_out), ptr(conv), B, n_pad, d, taps, lpad,
+                                     ptr(ly["pad"]), ptr(ly["ln_w"]), ptr(ly["ln_b"]), f32c(1e-5), st), "f5e_glu_dwconv")
             x = ops.gemm(conv, ly["wpw2"], bias=ly["bpw2"], residual=x)
             h = ln(x, ly["norm_ff"])  # :254-263
             x = ops.gemm(ops.gemm(h, ly["fw1"], bias=ly["fb1"], act=_lib.ACT_SILU), ly["fw2"], bias=ly["fb2"], residual=x)

@@ -134,12 +134,15 @@ int f5e_subsample_conv(const float* feats, int64_t ld_feats, const int32_t* n_fr
 int f5e_relpos_prepare(void* qkv, int32_t ld_qkv, const float* pos, const float* u, const float* v, float* key_bias,
                        int32_t ld_bias, int32_t samples, int32_t n_pad, int32_t heads, void* stream);
 
-/* ConvolutionModule between its two pointwise convs (convolution.py:116-127): GLU over channels, depthwise Conv1d(taps)
- * with left_pad zeros on the left (symmetric: (taps - 1) / 2; causal: taps - 1), eval BatchNorm1d folded into w / b by
- * the caller, swish.  g bf16 [samples * n_pad, 2 C] (value | gate) -> out bf16 [samples * n_pad, C]; frames outside
- * [0, len[s]) read as zero (what a batch-1 call sees), rows >= len[s] are written as zeros. */
+/* ConvolutionModule between its two pointwise convs (convolution.py:104-127): GLU over channels, depthwise Conv1d(taps)
+ * with left_pad frames of left context (symmetric: (taps - 1) / 2; causal: taps - 1), norm, swish.
+ * g bf16 [samples * n_pad, 2 C] (value | gate) -> out bf16 [samples * n_pad, C].  The GLU output reads as zero at frames
+ * >= len[s] and as pad_val[c] at frames < 0 (NULL: zero; the causal module pads BEFORE its biased pointwise conv, so its left
+ * context is glu(bias): the caller passes that vector).  norm = eval BatchNorm1d: folded into w / b by the caller (ln_w NULL);
+ * norm = LayerNorm over channels: ln_w / ln_b fp32 [C], ln_eps, C <= 256.  Rows >= len[s] are written as zeros. */
 int f5e_glu_dwconv(const void* g, const float* w, const float* b, const int32_t* len, void* out, int32_t samples,
-                   int32_t n_pad, int32_t C, int32_t taps, int32_t left_pad, void* stream);
+                   int32_t n_pad, int32_t C, int32_t taps, int32_t left_pad, const float* pad_val, const float* ln_w,
+                   const float* ln_b, float ln_eps, void* stream);
 
 /* Grouped Conv1d(dim, dim, k=31, groups, padding=15) over frames, per sample, as a tcgen05 implicit GEMM with the
  * fused epilogue (bias, Mish, residual).  x: bf16 [samples*n_pad, dim] contiguous; w_packed: bf16 [31*dim, 64]

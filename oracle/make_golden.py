@@ -190,7 +190,7 @@ def case_chunk_text(name):
     print(f"[{name}] {len(rows)} cases")
 
 
-def case_ppg_conformer(name):
+def case_ppg_conformer(name, causal=False, cnn_norm="batch_norm"):
     """The reference's own wenet ConformerEncoder (ppg/wenet/transformer/encoder.py:403-495) + the content Linear of
     ASRModel (asr_model.py:78-79, 241), built the way init_asr_model does (asr_model.py:814-836; the decoder / CTC heads
     are not on the extract path) with random weights, on the reference's kaldiFbank features of seeded noise."""
@@ -198,11 +198,11 @@ def case_ppg_conformer(name):
     from f5_tts.ppg.wenet.transformer.cmvn import GlobalCMVN
     from f5_tts.ppg.wenet.transformer.encoder import ConformerEncoder
     from oracle import ppg_oracle as PO
-    cfg = PO.ConformerConfig(blocks=3)
+    cfg = PO.ConformerConfig(blocks=3, causal=causal, cnn_norm=cnn_norm)
     sd = PO.make_conformer_state_dict(cfg, seed=99)
     enc = ConformerEncoder(cfg.input_dim, global_cmvn=GlobalCMVN(sd["encoder.global_cmvn.mean"], sd["encoder.global_cmvn.istd"]),
                            output_size=cfg.dim, attention_heads=cfg.heads, linear_units=cfg.ffn, num_blocks=cfg.blocks,
-                           input_layer="conv2d", cnn_module_kernel=cfg.kernel).eval()
+                           input_layer="conv2d", cnn_module_kernel=cfg.kernel, causal=causal, cnn_module_norm=cnn_norm).eval()
     esd = {k[len("encoder."):]: v for k, v in sd.items() if k.startswith("encoder.")}
     missing, unexpected = enc.load_state_dict(esd, strict=False)
     missing = [k for k in missing if "num_batches_tracked" not in k and "linear_xs_embs" not in k and "concat_linear" not in k]
@@ -219,7 +219,8 @@ def case_ppg_conformer(name):
     got = PO.conformer_extract(cfg, sd, got_feats)
     print(f"{name}: fbank max abs {float((got_feats - feats[0]).abs().max()):.2e}; extract rel-L2 {rel(got, ref):.2e} "
           f"shape {tuple(ref.shape)} mask frames {int(mask.sum())}")
-    torch.save(dict(blocks=cfg.blocks, seed=99, wave=wave[0], feats=feats[0], ppg=ref), os.path.join(OUT, name + ".pt"))
+    torch.save(dict(blocks=cfg.blocks, seed=99, causal=causal, cnn_norm=cnn_norm, wave=wave[0], feats=feats[0], ppg=ref),
+               os.path.join(OUT, name + ".pt"))
 
 
 if __name__ == "__main__":
@@ -239,3 +240,4 @@ if __name__ == "__main__":
     case_resample("resample")
     case_chunk_text("chunk_text")
     case_ppg_conformer("ppg_conformer")
+    case_ppg_conformer("ppg_conformer_causal_ln", causal=True, cnn_norm="layer_norm")  # the streaming wenet recipe's conv module

@@ -85,6 +85,8 @@ class ConformerConfig:
     blocks: int = 12
     kernel: int = 15
     cmvn: bool = True
+    causal: bool = False            # convolution.py:39-45: left-only padding of kernel - 1 frames
+    cnn_norm: str = "batch_norm"    # convolution.py:58-64: "batch_norm" | "layer_norm" (the streaming wenet recipes use the latter)
 
 
 def make_conformer_state_dict(cfg: ConformerConfig, seed: int = 99) -> dict:
@@ -125,8 +127,9 @@ def make_conformer_state_dict(cfg: ConformerConfig, seed: int = 99) -> dict:
         sd[p + "conv_module.depthwise_conv.bias"] = r(d, std=0.1)
         sd[p + "conv_module.norm.weight"] = 1.0 + r(d, std=0.1)
         sd[p + "conv_module.norm.bias"] = r(d, std=0.1)
-        sd[p + "conv_module.norm.running_mean"] = r(d, std=0.1)
-        sd[p + "conv_module.norm.running_var"] = 0.5 + torch.rand(d, generator=g)
+        if cfg.cnn_norm == "batch_norm":
+            sd[p + "conv_module.norm.running_mean"] = r(d, std=0.1)
+            sd[p + "conv_module.norm.running_var"] = 0.5 + torch.rand(d, generator=g)
         sd[p + "conv_module.pointwise_conv2.weight"] = r(d, d, 1, std=d ** -0.5)
         sd[p + "conv_module.pointwise_conv2.bias"] = r(d, std=0.1)
         for nm in ("norm_ff", "norm_mha", "norm_ff_macaron", "norm_conv", "norm_final"):
@@ -184,11 +187,16 @@ def conformer_extract(cfg: ConformerConfig, sd: dict, feats: torch.Tensor, dtype
         x = x + F.linear(a, W(p + "self_attn.linear_out.weight"), W(p + "self_attn.linear_out.bias"))
         # :243-248 convolution module (convolution.py:99-134): pointwise -> GLU -> depthwise k -> BatchNorm(eval) -> swish -> pointwise
         h = ln(x, p + "norm_conv").t()[None]
+        if cfg.causal:  # convolution.py:104-106: the left context is padded BEFORE the biased pointwise conv, so it is glu(bias), not 0
+            h = F.pad(h, (cfg.kernel - 1, 0))
         h = F.glu(F.conv1d(h, W(p + "conv_module.pointwise_conv1.weight"), W(p + "conv_module.pointwise_conv1.bias")), dim=1)
         h = F.conv1d(h, W(p + "conv_module.depthwise_conv.weight"), W(p + "conv_module.depthwise_conv.bias"),
-                     padding=(cfg.kernel - 1) // 2, groups=d)
-        h = F.batch_norm(h, W(p + "conv_module.norm.running_mean"), W(p + "conv_module.norm.running_var"),
-                         W(p + "conv_module.norm.weight"), W(p + "conv_module.norm.bias"), False, 0.0, 1e-5)
+                     padding=0 if cfg.causal else (cfg.kernel - 1) // 2, groups=d)
+        if cfg.cnn_norm == "layer_norm":
+            h = F.layer_norm(h.transpose(1, 2), (d,), W(p + "conv_module.norm.weight"), W(p + "conv_module.norm.bias"), 1e-5).transpose(1, 2)
+        else:
+            h = F.batch_norm(h, W(p + "conv_module.norm.running_mean"), W(p + "conv_module.norm.running_var"),
+                             W(p + "conv_module.norm.weight"), W(p + "conv_module.norm.bias"), False, 0.0, 1e-5)
         h = F.conv1d(swish(h), W(p + "conv_module.pointwise_conv2.weight"), W(p + "conv_module.pointwise_conv2.bias"))
         x = x + h[0].t()
         # :254-263 feed-forward, final norm

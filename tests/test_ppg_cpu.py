@@ -61,3 +61,14 @@ def test_oracle_conformer_matches_reference_golden():
     assert rel < 1e-5, rel
     ppg, n = PO.audio_to_ppg(cfg, sd, fx["wave"])
     assert n == got.shape[0] and ppg.shape == got.shape
+
+
+def test_oracle_conformer_causal_layernorm_matches_reference_golden():
+    """The streaming recipe's conv module (causal, LayerNorm): the causal left context is glu(bias), not zero
+    (convolution.py:104-113 pads before the biased pointwise conv) - the reference golden pins that."""
+    fx = torch.load(os.path.join(os.path.dirname(__file__), "golden", "ppg_conformer_causal_ln.pt"))
+    cfg = PO.ConformerConfig(blocks=fx["blocks"], causal=fx["causal"], cnn_norm=fx["cnn_norm"])
+    sd = PO.make_conformer_state_dict(cfg, seed=fx["seed"])
+    got = PO.conformer_extract(cfg, sd, fx["feats"])
+    rel = ((got - fx["ppg"]).norm() / fx["ppg"].norm()).item()
+    assert rel < 1e-5, rel

@@ -83,15 +83,17 @@ def make_model(cfg, sd, dev):
     from f5e_tts_b200.ppg import ASRModel
     sd16 = {k: (v.to(torch.bfloat16).float() if v.dim() >= 2 and "global_cmvn" not in k else v) for k, v in sd.items()}
     m = ASRModel(cfg.input_dim, output_size=cfg.dim, attention_heads=cfg.heads, linear_units=cfg.ffn, num_blocks=cfg.blocks,
-                 cnn_module_kernel=cfg.kernel)
+                 cnn_module_kernel=cfg.kernel, causal=cfg.causal, cnn_module_norm=cfg.cnn_norm)
     return m.load_state_dict(sd16).to(dev), sd16
 
 
-def test_conformer_vs_reference_golden(cuda_dev):
-    """The product against the output of the reference's own wenet modules (tests/golden/ppg_conformer.pt)."""
+@pytest.mark.parametrize("fixture", ["ppg_conformer", "ppg_conformer_causal_ln"])
+def test_conformer_vs_reference_golden(cuda_dev, fixture):
+    """The product against the output of the reference's own wenet modules (tests/golden/ppg_conformer*.pt): the default conv
+    module (symmetric, BatchNorm) and the streaming recipe's (causal, LayerNorm)."""
     from f5e_tts_b200.ppg import PPGModelWapper
-    fx = torch.load(os.path.join(os.path.dirname(__file__), "golden", "ppg_conformer.pt"))
-    cfg = PO.ConformerConfig(blocks=fx["blocks"])
+    fx = torch.load(os.path.join(os.path.dirname(__file__), "golden", fixture + ".pt"))
+    cfg = PO.ConformerConfig(blocks=fx["blocks"], causal=fx.get("causal", False), cnn_norm=fx.get("cnn_norm", "batch_norm"))
     sd = PO.make_conformer_state_dict(cfg, seed=fx["seed"])
     model, sd16 = make_model(cfg, sd, cuda_dev)
     wrap = PPGModelWapper(model=model, device=cuda_dev)
@@ -193,7 +195,8 @@ def test_kernels_of_the_conformer(cuda_dev):
     ln_ = torch.tensor([50, 23], dtype=torch.int32, device=cuda_dev)
     out = torch.empty(S * n_pad, Cc, device=cuda_dev, dtype=torch.bfloat16)
     for lpad in (7, 14):
-        check(lib.f5e_glu_dwconv(ptr(gin), ptr(wd), ptr(bd), ptr(ln_), ptr(out), S, n_pad, Cc, taps, lpad, stream_ptr()), "f5e_glu_dwconv")
+        check(lib.f5e_glu_dwconv(ptr(gin), ptr(wd), ptr(bd), ptr(ln_), ptr(out), S, n_pad, Cc, taps, lpad, None, None, None,
+                                 C.c_float(0.0), stream_ptr()), "f5e_glu_dwconv")
         for s_ in range(S):
             n = int(ln_[s_])
             x = F.glu(gin.view(S, n_pad, 2 * Cc)[s_, :n].float(), dim=-1).t()[None]
@@ -201,6 +204,17 @@ def test_kernels_of_the_conformer(cuda_dev):
             y = (y * torch.sigmoid(y))[0].t()
             got = out.view(S, n_pad, Cc)[s_].float()
             assert rel_l2(got[:n], y) < 1e-2 and (float(got[n:].abs().max()) == 0.0 if n < n_pad else True)
+    # causal left context = a per-channel constant, LayerNorm over channels before the swish
+    pv, lw, lb = torch.randn(Cc, generator=g).to(cuda_dev), (1 + 0.1 * torch.randn(Cc, generator=g)).to(cuda_dev), torch.randn(Cc, generator=g).to(cuda_dev)
+    check(lib.f5e_glu_dwconv(ptr(gin), ptr(wd), ptr(bd), ptr(ln_), ptr(out), S, n_pad, Cc, taps, taps - 1, ptr(pv), ptr(lw), ptr(lb),
+                             C.c_float(1e-5), stream_ptr()), "f5e_glu_dwconv")
+    for s_ in range(S):
+        n = int(ln_[s_])
+        x = F.glu(gin.view(S, n_pad, 2 * Cc)[s_, :n].float(), dim=-1).t()
+        x = torch.cat([pv[:, None].expand(Cc, taps - 1), x], dim=1)[None]
+        y = F.layer_norm(F.conv1d(x, wd[:, None], bd, groups=Cc)[0].t(), (Cc,), lw, lb, 1e-5)
+        y = y * torch.sigmoid(y)
+        assert rel_l2(out.view(S, n_pad, Cc)[s_, :n].float(), y) < 1e-2
 
 
 def test_voice_conversion_end_to_end(cuda_dev):
