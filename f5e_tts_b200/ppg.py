@@ -171,6 +171,7 @@ class ASRModel:
         self._pos: dict = {}
         self._graphs: dict = {}
         self.use_cuda_graph = False  # extension: replay one captured graph per (batch, frames) shape
+        self.max_cached_graphs = 8
 
     def load_state_dict(self, state_dict: dict, strict: bool = False):
         need = ["encoder.embed.conv.0.weight", "encoder.embed.out.0.weight", "encoder.after_norm.weight", "linear.weight"]
@@ -296,6 +297,8 @@ class ASRModel:
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
                 so = self._encode(sf, sl)
+            if len(self._graphs) >= self.max_cached_graphs:  # every graph pins its activations: keep the most recent shapes only
+                self._graphs.pop(next(iter(self._graphs)))
             self._graphs[key] = (graph, sf, sl, so)
         graph, sf, sl, so = self._graphs[key]
         sf.copy_(feats)
