@@ -26,6 +26,14 @@ constexpr int GEMM_STAGING_BYTES = 4096;  // 32 rows x 128 bytes per epilogue wa
 #ifndef GEMM_PAIR
 #define GEMM_PAIR 1                       // 0: never use CTA pairs (A/B switch for measurements)
 #endif
+// 1: 256 x 128 pair tiles where 256 x 256 tiles quantise badly over the 74 pairs (out-projection / FF2 at the bench shape).
+// Measured 8.7 % slower per step, so it is off; kept as a switch for the next look at it.
+#ifndef GEMM_NARROW_PAIR
+#define GEMM_NARROW_PAIR 0
+#endif
+#ifndef GEMM_NARROW_STAGES
+#define GEMM_NARROW_STAGES 6
+#endif
 
 // CG = CTAs per tile: 1, or 2 = a CTA PAIR (cta_group::2) computing a 256 x BN tile; every CTA then stages only half of
 // the W tile, which halves the shared-memory operand traffic per MMA: a single-CTA 128x256 tile needs 192 B/clk of
@@ -438,6 +446,10 @@ int gemm_configure() {
                                       GemmSmem<256, 5, 2>::TOTAL));
   F5E_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<128, 6, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       GemmSmem<128, 6, 1>::TOTAL));
+#if GEMM_NARROW_PAIR
+  F5E_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<128, GEMM_NARROW_STAGES, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      GemmSmem<128, GEMM_NARROW_STAGES, 2>::TOTAL));
+#endif
   return 0;
 }
 
@@ -467,13 +479,26 @@ int gemm_bf16(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloa
   }
   // CTA pairs when there are enough 256-row tiles to fill the 74 pairs; each CTA then loads a 128-row half of the W tile
   const bool pair = wide && GEMM_PAIR && ((M + 255) / 256) * ((N + 255) / 256) >= num_sms() / 2;
-  rc = make_tmap_2d(&tmB, W, 2, (uint64_t)K, (uint64_t)N, (uint64_t)ldw * 2, GEMM_BK, (wide && !pair) ? 256 : 128);
+#if GEMM_NARROW_PAIR
+  auto wave_eff = [&](int bn) {
+    const long long t = (long long)((M + 255) / 256) * ((N + bn - 1) / bn);
+    const long long slots = num_sms() / 2, waves = (t + slots - 1) / slots;
+    return (double)t / (double)(waves * slots);
+  };
+  const bool narrow = pair && N % 128 == 0 && wave_eff(128) > wave_eff(256) + 0.04;
+#else
+  const bool narrow = false;
+#endif
+  rc = make_tmap_2d(&tmB, W, 2, (uint64_t)K, (uint64_t)N, (uint64_t)ldw * 2, GEMM_BK, narrow ? 64 : ((wide && !pair) ? 256 : 128));
   if (rc) return rc;
   if (ep.out_f32)
     rc = make_tmap_2d(&tmC, ep.out, 4, (uint64_t)N, (uint64_t)M, (uint64_t)ep.ldo * 4, 32, 32);
   else
     rc = make_tmap_2d(&tmC, ep.out, 2, (uint64_t)(ep.split3 > 0 ? 3 * ep.split3 : N), (uint64_t)M, (uint64_t)ep.ldo * 2, 64, 32);
   if (rc) return rc;
+#if GEMM_NARROW_PAIR
+  if (narrow) return launch_gemm<128, GEMM_NARROW_STAGES, 2>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
+#endif
   if (pair) return launch_gemm<256, 5, 2>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
   if (wide) return launch_gemm<256, 4, 1>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
   return launch_gemm<128, 6, 1>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
