@@ -489,7 +489,15 @@ int gemm_bf16(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloa
 #else
   const bool narrow = false;
 #endif
-  rc = make_tmap_2d(&tmB, W, 2, (uint64_t)K, (uint64_t)N, (uint64_t)ldw * 2, GEMM_BK, narrow ? 64 : ((wide && !pair) ? 256 : 128));
+  // Latency shapes (batch 1: M ~ 2 k rows): 128 x 256 tiles leave most SMs idle (N = 1024: 60 tiles on 148 SMs); 128 x 128 tiles fill
+  // them.  Only when the wide tiling cannot occupy the machine - at full occupancy the wide tile is the faster one.
+#ifndef GEMM_SMALL_M_TILES
+#define GEMM_SMALL_M_TILES 1
+#endif
+  const long long tiles_wide = (long long)((M + GEMM_BM - 1) / GEMM_BM) * ((N + 255) / 256);
+  const bool small = GEMM_SMALL_M_TILES && wide && !pair && tiles_wide < num_sms() && N % 128 == 0;
+  rc = make_tmap_2d(&tmB, W, 2, (uint64_t)K, (uint64_t)N, (uint64_t)ldw * 2, GEMM_BK,
+                    narrow ? 64 : ((wide && !pair && !small) ? 256 : 128));
   if (rc) return rc;
   if (ep.out_f32)
     rc = make_tmap_2d(&tmC, ep.out, 4, (uint64_t)N, (uint64_t)M, (uint64_t)ep.ldo * 4, 32, 32);
@@ -500,7 +508,7 @@ int gemm_bf16(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloa
   if (narrow) return launch_gemm<128, GEMM_NARROW_STAGES, 2>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
 #endif
   if (pair) return launch_gemm<256, 5, 2>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
-  if (wide) return launch_gemm<256, 4, 1>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
+  if (wide && !small) return launch_gemm<256, 4, 1>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
   return launch_gemm<128, 6, 1>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
 }
 
