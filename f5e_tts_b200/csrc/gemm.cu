@@ -494,8 +494,13 @@ int gemm_bf16(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloa
 #ifndef GEMM_SMALL_M_TILES
 #define GEMM_SMALL_M_TILES 1
 #endif
-  const long long tiles_wide = (long long)((M + GEMM_BM - 1) / GEMM_BM) * ((N + 255) / 256);
-  const bool small = GEMM_SMALL_M_TILES && wide && !pair && tiles_wide < num_sms() && N % 128 == 0;
+  auto fill = [&](int bn) {  // fraction of SM-waves doing work under the static tile schedule
+    const long long t = (long long)((M + GEMM_BM - 1) / GEMM_BM) * ((N + bn - 1) / bn);
+    const long long waves = (t + num_sms() - 1) / num_sms();
+    return (double)t / (double)(waves * num_sms());
+  };
+  // the 128 x 128 tile is smem-bandwidth-bound (~0.85 of the wide tile's rate): it must win by more than that
+  const bool small = GEMM_SMALL_M_TILES && wide && !pair && N % 128 == 0 && 0.85 * fill(128) > fill(256);
   rc = make_tmap_2d(&tmB, W, 2, (uint64_t)K, (uint64_t)N, (uint64_t)ldw * 2, GEMM_BK,
                     narrow ? 64 : ((wide && !pair && !small) ? 256 : 128));
   if (rc) return rc;
