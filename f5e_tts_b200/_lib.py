@@ -5,11 +5,12 @@ There is deliberately no fallback: if the library is missing or a call fails, a 
 from __future__ import annotations
 
 import ctypes as C
-import os  # noqa: F401
+import os
 from pathlib import Path
 
 _HERE = Path(__file__).resolve().parent
-_LIB_PATH = _HERE / "libf5e_b200.so"
+_SUFFIX = os.environ.get("F5E_LIB_SUFFIX", "")  # developer knob, see build.py
+_LIB_PATH = _HERE / (f"libf5e_b200_{_SUFFIX}.so" if _SUFFIX else "libf5e_b200.so")
 _lib = None
 
 ACT_NONE, ACT_GELU_TANH, ACT_GELU_ERF, ACT_MISH, ACT_RELU, ACT_SILU = range(6)

@@ -11,13 +11,15 @@ from pathlib import Path
 
 HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
-LIB = HERE / "libf5e_b200.so"
+# F5E_LIB_SUFFIX (developer knob): build / load libf5e_b200_<suffix>.so with F5E_NVCC_FLAGS beside the product library,
+# so several compile-time variants of a kernel can travel to the GPU box in one snapshot (tools/attn_lab.py).
+SUFFIX = os.environ.get("F5E_LIB_SUFFIX", "")
+LIB = HERE / (f"libf5e_b200_{SUFFIX}.so" if SUFFIX else "libf5e_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
-    "-Xcompiler", "-fPIC", "--use_fast_math_placeholder",
-]
-FLAGS = [f for f in FLAGS if f != "--use_fast_math_placeholder"] + os.environ.get("F5E_NVCC_FLAGS", "").split()
+    "-Xcompiler", "-fPIC",
+] + os.environ.get("F5E_NVCC_FLAGS", "").split()
 
 
 def _sources():
@@ -35,7 +37,7 @@ def _stamp() -> str:
 
 
 def build(force: bool = False, verbose: bool = False) -> Path:
-    stamp_file = HERE / "csrc" / ".build_stamp"
+    stamp_file = HERE / "csrc" / (".build_stamp" + ("_" + SUFFIX if SUFFIX else ""))
     stamp = _stamp()
     if not force and LIB.exists() and stamp_file.exists() and stamp_file.read_text() == stamp:
         return LIB
@@ -43,7 +45,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         if LIB.exists():  # GPU box without the sources changed: use the shipped library
             return LIB
         raise RuntimeError(f"nvcc not found at {NVCC} and no prebuilt {LIB}")
-    objdir = HERE / "build"
+    objdir = HERE / ("build_" + SUFFIX if SUFFIX else "build")
     objdir.mkdir(exist_ok=True)
 
     def compile_one(src: Path) -> Path:

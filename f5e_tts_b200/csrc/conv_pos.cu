@@ -71,7 +71,7 @@ conv_pos_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
   const uint32_t tmem_base = *tmem_holder;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {  // see gemm.cu: elect.sync lets the compiler issue UTMALDG / UTCHMMA without a serialisation loop
       int stage = 0, it = 0;
       uint32_t phase = 0;
       for (int u = blockIdx.x; u < num_units; u += gridDim.x, ++it) {
@@ -92,7 +92,7 @@ conv_pos_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t idesc = umma_idesc(kFmtBF16, CV_BM, (uint32_t)cpg, 0, 0);
       const int ksteps = (cpg + 15) / 16;
       int stage = 0, it = 0;

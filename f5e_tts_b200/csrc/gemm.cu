@@ -56,12 +56,14 @@ __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, const vo
                : "memory");
 }
 
-// Send the warp's staged 32 x 128-byte block to global memory (plain store or reduce-add); lane 0 issues.
+// Send the warp's staged 32 x 128-byte block to global memory (plain store or reduce-add).  ONE elected thread issues:
+// elect.sync picks the same leader for the same (full) member mask every time, so the bulk groups it commits are the
+// ones it later waits on, and - unlike `lane == 0` - the compiler issues UTMASTG / UTMAREDG without a serialisation loop.
 __device__ __forceinline__ void staging_flush(const CUtensorMap* tmC, const uint8_t* stage, int c0, int c1, bool accumulate,
                                               int lane) {
   fence_proxy_async_smem();
   __syncwarp();
-  if (lane == 0) {
+  if (elect_one()) {
     if (accumulate) tma_reduce_add_2d(tmC, stage, c0, c1);
     else tma_store_2d(tmC, stage, c0, c1);
     tma_store_commit();
@@ -70,7 +72,7 @@ __device__ __forceinline__ void staging_flush(const CUtensorMap* tmC, const uint
 // The staging block may be rewritten once the previous bulk store has finished READING it.
 template <int NBUF>
 __device__ __forceinline__ void staging_acquire(int lane) {
-  if (lane == 0) tma_store_wait_read<NBUF - 1>();  // the block flushed NBUF flushes ago has been read out
+  if (elect_one()) tma_store_wait_read<NBUF - 1>();  // the block flushed NBUF flushes ago has been read out
   __syncwarp();
 }
 // 16-byte slot j (0..7) of row r inside a 128B-swizzled 32-row block
@@ -129,7 +131,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const uint32_t tmem_base = *tmem_holder;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {  // elect.sync, not `lane == 0`: the compiler then knows ONE thread is active and issues
+                        // UTMALDG / UTCHMMA directly instead of wrapping each in an ELECT / BRA.U.ANY loop
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
@@ -157,7 +160,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && rank == 0) {
+    if (rank == 0 && elect_one()) {
       constexpr uint32_t idesc = umma_idesc(kFmtBF16, TILE_M, BN, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
@@ -375,7 +378,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) {
+          if (elect_one()) {
             tma_store_2d(&tmC, stage_buf, col0, row0);
             tma_store_2d(&tmC, stage_buf, col0 + ep.split3, row0);
             tma_store_commit();
@@ -402,7 +405,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
-    if (lane == 0) tma_store_wait<0>();  // every bulk store has completed before the CTA's shared memory goes away
+    __syncwarp();
+    if (elect_one()) tma_store_wait<0>();  // every bulk store has completed before the CTA's shared memory goes away
   }
 
   tc_fence_before();

@@ -203,14 +203,20 @@ class DiT(nn.Module):
     def clear_cache(self):  # backbones/dit.py:293-294
         self.text_cond = self.text_uncond = None
 
-    # any parameter change invalidates the packed plan
+    # Any parameter change invalidates the packed plan: `_apply` (.to / .half / .cuda), `load_state_dict` on this module
+    # OR on a parent (the reference's load_checkpoint loads into the CFM: infer/utils_infer.py:196-234, which reaches the
+    # children through _load_from_state_dict only), and in-place updates (EMA copy_, optimizer steps), which bump the
+    # parameters' version counters.
     def _apply(self, fn, *a, **k):
         self._plan, self._ws = None, {}
         return super()._apply(fn, *a, **k)
 
-    def load_state_dict(self, *a, **k):
+    def _load_from_state_dict(self, *a, **k):
         self._plan, self._ws = None, {}
-        return super().load_state_dict(*a, **k)
+        return super()._load_from_state_dict(*a, **k)
+
+    def _param_versions(self):
+        return tuple(p._version for p in self.parameters()) + tuple(b._version for b in self.buffers())
 
     def forward(self, *a, **k):
         raise NotImplementedError("f5e_tts_b200.DiT is inference-only: use .sample (training stays with the reference)")
@@ -218,7 +224,9 @@ class DiT(nn.Module):
     # ---- packed weights ("plan") ------------------------------------------------------------------
     def _get_plan(self):
         if self._plan is not None:
-            return self._plan
+            if self._plan.versions == self._param_versions():
+                return self._plan
+            self._plan, self._ws = None, {}
         dev = self.proj_out.weight.device
         if dev.type != "cuda":
             raise RuntimeError("f5e_tts_b200.DiT has no CPU path: move the module to a B200 (cuda) device")
@@ -315,6 +323,15 @@ class DiT(nn.Module):
                 w = conv.weight.detach().float().to(dev) * s[:, None, None]                # fold eval-mode BatchNorm
                 b = (conv.bias.detach().float().to(dev) - bn.running_mean.detach().float().to(dev)) * s + bn.bias.detach().float().to(dev)
                 P.ppg["convs"].append((bf(w.permute(0, 2, 1).reshape(w.shape[0], -1)), f32(b)))  # [co, tap*C + ci]
+        P.versions = self._param_versions()
+        pd = self.proj_out.weight.dtype
+        if pd != torch.bfloat16 and not getattr(DiT, "_warned_dtype", False):
+            # the reference's load_checkpoint casts to fp16 on the GPU (infer/utils_infer.py:185-194); see DESIGN.md 2.
+            import warnings
+            warnings.warn(f"f5e_tts_b200.DiT: parameters are {pd}; the sm_100a kernels compute in bf16 with fp32 accumulation "
+                          "(weights are packed to bf16 once), the ODE state / noise / time grid keep the module dtype",
+                          stacklevel=3)
+            DiT._warned_dtype = True
         self._plan = P
         return P
 
@@ -403,6 +420,10 @@ class DiT(nn.Module):
     @torch.no_grad()
     def sample(self, x, cond, text, ppg, time, drop_audio_cond, drop_text, drop_ppg, mask=None):
         """backbones/dit.py:417-472."""
+        with _SOLVE_LOCK:  # one plan / workspace per model: a direct call must not interleave with a running CFM solve
+            return self._sample_locked(x, cond, text, ppg, time, drop_audio_cond, drop_text, drop_ppg, mask)
+
+    def _sample_locked(self, x, cond, text, ppg, time, drop_audio_cond, drop_text, drop_ppg, mask):
         P = self._get_plan()
         B, N = x.shape[0], x.shape[1]
         dev = P.table.device
@@ -478,7 +499,13 @@ class CFM(nn.Module):
         self.use_cuda_graph = False       # capture the whole Euler loop in one CUDA graph launch
         self.store_trajectory = True      # False: return only [y0, y1] instead of steps+1 states
         self.emulate_lowp_state = False   # True: round the ODE state to bf16 every step like a bf16 reference run
-        self.pack_valid_rows = True       # batch > 1: run the DiT blocks on valid frames only (padding costs no FLOPs)
+        # batch > 1: run the DiT blocks on the valid frames only (padding costs no FLOPs).  The state of PADDED frames is
+        # then frozen at y0 = 0, whereas the reference's padded frames evolve with every Euler step and leak through the two
+        # unmasked k=31 ConvPositionEmbedding convs into the last <= 30 valid frames of every shorter sample.
+        # None (default) = pack only where that is exact: `isolate_samples` (padded frames never reach a valid one) or a
+        # batch whose samples all have the same length.  True = always pack (throughput knob; the deviation is confined to
+        # those tail frames and measured in tests/test_parity_gpu.py::test_packed_rows_tail_deviation), False = never.
+        self.pack_valid_rows = None
         # True: a sample's result does not depend on what it is batched with - padded frames are zeroed at the inputs of
         # the ConvPositionEmbedding convs and the text / PPG embedders run per sample at the sample's own length, so a
         # padded batch reproduces the batch-1 solves of infer/utils_infer.py:474-482 (pipeline.infer_batch_process).
@@ -637,9 +664,14 @@ class CFM(nn.Module):
         mod = dit._modulation(t[:-1])
         klen = duration.to(torch.int32).repeat(nb).contiguous() if batch > 1 else None
         # batch > 1: the DiT blocks run on the valid frames only (no FLOPs on padding)
-        pack, pack_keep = (make_packing(klen, N) if (klen is not None and self.pack_valid_rows) else (None, None))
+        want_pack = self.pack_valid_rows
+        if want_pack is None:
+            want_pack = isolate or bool((duration == max_duration).all())
+        pack, pack_keep = (make_packing(klen, N) if (klen is not None and want_pack) else (None, None))
         y = y0.float().contiguous()
-        traj = torch.empty(steps, B, N, md, device=y.device, dtype=torch.float32) if self.store_trajectory else None
+        traj = None
+        if self.store_trajectory:  # a packed solve writes the valid rows only: padded rows keep y0 there (zeros)
+            traj = (torch.zeros if pack is not None else torch.empty)(steps, B, N, md, device=y.device, dtype=torch.float32)
         dt_arr = (C.c_float * steps)(*dts)
         check(_lib.load().f5e_ode_solve_guided(
             C.byref(P.model), C.byref(buf), ptr(y), ptr(mod), P.mod_size, dt_arr, steps, C.byref(guidance), ptr(klen), B, N,

@@ -164,23 +164,46 @@ def get_inference_prompt(metainfo, speed=1.0, text_converter=None, target_sample
     ref_rms_all, ref_mel_all, ref_len_all = _prepare_references(metainfo, dev, slab, target_sample_rate, n_fft, win_length,
                                                                n_mel_channels, hop_length, mel_spec_type, target_rms)
     # ---- text, durations, buckets: host integer logic, identical to the reference ----
+    def fields(i, row):
+        prompt_text = row[1]
+        if len(prompt_text[-1].encode("utf-8")) == 1:
+            prompt_text = prompt_text + " "
+        text = [prompt_text + row[3]]
+        return prompt_text, (ref_rms_all[i], ref_mel_all[i], ref_len_all[i], text_converter(text) if text_converter is not None else text)
+
+    def emit(utts, total_mel_lens, cols):
+        ref_rms_list, ref_mels, ref_mel_lens, texts = cols
+        return (utts, ref_rms_list, _pad_ref_mels(ref_mels), ref_mel_lens, total_mel_lens, [t for tl in texts for t in tl])
+
+    return _bucket_batches(metainfo, ref_len_all, fields, emit, speed, target_sample_rate, hop_length, use_truth_duration,
+                           infer_batch_size, num_buckets, min_secs, max_secs)
+
+
+def _pad_ref_mels(ref_mels):
+    T = max(m.shape[-1] for m in ref_mels)
+    return torch.stack([torch.nn.functional.pad(m, (0, T - m.shape[-1]), value=0) for m in ref_mels]).permute(0, 2, 1)
+
+
+def _bucket_batches(metainfo, ref_len_all, fields, emit, speed, target_sample_rate, hop_length, use_truth_duration,
+                    infer_batch_size, num_buckets, min_secs, max_secs):
+    """The duration estimate / bucket / flush / shuffle loop that get_inference_prompt (eval/utils_eval.py:131-219) and
+    get_vc_inference_prompt (:322-397) share: host integer logic whose bucket contents and order must equal the reference's.
+    fields(i, row) -> (prompt_text used for the duration estimate, per-utterance columns); emit(utts, total_mel_lens, columns)
+    -> the tuple of one flushed batch."""
     prompts_all = []
     min_tokens = min_secs * target_sample_rate // hop_length
     max_tokens = max_secs * target_sample_rate // hop_length
     batch_accum = [0] * num_buckets
-    utts, ref_rms_list, ref_mels, ref_mel_lens, total_mel_lens, final_text_list = ([[] for _ in range(num_buckets)] for _ in range(6))
+    utts, total_mel_lens = [[] for _ in range(num_buckets)], [[] for _ in range(num_buckets)]
+    cols = [None] * num_buckets
 
     def flush(b):
-        T = max(m.shape[-1] for m in ref_mels[b])
-        padded = torch.stack([torch.nn.functional.pad(m, (0, T - m.shape[-1]), value=0) for m in ref_mels[b]]).permute(0, 2, 1)
-        prompts_all.append((utts[b], ref_rms_list[b], padded, ref_mel_lens[b], total_mel_lens[b], final_text_list[b]))
+        prompts_all.append(emit(utts[b], total_mel_lens[b], cols[b]))
+        batch_accum[b], utts[b], total_mel_lens[b], cols[b] = 0, [], [], None
 
     for i, row in enumerate(metainfo):
-        utt, prompt_text, _, gt_text = row[0], row[1], row[2], row[3]
-        if len(prompt_text[-1].encode("utf-8")) == 1:
-            prompt_text = prompt_text + " "
-        text = [prompt_text + gt_text]
-        text_list = text_converter(text) if text_converter is not None else text
+        utt, gt_text = row[0], row[3]
+        prompt_text, item = fields(i, row)
         ref_mel_len = ref_len_all[i]
         if use_truth_duration:
             gt_wave, gt_sr = row[4]
@@ -194,17 +217,15 @@ def get_inference_prompt(metainfo, speed=1.0, text_converter=None, target_sample
         assert min_tokens <= total_mel_len <= max_tokens, (
             f"Audio {utt} has duration {total_mel_len * hop_length // target_sample_rate}s out of range [{min_secs}, {max_secs}].")
         b = math.floor((total_mel_len - min_tokens) / (max_tokens - min_tokens + 1) * num_buckets)
+        if cols[b] is None:
+            cols[b] = tuple([] for _ in item)
         utts[b].append(utt)
-        ref_rms_list[b].append(ref_rms_all[i])
-        ref_mels[b].append(ref_mel_all[i])
-        ref_mel_lens[b].append(ref_mel_len)
         total_mel_lens[b].append(total_mel_len)
-        final_text_list[b].extend(text_list)
+        for c, v in zip(cols[b], item):
+            c.append(v)
         batch_accum[b] += total_mel_len
         if batch_accum[b] >= infer_batch_size:
             flush(b)
-            batch_accum[b] = 0
-            utts[b], ref_rms_list[b], ref_mels[b], ref_mel_lens[b], total_mel_lens[b], final_text_list[b] = [], [], [], [], [], []
     for b, frames in enumerate(batch_accum):
         if frames > 0:
             flush(b)
@@ -255,51 +276,17 @@ def get_vc_inference_prompt(metainfo, ppg_model, speed=1.0, target_sample_rate=T
                 t = (int(1 + (2 * int(out_lens[r]) - 400) // 160) - 1) // 2  # frames the batch-1 call of the reference returns
                 ppg_all[i], ppg_len_all[i] = ppg[r, :t], int(true_len[r])
     # ---- durations, buckets: host integer logic, identical to the reference ----
-    prompts_all = []
-    min_tokens = min_secs * target_sample_rate // hop_length
-    max_tokens = max_secs * target_sample_rate // hop_length
-    batch_accum = [0] * num_buckets
-    utts, ref_rms_list, ref_mels, ref_mel_lens, total_mel_lens, ppg_list, ppg_lens = ([[] for _ in range(num_buckets)] for _ in range(7))
+    def fields(i, row):  # the VC loop estimates the duration on the RAW prompt text (no space appended, :350-357)
+        return row[1], (ref_rms_all[i], ref_mel_all[i], ref_len_all[i], ppg_all[i], ppg_len_all[i])
 
-    def flush(b):
-        T = max(m.shape[-1] for m in ref_mels[b])
-        padded = torch.stack([torch.nn.functional.pad(m, (0, T - m.shape[-1]), value=0) for m in ref_mels[b]]).permute(0, 2, 1)
-        P = max(ppg_lens[b])  # padded_ppg_batch (:226-242): truncate / pad every PPG to the longest ppg_length of the batch
-        pp = torch.stack([torch.nn.functional.pad(p[:P], (0, 0, 0, P - min(p.shape[0], P)), value=0) for p in ppg_list[b]])
-        prompts_all.append((utts[b], ref_rms_list[b], padded, ref_mel_lens[b], total_mel_lens[b], pp))
+    def emit(utts, total_mel_lens, cols):
+        ref_rms_list, ref_mels, ref_mel_lens, ppg_list, ppg_lens = cols
+        P = max(ppg_lens)  # padded_ppg_batch (:226-242): truncate / pad every PPG to the longest ppg_length of the batch
+        pp = torch.stack([torch.nn.functional.pad(p[:P], (0, 0, 0, P - min(p.shape[0], P)), value=0) for p in ppg_list])
+        return (utts, ref_rms_list, _pad_ref_mels(ref_mels), ref_mel_lens, total_mel_lens, pp)
 
-    for i, row in enumerate(metainfo):
-        utt, prompt_text, gt_text = row[0], row[1], row[3]
-        ref_mel_len = ref_len_all[i]
-        if use_truth_duration:
-            gt_wave, gt_sr = row[4]
-            total_mel_len = ref_mel_len + int(_resampled_length(gt_wave.shape[-1], gt_sr, target_sample_rate) / hop_length / speed)
-        else:
-            ref_text_len = len(prompt_text.encode("utf-8"))
-            gen_text_len = len(gt_text.encode("utf-8"))
-            total_mel_len = ref_mel_len + int(ref_mel_len / ref_text_len * gen_text_len / speed)
-        assert infer_batch_size > 0, "infer_batch_size should be greater than 0."
-        assert min_tokens <= total_mel_len <= max_tokens, (
-            f"Audio {utt} has duration {total_mel_len * hop_length // target_sample_rate}s out of range [{min_secs}, {max_secs}].")
-        b = math.floor((total_mel_len - min_tokens) / (max_tokens - min_tokens + 1) * num_buckets)
-        utts[b].append(utt)
-        ref_rms_list[b].append(ref_rms_all[i])
-        ref_mels[b].append(ref_mel_all[i])
-        ref_mel_lens[b].append(ref_mel_len)
-        total_mel_lens[b].append(total_mel_len)
-        ppg_list[b].append(ppg_all[i])
-        ppg_lens[b].append(ppg_len_all[i])
-        batch_accum[b] += total_mel_len
-        if batch_accum[b] >= infer_batch_size:
-            flush(b)
-            batch_accum[b] = 0
-            utts[b], ref_rms_list[b], ref_mels[b], ref_mel_lens[b], total_mel_lens[b], ppg_list[b], ppg_lens[b] = [], [], [], [], [], [], []
-    for b, frames in enumerate(batch_accum):
-        if frames > 0:
-            flush(b)
-    random.seed(666)
-    random.shuffle(prompts_all)
-    return prompts_all
+    return _bucket_batches(metainfo, ref_len_all, fields, emit, speed, target_sample_rate, hop_length, use_truth_duration,
+                           infer_batch_size, num_buckets, min_secs, max_secs)
 
 
 # ---------------------------------------------------------------------------------------------------------------------

@@ -83,16 +83,22 @@ class GumbelVectorQuantizer(nn.Module):
         self._plan = None
         return super()._apply(fn, *a, **k)
 
-    def load_state_dict(self, *a, **k):
+    def _load_from_state_dict(self, *a, **k):  # also reached through a parent's load_state_dict (DiT.quantizer)
         self._plan = None
-        return super().load_state_dict(*a, **k)
+        return super()._load_from_state_dict(*a, **k)
+
+    def _param_versions(self):  # in-place parameter updates bump these
+        return tuple(p._version for p in self.parameters())
 
     def _get_plan(self):
+        if self._plan is not None and self._plan["versions"] != self._param_versions():
+            self._plan = None
         if self._plan is None:
             dev = self.vars.device
             w = self.weight_proj.weight.detach().float().contiguous()
             self._plan = dict(w3=split3_weight(w), w=w, b=self.weight_proj.bias.detach().float().contiguous(),
-                              vars=self.vars.detach().float().reshape(-1, self.vars.shape[-1]).contiguous(), dev=dev)
+                              vars=self.vars.detach().float().reshape(-1, self.vars.shape[-1]).contiguous(), dev=dev,
+                              versions=self._param_versions())
         return self._plan
 
     @torch.no_grad()

@@ -106,12 +106,21 @@ class Vocos(nn.Module):
         self._plan, self._ws = None, {}
         return super()._apply(fn, *a, **k)
 
+    def _load_from_state_dict(self, *a, **k):  # reached when a PARENT module's load_state_dict loads this one
+        self._plan, self._ws = None, {}
+        return super()._load_from_state_dict(*a, **k)
+
+    def _param_versions(self):  # in-place parameter updates (copy_, optimizer steps) bump these
+        return tuple(p._version for p in self.parameters())
+
     def forward(self, *a, **k):
         raise NotImplementedError("f5e_tts_b200.Vocos is decode-only (the reference never calls vocoder.forward)")
 
     def _get_plan(self):
         if self._plan is not None:
-            return self._plan
+            if self._plan[-1] == self._param_versions():
+                return self._plan
+            self._plan, self._ws = None, {}
         dev = self.head.out.weight.device
         if dev.type != "cuda":
             raise RuntimeError("f5e_tts_b200.Vocos has no CPU path: move the module to a B200 (cuda) device")
@@ -151,7 +160,7 @@ class Vocos(nn.Module):
         m.w_head, m.b_head = W3(self.head.out.weight), F(self.head.out.bias)
         window, tw = fft_tables(dev)
         m.window, m.twiddles = window.data_ptr(), tw.data_ptr()
-        self._plan = (m, blocks, keep, (window, tw))
+        self._plan = (m, blocks, keep, (window, tw), self._param_versions())
         return self._plan
 
     def _workspace(self, batch, t_pad):

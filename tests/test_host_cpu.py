@@ -147,3 +147,43 @@ def test_gather_world_size_2_gloo(tmp_path):
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                         "--master-port", "29613", str(w), ROOT], capture_output=True, text=True, timeout=240)
     assert r.returncode == 0 and "GLOO_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def _header_struct_fields(name):
+    """(field name, is_pointer) of a `typedef struct <name> {...}` in include/f5e_b200.h, in declaration order."""
+    import re
+
+    from f5e_tts_b200 import _lib
+
+    src = re.sub(r"/\*.*?\*/", "", _lib.header_path().read_text(), flags=re.S)
+    body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (name, name), src, flags=re.S).group(1)
+    out = []
+    for decl in body.split(";"):
+        decl = decl.strip()
+        if not decl:
+            continue
+        ptr_type = "*" in decl.split(",")[0]
+        names = re.findall(r"[*\s,]([A-Za-z_][A-Za-z0-9_]*)\s*(?=,|$)", decl)
+        out += [(n, ptr_type) for n in names]
+    return out
+
+
+def test_epilogue_struct_matches_header_and_docs():
+    """The ctypes mirror, the header and the stub printed in INTEGRATION.md declare the same fields in the same order
+    (a stale stub mis-lays the struct silently)."""
+    import ctypes as C
+    import re
+    from pathlib import Path
+
+    from f5e_tts_b200 import _lib
+
+    hdr = _header_struct_fields("f5e_epilogue")
+    mirror = [(n, t is C.c_void_p) for n, t in _lib.Epilogue._fields_]
+    assert mirror == hdr
+    doc = (Path(_lib.header_path()).parent.parent / "INTEGRATION.md").read_text()
+    stub = doc[doc.index("class f5e_epilogue(C.Structure):"):]
+    stub = stub[:stub.index("]\n") + 1]
+    doc_fields = [(n, t == "c_void_p") for n, t in re.findall(r'\("([a-z0-9_]+)", C\.(c_void_p|c_int32)\)', stub)]
+    assert doc_fields == hdr
+    g = _header_struct_fields("f5e_guidance")
+    assert [n for n, _ in g] == [n for n, _ in _lib.Guidance._fields_]
