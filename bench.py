@@ -8,6 +8,16 @@ A "step" is one pass of the hot path over one batch: CFM.sample (32 Euler steps 
 CFG + Euler) on 16 utterances of ~10 s, then the Vocos decode of every generated span (BASELINE.json configs[1]).
 Under torchrun every rank runs its own batch (per-utterance sharding, no data-path collective inside the solve); the e2e leg
 adds the NCCL gather of the waveforms to rank 0.  One JSON line is printed by rank 0.
+
+Timed regions of the B200 arm, in order (each bracketed by barrier + synchronize, CUDA events, max over ranks):
+  1. `value`    inputs resident in HBM, in-stream profiler OFF;
+  2. `e2e`      raw prompt waves in pinned host memory -> H2D -> MelSpec -> CFM.sample -> Vocos -> (NCCL gather) -> D2H into
+                pinned memory; the gather + D2H of step i run on a side stream under the solve of step i + 1;
+  3. roofline   ONE more step with every launch of the GEMM / attention / norm classes bracketed by events
+                (f5e_prof_begin) -> `roofline` (DiT-block GEMMs), `roofline_attention`, `roofline_hbm`;
+  4. extras     `gpu_baseline` (the path restated in eager PyTorch bf16 on the same GPU, 2 NFE steps, with the reference's
+                expanded bool mask and with flash SDPA), `extra.latency` (batch 1), `extra.eval_set` (BASELINE configs[3]
+                shape sharded over the ranks: strong scaling), `cpu_baseline` (rank 0, N = 1 only).
 """
 from __future__ import annotations
 
@@ -43,6 +53,9 @@ def parse():
     ap.add_argument("--graph", type=int, default=0, help="capture the Euler loop in one CUDA graph per solve")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=15.0)
+    ap.add_argument("--no-extras", action="store_true", help="skip gpu_baseline / latency / eval_set")
+    ap.add_argument("--eval-utterances", type=int, default=1088)
+    ap.add_argument("--pack", type=int, default=-1, help="CFM.pack_valid_rows: -1 default (only where exact), 0 never, 1 always")
     return ap.parse_args()
 
 
@@ -179,7 +192,7 @@ def cpu_arm(sd_fp32, w, nfe, budget_s):
         O.vocos_decode(vsd, m)
         voc_s = time.perf_counter() - t0
     audio = (dur - ref_len) * HOP / SR
-    return dict(value=audio / (total + voc_s), unit=UNIT, cores=cores, kind="port",
+    return dict(value=audio / (total + voc_s), unit=UNIT, cores=cores, kind="port", steps_timed=steps_done,
                 sample=f"oracle port (torch fp32) on {cores} host threads: utterance 0 of the workload ({dur} frames, {ref_len} ref), "
                        f"{steps_done} of {nfe} Euler steps timed ({t_used:.1f} s) and extrapolated linearly, Vocos decode timed in full"), per_step
 
@@ -208,7 +221,7 @@ def run_reference(a, rank):
         return
     w = make_workload(a.batch, a.seconds, 0)
     sd = reference_weights()
-    vals, per = [], []
+    vals, per, timed_steps = [], [], 0
     budget = max(2.0, min(a.cpu_budget_s, 120.0 / max(1, a.steps + a.warmup)))
     r = None
     for s in range(a.warmup + a.steps):
@@ -216,12 +229,17 @@ def run_reference(a, rank):
         if s >= a.warmup:
             vals.append(r["value"])
             per.append(per_step)
+            timed_steps = r["steps_timed"]
     v = statistics.mean(vals)
     r["value"] = v
     line = dict(metric=METRIC, value=v, unit=UNIT, impl="reference", n_gpus=a.gpus, steps=a.steps, warmup=a.warmup,
                 ms_per_step=1e3 * statistics.mean(per) * a.nfe, higher_is_better=True, scaling="weak", vs_baseline=None,
                 dtype="f32", data="synthetic",
-                config=workload_config(a, w), cpu_baseline=r,
+                config=dict(workload_config(a, w), cuda_graph=bool(a.graph)),  # same keys / values as the B200 arm's config
+                extrapolated=True, steps_timed=timed_steps,
+                extrapolation="ONE utterance of the batch at batch 1, steps_timed of nfe Euler steps per bench step, scaled "
+                              "linearly to nfe steps; audio-s/s of that utterance (per-utterance cost is what shards)",
+                cpu_baseline=r,
                 e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
     print(json.dumps(line), flush=True)
 
@@ -237,9 +255,193 @@ def workload_config(a, w):
 # ----------------------------------------------------------------------------------------------------------------------
 # B200 arm
 # ----------------------------------------------------------------------------------------------------------------------
-def run_b200(a, rank, local_rank, world):
+MUFU_LANES_PER_CLK_SM = 16.0   # MUFU.EX2 results per clock per SM (measured: tools/ubench/tmem_bw.cu, 15.8)
+N_SMS = 148
+
+
+def profile_step(lib, step_fn, dur, B, peak_tf, peak_gbs, sm_mhz):
+    """One more step with every GEMM / attention / norm launch bracketed by an event pair on the launching stream
+    -> the three roofline blocks of the JSON line.  Algorithmic work only: valid frames, no padding credited."""
     import ctypes as C
 
+    import torch
+
+    lib.f5e_prof_begin(1 | 2 | 8)  # F5E_PROF_GEMM | ATTN | NORM
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    step_fn()
+    e1.record()
+    torch.cuda.synchronize()
+    ms_total = e0.elapsed_time(e1)
+    nrec = lib.f5e_prof_end()
+    rows_valid = 2.0 * float(dur.sum())
+    rows_padded = 2 * B * int(dur.max())
+    sum_n2 = 2.0 * float((dur.double() ** 2).sum())
+    g_ms = g_fl = a_ms = r_ms = r_by = 0.0
+    g_n = a_n = r_n = 0
+    cls, ms_, dims = C.c_int32(), C.c_float(), (C.c_int64 * 3)()
+    for i in range(nrec):
+        lib.f5e_prof_read(C.c_int64(i), C.byref(cls), C.byref(ms_), dims)
+        d0, d1, d2 = dims[0], dims[1], dims[2]
+        if cls.value == 1:
+            M, N, K = d0, d1, d2
+            if (N, K - LN_FOLD_K) in ((3072, 1024), (2048, 1024)):
+                K -= LN_FOLD_K  # the mean-correction block is overhead, not algorithmic work
+            if M in (rows_padded, int(rows_valid)) and (N, K) in DIT_GEMM_NK:  # padded or packed rows
+                g_ms += ms_.value
+                g_fl += 2.0 * rows_valid * N * K
+                g_n += 1
+        elif cls.value == 2 and d0 == 2 * B:  # the DiT blocks' attention (not the text / PPG embedders')
+            a_ms += ms_.value
+            a_n += 1
+        elif cls.value == 8 and d2 == 1 and d1 == 1024 and d0 in (rows_padded, int(rows_valid)):  # row_stats of the DiT blocks
+            r_ms += ms_.value
+            r_by += rows_valid * (d1 * 2 + 4 + 64 * 2)  # bf16 row in, fp32 rstd + bf16 [64] mean-correction row out
+            r_n += 1
+    lib.f5e_prof_begin(0)
+    out = {}
+    ach = g_fl / (g_ms * 1e-3) / 1e12 if g_ms > 0 else None
+    out["gemm"] = dict(achieved=ach, launches=g_n, avg_launch_ms=(g_ms / g_n if g_n else None),
+                       share_of_step=(g_ms / ms_total if ms_total else None), frac=(ach / peak_tf if ach else None))
+    if a_n:
+        fl = 4.0 * 1024 * sum_n2  # QK^T + PV over the valid keys / queries of the doubled batch, 16 heads x 64
+        avg = a_ms / a_n
+        tf = fl / (avg * 1e-3) / 1e12
+        floor_ms = 16.0 * sum_n2 / (MUFU_LANES_PER_CLK_SM * N_SMS * sm_mhz * 1e6) * 1e3  # one ex2 per (query, key, head)
+        out["attention"] = dict(bound="mufu+tensor", kernel="attention_kernel (DiT blocks)", flops_per_launch=fl, achieved=tf,
+                                peak=peak_tf, unit="TFLOP/s", frac=tf / peak_tf, launches=a_n, avg_launch_ms=avg,
+                                share_of_step=a_ms / ms_total, mufu_floor_ms=floor_ms, frac_of_mufu_floor=floor_ms / avg,
+                                mufu_floor="16 heads x sum N^2 exponentials / (16 lanes/clk/SM x 148 SMs x the SM clock sampled "
+                                           "during the timed region)")
+    if r_n:
+        avg = r_ms / r_n
+        gbs = r_by / r_n / (avg * 1e-3) / 1e9
+        out["hbm"] = dict(bound="hbm", kernel="row_stats_kernel (LayerNorm statistics of the folded adaLN path)",
+                          bytes_per_launch=r_by / r_n, achieved=gbs, peak=peak_gbs, unit="GB/s", frac=gbs / peak_gbs,
+                          launches=r_n, avg_launch_ms=avg, share_of_step=r_ms / ms_total)
+    return out, ms_total
+
+
+def gpu_baseline(sd_fp32, w, dev, nfe_steps=2):
+    """The kernel to beat (BASELINE.md B-GPU-ref): the path restated in eager PyTorch bf16 (cuBLAS, SDPA, cuDNN convs) on the
+    SAME GPU and workload, `nfe_steps` Euler steps (cond + uncond evaluation each).  Once with the reference's expanded bool
+    mask (modules.py:483-492: the math / mem-efficient SDPA backends) and once with flash SDPA (per sample, valid keys only)."""
+    import torch
+
+    from oracle import f5e_oracle as O
+
+    cfg = O.DiTConfig(**ARCH)
+    o16 = O.OracleDiT(cfg, sd_fp32, torch.bfloat16, dev)
+    ref_len, dur, text = w["ref_len"].to(dev), w["dur"].to(dev), w["text"].to(dev)
+    mel = O.mel_spectrogram(w["ref_wav"].to(dev)).permute(0, 2, 1)[:, : int(ref_len.max())].contiguous()
+    kw = dict(steps=nfe_steps, cfg_strength=2.0, sway_sampling_coef=-1.0, seed=0)
+    res = {}
+    for name, backend in (("bool_mask", "mask"), ("flash", "flash")):
+        o16.attn_backend = backend
+        fn = lambda: O.cfm_sample(o16, mel, text, dur, lens=ref_len, **kw)  # noqa: E731
+        fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(2):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        res[name] = e0.elapsed_time(e1) / 2 / nfe_steps
+    return dict(kind="oracle port, eager PyTorch bf16 (cuBLAS / SDPA / cuDNN), same GPU, same workload",
+                nfe_steps_timed=nfe_steps, ms_per_nfe_step_bool_mask=res["bool_mask"], ms_per_nfe_step_flash=res["flash"])
+
+
+def latency_leg(model, vocoder, dev, nfe):
+    """BASELINE.md "C1 shape on GPU": ONE ~10 s utterance (940 frames, 315 of them prompt), nfe Euler steps, CFG 2 - what
+    infer_cli.py runs.  Steady state: the CUDA graph of the Euler loop is cached by shape after the first solve."""
+    import torch
+
+    g = torch.Generator().manual_seed(7)
+    cond = torch.randn(1, 315, 100, generator=g).to(dev)
+    text = torch.randint(1, 2545, (1, 150), generator=g).to(dev)
+    keep = model.use_cuda_graph
+    out = {}
+    for graph in (0, 1):
+        model.use_cuda_graph = bool(graph)
+        fn = lambda: model.sample(cond, text, None, 940, steps=nfe, cfg_strength=2.0, sway_sampling_coef=-1.0, seed=0)  # noqa: E731
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(3):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        out["graph" if graph else "stream"] = e0.elapsed_time(e1) / 3
+    model.use_cuda_graph = keep
+    best = min(out.values())
+    return dict(workload="batch 1 x 940 frames (315 prompt), nfe %d, cfg 2, mel only" % nfe, ms_per_solve_stream=out["stream"],
+                ms_per_solve_graph=out["graph"], ms_per_nfe_step=best / nfe, floor_ms_per_nfe_step=0.62,
+                audio_s_per_s=(940 - 315) * HOP / SR / (best / 1e3))
+
+
+def eval_set_leg(model, vocoder, dev, rank, world, n_utt, nfe=16):
+    """BASELINE configs[3]: a Seed-TTS-test-en shaped synthetic set (n_utt utterances of 3-15 s, NFE 16) - a FIXED total
+    sharded over the ranks (strong scaling) through evaluate.split_batches (LPT on the modelled cost), then the ONE
+    exchange of the path: lengths + one padded NCCL gather of the waveforms to rank 0."""
+    import torch
+    import torch.distributed as dist
+
+    from f5e_tts_b200 import dist as fdist
+    from f5e_tts_b200 import evaluate as E
+    from f5e_tts_b200 import pipeline as P
+
+    g = torch.Generator().manual_seed(0)  # the same list on every rank, like the reference
+    meta = []
+    for i in range(n_utt):
+        secs = 3.0 + 3.0 * torch.rand(1, generator=g).item()
+        wave = 0.05 * torch.randn(1, int(secs * 16000), generator=g)
+        meta.append((f"u{i}", "reference transcript of the prompt audio.", (wave, 16000),
+                     " " + "some generated words " * int(1 + 4 * torch.rand(1, generator=g).item()), None))
+    prompts = P.get_inference_prompt(meta, device=dev, infer_batch_size=16 * 1031, num_buckets=200, min_secs=3, max_secs=40)
+    E.infer_batches(model, vocoder, prompts[:1], nfe_step=nfe, seed=0)  # warm-up
+    if world > 1:
+        fdist.gather_varlen(torch.ones(1, device=dev, dtype=torch.int64), torch.zeros(1, device=dev), dst=0)
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    res = E.infer_batches(model, vocoder, prompts, nfe_step=nfe, seed=0, rank=rank, world=world, split="lpt")
+    torch.cuda.synchronize()
+    t_mine = time.perf_counter() - t0
+    lens = torch.tensor([x.shape[-1] for _, x in res], device=dev)
+    payload = torch.cat([x.reshape(-1) for _, x in res]).to(dev) if res else torch.zeros(0, device=dev)
+    t0 = time.perf_counter()
+    gathered = fdist.gather_varlen(lens, payload, dst=0) if world > 1 else (lens, payload)
+    torch.cuda.synchronize()
+    t_gather = time.perf_counter() - t0
+    t = torch.tensor([t_mine, t_gather, float(len(res)), float(lens.sum())], device=dev, dtype=torch.float64)
+    tmax, tsum = t.clone(), t.clone()
+    busy = [t_mine]
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        allb = torch.zeros(world, device=dev, dtype=torch.float64)
+        allb[rank] = t_mine
+        dist.all_reduce(allb)
+        busy = allb.tolist()
+    if rank != 0:
+        return None
+    audio = float(tsum[3]) / SR
+    assert int(tsum[2]) == n_utt and (world == 1 or int(gathered[0].numel()) == n_utt)
+    mean_busy = sum(busy) / len(busy)
+    return dict(workload=f"BASELINE configs[3] shape: {n_utt} synthetic utterances (3-6 s prompts, 3-15 s total), {len(prompts)} "
+                         f"bucketed batches, nfe {nfe}, cfg 2, Vocos decode, per-batch D2H; fixed total sharded over the ranks",
+                scaling="strong", n_gpus=world, generated_audio_s=audio, audio_s_per_s=audio / (float(tmax[0]) + float(tmax[1])),
+                solve_s_max_over_ranks=float(tmax[0]), per_rank_busy_s=[round(b, 3) for b in busy],
+                lpt_imbalance=max(busy) / mean_busy if mean_busy > 0 else None, gather_ms=1e3 * float(tmax[1]),
+                gather_bytes=int(tsum[3]) * 4, timing="host wall clock around synchronised regions (many launches and D2H copies "
+                                                      "per batch), max over ranks")
+
+
+def run_b200(a, rank, local_rank, world):
     import torch
     import torch.distributed as dist
 
@@ -254,6 +456,8 @@ def run_b200(a, rank, local_rank, world):
     model, sd_fp32 = build_model(dev)
     model.use_cuda_graph = bool(a.graph)
     model.store_trajectory = False  # every caller of the reference discards the trajectory
+    if a.pack >= 0:
+        model.pack_valid_rows = bool(a.pack)
     from f5e_tts_b200.vocos import Vocos
 
     vocoder = Vocos(seed=4321).to(dev)
@@ -262,39 +466,55 @@ def run_b200(a, rank, local_rank, world):
     ref_len, dur, text = w["ref_len"], w["dur"], w["text"]
     kw = dict(steps=a.nfe, cfg_strength=2.0, sway_sampling_coef=-1.0, seed=0)
 
-    # reference prompt mels through the MelSpec kernel (once, outside the timed region: it is input preparation)
+    # device-resident inputs of region 1: the prompt mels (MelSpec kernel), token ids, lengths
     mel = model.mel_spec(w["ref_wav"].to(dev)).permute(0, 2, 1)[:, : int(ref_len.max())].contiguous()  # [B, Tref, 100] fp32
     d_cond, d_text, d_ref, d_dur = mel, text.to(dev), ref_len.to(dev), dur.to(dev)
-    h_cond, h_text = mel.cpu().pin_memory(), text.pin_memory()
+    # host buffers of region 2: RAW prompt waves (CFM.sample takes them, cfm.py:371-374), token ids, lengths; result buffer
+    h_wave, h_text = w["ref_wav"].pin_memory(), text.pin_memory()
     h_ref, h_dur = ref_len.pin_memory(), dur.pin_memory()
     gen_len = (dur - ref_len)
     wav_len = (gen_len - 1) * HOP
-    h_wav = torch.empty(B, int(wav_len.max()), dtype=torch.float32).pin_memory()
+    l_loc = torch.tensor([int(wav_len.max())], device=dev, dtype=torch.int64)
+    if world > 1:
+        dist.all_reduce(l_loc, op=dist.ReduceOp.MAX)
+    l_max = int(l_loc)
+    h_out = torch.empty(world * B if rank == 0 else 1, l_max, dtype=torch.float32).pin_memory()
+    side = torch.cuda.Stream(device=dev)
+    gather_ms = []
 
     def step_device():
         out, _ = model.sample(d_cond, d_text, None, d_dur, lens=d_ref, **kw)
         return vocoder.decode_varlen(out, d_ref, d_dur)  # fp32 [B, max (gen-1)*256], zero padded
 
     def step_e2e():
-        cond = h_cond.to(dev, non_blocking=True)
+        wave = h_wave.to(dev, non_blocking=True)
         txt = h_text.to(dev, non_blocking=True)
         rl = h_ref.to(dev, non_blocking=True)
         du = h_dur.to(dev, non_blocking=True)
-        out, _ = model.sample(cond, txt, None, du, lens=rl, **kw)
+        out, _ = model.sample(wave, txt, None, du, lens=rl, **kw)   # MelSpec of the prompts runs inside
         wav = vocoder.decode_varlen(out, rl, du)
-        if world > 1:  # the one exchange of the sharded eval: gather every rank's waveforms on rank 0 over NVLink
-            from f5e_tts_b200 import dist as fdist
+        # delivery (gather to rank 0 over NVLink, then D2H into pinned memory) on a side stream: it overlaps the next solve
+        main = torch.cuda.current_stream()
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            wav.record_stream(side)
+            if wav.shape[1] != l_max:
+                wav = torch.nn.functional.pad(wav, (0, l_max - wav.shape[1]))
+            if world > 1:
+                g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                g0.record(side)
+                if rank == 0:
+                    allw = torch.empty(world, B, l_max, device=dev, dtype=torch.float32)
+                    dist.gather(wav.contiguous(), list(allw.unbind(0)), dst=0)
+                    wav = allw.view(world * B, l_max)
+                else:
+                    dist.gather(wav.contiguous(), None, dst=0)
+                g1.record(side)
+                gather_ms.append((g0, g1))
+            if rank == 0:
+                h_out.copy_(wav, non_blocking=True)
 
-            wav = fdist.gather_padded(wav, dst=0)
-        if rank == 0:
-            tgt = h_wav if world == 1 else None
-            if tgt is not None:
-                tgt.copy_(wav, non_blocking=True)
-            else:
-                wav.cpu()
-        torch.cuda.current_stream().synchronize()
-
-    def timed(fn, n):
+    def timed(fn, n, drain=None):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
@@ -302,6 +522,8 @@ def run_b200(a, rank, local_rank, world):
         e0.record()
         for _ in range(n):
             fn()
+        if drain is not None:
+            torch.cuda.current_stream().wait_stream(drain)  # the last step's delivery is inside the timed region
         e1.record()
         torch.cuda.synchronize()
         if world > 1:
@@ -313,36 +535,17 @@ def run_b200(a, rank, local_rank, world):
 
     for _ in range(a.warmup):
         step_device()
-    # --- timed region 1: inputs resident in HBM; GEMM launches bracketed by events for the roofline leg
+    # --- timed region 1: inputs resident in HBM, profiler off
     clocks = ClockSampler(local_rank)
     n0 = lib.f5e_launch_count()
-    lib.f5e_prof_begin(1)  # F5E_PROF_GEMM
     torch.cuda.profiler.start()  # cudaProfilerStart: `ncu --profile-from-start off` captures the timed region only
     ms_total = timed(step_device, a.steps)
     torch.cuda.profiler.stop()
-    nrec = lib.f5e_prof_end()
     launches = lib.f5e_launch_count() - n0
     clk = clocks.stop()
-    # per-launch records -> achieved TFLOP/s of the DiT-block GEMM kernel
-    rows_valid = 2.0 * float(dur.sum())
-    n_pad = int(dur.max())
-    rows_padded = 2 * B * n_pad
-    g_ms, g_fl, g_n = 0.0, 0.0, 0
-    cls, ms_, dims = C.c_int32(), C.c_float(), (C.c_int64 * 3)()
-    for i in range(nrec):
-        lib.f5e_prof_read(C.c_int64(i), C.byref(cls), C.byref(ms_), dims)
-        M, N, K = dims[0], dims[1], dims[2]
-        if (N, K - LN_FOLD_K) in ((3072, 1024), (2048, 1024)):
-            K -= LN_FOLD_K  # the mean-correction block is overhead, not algorithmic work
-        if cls.value == 1 and M in (rows_padded, int(rows_valid)) and (N, K) in DIT_GEMM_NK:  # padded or packed rows
-            g_ms += ms_.value
-            g_fl += 2.0 * rows_valid * N * K  # algorithmic: valid rows only, padding not credited
-            g_n += 1
-    lib.f5e_prof_begin(0)
     ms_step = ms_total / a.steps
     audio = audio_seconds(w)
-    # the other ranks' workloads have different lengths: sum the audio over ranks
-    tot_audio = torch.tensor([audio], device=dev, dtype=torch.float64)
+    tot_audio = torch.tensor([audio], device=dev, dtype=torch.float64)  # ranks own different lengths: sum the audio
     if world > 1:
         dist.all_reduce(tot_audio)
     value = float(tot_audio) / (ms_step / 1e3)
@@ -350,36 +553,68 @@ def run_b200(a, rank, local_rank, world):
     # --- timed region 2: end to end through the public API with HOST buffers
     for _ in range(2):
         step_e2e()
-    ms_e2e = timed(step_e2e, a.steps) / a.steps
+    torch.cuda.synchronize()
+    gather_ms.clear()
+    ms_e2e = timed(step_e2e, a.steps, drain=side) / a.steps
     e2e_value = float(tot_audio) / (ms_e2e / 1e3)
-    h2d = h_cond.numel() * 4 + h_text.numel() * 8 + h_ref.numel() * 8 + h_dur.numel() * 8
-    d2h = h_wav.numel() * 4 * (world if world > 1 else 1)
+    h2d = h_wave.numel() * 4 + h_text.numel() * 8 + h_ref.numel() * 8 + h_dur.numel() * 8
+    d2h = h_out.numel() * 4 if rank == 0 else 0
+    g_ms = [x.elapsed_time(y) for x, y in gather_ms] if gather_ms else []
 
+    # --- region 3: one profiled step -> rooflines (rank 0's numbers are reported)
+    peak_tf, peak_gbs, peak_src = measured_peaks()
+    roof, ms_prof = profile_step(lib, step_device, dur, B, peak_tf, peak_gbs, (clk or {}).get("sm_mhz", 1965.0))
+
+    extra = {}
+    if not a.no_extras:
+        ev = eval_set_leg(model, vocoder, dev, rank, world, a.eval_utterances)
+        if rank == 0:
+            extra["eval_set"] = ev
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    peak_tf, peak_gbs, peak_src = measured_peaks()
-    ach = g_fl / (g_ms * 1e-3) / 1e12 if g_ms > 0 else None
-    traffic = None
+    traffic = {}
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
-        traffic = json.load(open(tp)).get("gemm_bf16_kernel")
+        traffic = json.load(open(tp))
     step_flops = 2.0 * sum(dit_flops(float(n)) for n in dur)
+    gm = roof["gemm"]
     line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=a.steps, warmup=a.warmup, ms_per_step=ms_step,
                 higher_is_better=True, scaling="weak", vs_baseline=None, dtype="bf16", data="synthetic",
                 config=dict(workload_config(a, w), cuda_graph=bool(a.graph)),
                 ms_per_nfe_step=ms_step / a.nfe,
                 model_tflops=step_flops * a.nfe / (ms_step * 1e-3) / 1e12,
                 e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=int(h2d), d2h_bytes_per_step=int(d2h),
-                         ms_per_step=ms_e2e),
+                         ms_per_step=ms_e2e, inputs="raw prompt waves (MelSpec inside the timed region), token ids, lengths",
+                         delivery="gather + D2H of step i on a side stream under the solve of step i+1; the last one drained "
+                                  "inside the timed region",
+                         gather_ms_per_step=(statistics.mean(g_ms) if g_ms else 0.0)),
                 gpu_launches=int(launches),
-                roofline=dict(bound="tensor", kernel="gemm_bf16_kernel (DiT block qkv/out/ff1/ff2)", achieved=ach, peak=peak_tf,
-                              unit="TFLOP/s", frac=(ach / peak_tf if ach else None), traffic=traffic, peak_source=peak_src,
-                              launches=g_n, avg_launch_ms=(g_ms / g_n if g_n else None),
-                              share_of_step=(g_ms / ms_total if ms_total else None)),
+                pack_valid_rows=bool(model.last_aux["packed_rows"]),
+                roofline=dict(bound="tensor", kernel="gemm_bf16_kernel (DiT block qkv/out/ff1/ff2)", achieved=gm["achieved"],
+                              peak=peak_tf, unit="TFLOP/s", frac=gm["frac"], traffic=traffic.get("gemm_bf16_kernel"),
+                              peak_source=peak_src, launches=gm["launches"], avg_launch_ms=gm["avg_launch_ms"],
+                              share_of_step=gm["share_of_step"],
+                              measured="in-stream event pairs around every launch of ONE extra step (profiler off in the "
+                                       "headline region); %.1f ms with the events vs %.1f ms without" % (ms_prof, ms_step)),
                 clocks=clk)
-    if not a.no_cpu_baseline:
+    if "attention" in roof:
+        line["roofline_attention"] = dict(roof["attention"], traffic=traffic.get("attention_kernel"))
+    if "hbm" in roof:
+        line["roofline_hbm"] = dict(roof["hbm"], traffic=traffic.get("row_stats_kernel"), peak_source=peak_src)
+    if not a.no_extras:
+        try:
+            line["gpu_baseline"] = gpu_baseline(sd_fp32, w, dev)
+        except Exception as e:  # the baseline arm must never take the headline down with it
+            line["gpu_baseline"] = dict(error=repr(e)[:200])
+        try:
+            extra["latency"] = latency_leg(model, vocoder, dev, a.nfe)
+        except Exception as e:
+            extra["latency"] = dict(error=repr(e)[:200])
+    if extra:
+        line["extra"] = extra
+    if not a.no_cpu_baseline and world == 1:
         cb, _ = cpu_arm(sd_fp32, make_workload(a.batch, a.seconds, 0), a.nfe, a.cpu_budget_s)
         line["cpu_baseline"] = cb
     print(json.dumps(line), flush=True)

@@ -50,10 +50,16 @@ constexpr uint32_t ATT_TMEM_COLS = 256;
 constexpr uint32_t ATT_TMEM_O = 128;   // S [0,128) fp32 | O [128,192) fp32 | P [192,256) bf16 pairs (128 keys)
 constexpr uint32_t ATT_TMEM_P = 192;
 
+// ATT_KO_* (developer knobs, WRONG results on purpose): knock one unit out to see what it costs in time and in joules
+// (tools/attn_lab.py --sustain; profiles/r02_attention.md).
 __device__ __forceinline__ float ex2_approx(float x) {
+#ifdef ATT_KO_MUFU
+  return x * 0.001f;
+#else
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+#endif
 }
 
 #ifdef ATT_TRACE
@@ -149,9 +155,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __res
 #pragma unroll
           for (int kv = 0; kv < 2; ++kv) {  // K_j then V_j
             mbar_wait(&kv_empty[slot], phase ^ 1);
+#ifdef ATT_KO_TMA
+            mbar_arrive(&kv_full[slot]);
+#else
             mbar_expect_tx(&kv_full[slot], ATT_TILE_BYTES);
             tma_load_2d(smem + ATT_SMEM_KV + slot * ATT_TILE_BYTES, &tmQKV, &kv_full[slot],
                         (kv + 1) * inner + it.head * ATT_DH, row_base + j * ATT_BN);
+#endif
             if (++slot == ATT_KV_SLOTS) { slot = 0; phase ^= 1; }
           }
         }
@@ -174,8 +184,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __res
         tc_fence_after();
         const uint64_t kdesc = umma_desc_kmajor_sw128(smem_u32(smem + ATT_SMEM_KV + sl * ATT_TILE_BYTES));
         const uint32_t idesc_qk = umma_idesc(kFmtBF16, ATT_BM, (uint32_t)nc, 0, 0);
+#ifndef ATT_KO_MMA
 #pragma unroll
         for (int k = 0; k < ATT_DH / 16; ++k) umma_f16_ss(tmem_base, qdesc + 2 * k, kdesc + 2 * k, idesc_qk, k != 0);
+#endif
         umma_commit(&kv_empty[sl]);
         umma_commit(s_full);
         ATT_T(4, b, 0);
@@ -186,8 +198,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __res
         tc_fence_after();
         // 16 keys = 2048 bytes of the MN-major V tile per K step: the descriptor's address field advances by 2048 >> 4
         const uint64_t vdesc = umma_desc_mnmajor_sw128(smem_u32(smem + ATT_SMEM_KV + sl * ATT_TILE_BYTES), 1024, 1024);
+#ifndef ATT_KO_MMA
         for (int k = 0; k < nc / 16; ++k)  // A = P straight from TMEM: 16 bf16 keys = 8 columns per K step
           umma_f16_ts(tmem_base + ATT_TMEM_O, tmem_base + ATT_TMEM_P + k * 8, vdesc + k * 128, idesc_pv, !(first && k == 0));
+#endif
         umma_commit(&kv_empty[sl]);
         umma_commit(o_full);
         ATT_T(4, b, 2);

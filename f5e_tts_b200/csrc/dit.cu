@@ -2,6 +2,8 @@
 // of the hand-written kernels of this library; there are no library GEMMs and no host synchronisation.
 #include "../../include/f5e_b200.h"
 #include "host.h"
+#include <mutex>
+#include <vector>
 
 using namespace f5e;
 
@@ -12,6 +14,30 @@ using namespace f5e;
   } while (0)
 
 static_assert(sizeof(f5e_fold_job) == sizeof(FoldJob), "f5e_fold_job must mirror FoldJob");
+
+// ---- cache of instantiated Euler-loop graphs (f5e_ode_solve_guided, use_graph != 0) ----------------------------------
+namespace {
+struct GraphKey {  // two independent 64-bit FNV-1a style hashes over the bytes of every argument the graph bakes in
+  uint64_t h = 1469598103934665603ull, h2 = 0x9E3779B97F4A7C15ull;
+  void add(const void* p, size_t n) {
+    const unsigned char* c = static_cast<const unsigned char*>(p);
+    for (size_t i = 0; i < n; ++i) {
+      h = (h ^ c[i]) * 1099511628211ull;
+      h2 = (h2 + c[i] + 0x632BE59BD9B4E019ull) * 0xFF51AFD7ED558CCDull;
+      h2 ^= h2 >> 29;
+    }
+  }
+};
+struct GraphEntry {
+  uint64_t key, key2;
+  cudaGraphExec_t exec;
+  uint64_t last_use;
+};
+constexpr size_t GRAPH_CACHE_ENTRIES = 8;
+std::mutex g_graph_mu;
+std::vector<GraphEntry> g_graphs;
+uint64_t g_graph_clock = 0;
+}  // namespace
 
 static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_dit_buffers* b, const float* mod,
                             int mod_stride, const int* klen, int samples, int n_pad, const f5e_dit_packing* pack,
@@ -189,8 +215,31 @@ int f5e_ode_solve_guided(const f5e_dit_model* model, const f5e_dit_buffers* buf,
   };
   if (!use_graph) return enqueue(st);
 
+  // CUDA-graph path.  The instantiated graph is CACHED on everything it bakes in (every pointer and scalar argument of
+  // every launch derives from the arguments hashed below), so a caller that keeps its buffers (model.py does, per shape)
+  // pays capture + instantiation once and afterwards ONE cudaGraphLaunch per solve with no host synchronisation:
+  // this is what makes the batch-1 latency shape GPU-bound instead of launch-bound (~170 launches per NFE step).
+  GraphKey key;
+  key.add(model, sizeof(*model));
+  key.add(model->layers, sizeof(f5e_dit_layer) * (size_t)model->depth);
+  key.add(buf, sizeof(*buf));
+  key.add(&y, sizeof(y)); key.add(&mod, sizeof(mod)); key.add(&mod_size, sizeof(mod_size));
+  key.add(dt_host, sizeof(float) * (size_t)steps); key.add(&steps, sizeof(steps));
+  key.add(g, sizeof(*g)); key.add(&klen, sizeof(klen)); key.add(&batch, sizeof(batch)); key.add(&n_pad, sizeof(n_pad));
+  key.add(&traj, sizeof(traj)); key.add(&round_bf16, sizeof(round_bf16));
+  if (pack) key.add(pack, sizeof(*pack));
+  int device = 0;
+  F5E_CUDA_CHECK(cudaGetDevice(&device));
+  key.add(&device, sizeof(device));
+  std::lock_guard<std::mutex> lock(g_graph_mu);
+  for (auto& e : g_graphs)
+    if (e.key == key.h && e.key2 == key.h2) {
+      e.last_use = ++g_graph_clock;
+      F5E_CUDA_CHECK(cudaGraphLaunch(e.exec, st));
+      return 0;
+    }
   // Capture on a private stream (the caller's may be the legacy default stream, which cannot be captured);
-  // nothing executes during capture.  The instantiated graph is then launched on the caller's stream.
+  // nothing executes during capture.
   cudaStream_t cap = nullptr;
   F5E_CUDA_CHECK(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
   cudaGraph_t graph = nullptr;
@@ -209,18 +258,28 @@ int f5e_ode_solve_guided(const f5e_dit_model* model, const f5e_dit_buffers* buf,
   }
   F5E_CUDA_CHECK(ce);
   ce = cudaGraphInstantiate(&exec, graph, 0);
-  if (ce != cudaSuccess) {
-    cudaGraphDestroy(graph);
-    F5E_CUDA_CHECK(ce);
-  }
-  ce = cudaGraphLaunch(exec, st);
-  // the executable graph must outlive its launch, so this path drains the stream once per solve before releasing it
-  cudaError_t cs = cudaStreamSynchronize(st);
-  cudaGraphExecDestroy(exec);
   cudaGraphDestroy(graph);
   F5E_CUDA_CHECK(ce);
-  F5E_CUDA_CHECK(cs);
+  if (g_graphs.size() >= GRAPH_CACHE_ENTRIES) {  // evict the least recently used one; it may still be running on `st`
+    size_t lru = 0;
+    for (size_t i = 1; i < g_graphs.size(); ++i)
+      if (g_graphs[i].last_use < g_graphs[lru].last_use) lru = i;
+    cudaDeviceSynchronize();
+    cudaGraphExecDestroy(g_graphs[lru].exec);
+    g_graphs.erase(g_graphs.begin() + (long)lru);
+  }
+  g_graphs.push_back(GraphEntry{key.h, key.h2, exec, ++g_graph_clock});
+  F5E_CUDA_CHECK(cudaGraphLaunch(exec, st));
   return 0;
+}
+
+int f5e_graph_cache_clear(void) {
+  std::lock_guard<std::mutex> lock(g_graph_mu);
+  cudaDeviceSynchronize();
+  for (auto& e : g_graphs) cudaGraphExecDestroy(e.exec);
+  const int n = (int)g_graphs.size();
+  g_graphs.clear();
+  return n;
 }
 
 int f5e_pack_cols(void* dst, int32_t ld_dst, int32_t col0, const void* src, int32_t src_is_f32, int32_t ld_src,

@@ -190,6 +190,8 @@ class DiT(nn.Module):
         self._ws = {}
         # Euler loop only: fold the adaLN LayerNorms into the QKV / FF1 GEMMs (no normalised copy of the activations)
         self.fold_layernorm = os.environ.get("F5E_FOLD_LN", "1") != "0"
+        self.fold_min_rows = int(os.environ.get("F5E_FOLD_MIN_ROWS", "6144"))
+        self._gbuf = {}  # persistent buffers of the cached-CUDA-graph path, per solve shape
         self.initialize_weights()
 
     def initialize_weights(self):  # backbones/dit.py:273-283
@@ -207,12 +209,17 @@ class DiT(nn.Module):
     # OR on a parent (the reference's load_checkpoint loads into the CFM: infer/utils_infer.py:196-234, which reaches the
     # children through _load_from_state_dict only), and in-place updates (EMA copy_, optimizer steps), which bump the
     # parameters' version counters.
+    def _drop_plan(self):
+        if getattr(self, "_gbuf", None):  # cached graphs refer to the plan's weights and to these buffers
+            _lib.load().f5e_graph_cache_clear()
+        self._plan, self._ws, self._gbuf = None, {}, {}
+
     def _apply(self, fn, *a, **k):
-        self._plan, self._ws = None, {}
+        self._drop_plan()
         return super()._apply(fn, *a, **k)
 
     def _load_from_state_dict(self, *a, **k):
-        self._plan, self._ws = None, {}
+        self._drop_plan()
         return super()._load_from_state_dict(*a, **k)
 
     def _param_versions(self):
@@ -226,7 +233,7 @@ class DiT(nn.Module):
         if self._plan is not None:
             if self._plan.versions == self._param_versions():
                 return self._plan
-            self._plan, self._ws = None, {}
+            self._drop_plan()
         dev = self.proj_out.weight.device
         if dev.type != "cuda":
             raise RuntimeError("f5e_tts_b200.DiT has no CPU path: move the module to a B200 (cuda) device")
@@ -345,6 +352,9 @@ class DiT(nn.Module):
                      ff=mk(D * self.ff_mult), pred=mk(self.mel_dim, torch.float32), stats=mk(1, torch.float32),
                      stats_a=torch.zeros(rows, 64, device=dev, dtype=torch.bfloat16))
             b = _Buffers(**{k: v.data_ptr() for k, v in t.items()})
+            if self._gbuf:  # cached graphs refer to the workspace being replaced
+                _lib.load().f5e_graph_cache_clear()
+                self._gbuf = {}
             self._ws = {key: (t, b)}  # keep only the latest shape
         return self._ws[key]
 
@@ -637,7 +647,10 @@ class CFM(nn.Module):
         t_emb, p_emb = {}, {}  # the reference caches text_cond / text_uncond the same way (dit.py:433-441)
         isolate = bool(self.isolate_samples) and batch > 1
         P.model.isolate_samples = int(isolate)
-        fold = bool(getattr(dit, "fold_layernorm", False))
+        # Folding the LayerNorms into the QKV / FF1 GEMMs costs one rewrite of those weights per Euler step (~0.9 GB of HBM
+        # traffic for F5TTS_v1_Base) and saves writing + reading the normalised activations (8 KB per row and layer): it pays
+        # from a few thousand rows on, not at the batch-1 latency shape.
+        fold = bool(getattr(dit, "fold_layernorm", False)) and S * N >= dit.fold_min_rows
         P.model.fold_jobs = P.fold_jobs.data_ptr() if fold else None
         P.model.fold_n_jobs, P.model.fold_rows = (P.fold_n_jobs, P.fold_rows) if fold else (0, 0)
 
@@ -672,6 +685,33 @@ class CFM(nn.Module):
         traj = None
         if self.store_trajectory:  # a packed solve writes the valid rows only: padded rows keep y0 there (zeros)
             traj = (torch.zeros if pack is not None else torch.empty)(steps, B, N, md, device=y.device, dtype=torch.float32)
+        if self.use_cuda_graph:
+            # the cached graph bakes every address in: keep the solve's buffers per shape and copy this call's values in
+            gk = (S, N, steps, traj is not None, None if pack is None else pack.rows_packed, klen is None)
+            gb = dit._gbuf.get(gk)
+            if gb is None:
+                if len(dit._gbuf) >= 4:
+                    _lib.load().f5e_graph_cache_clear()
+                    dit._gbuf.clear()
+                gb = dit._gbuf[gk] = dict(y=torch.empty_like(y), mod=torch.empty_like(mod),
+                                          traj=None if traj is None else torch.empty_like(traj),
+                                          klen=None if klen is None else torch.empty_like(klen),
+                                          pack=None if pack is None else [torch.empty_like(t) for t in pack_keep])
+            gb["y"].copy_(y)
+            gb["mod"].copy_(mod)
+            y, mod = gb["y"], gb["mod"]
+            if traj is not None:
+                if pack is not None:
+                    gb["traj"].zero_()
+                traj = gb["traj"]
+            if klen is not None:
+                gb["klen"].copy_(klen)
+                klen = gb["klen"]
+            if pack is not None:
+                for dst, src in zip(gb["pack"], pack_keep):
+                    dst.copy_(src)
+                pack_keep = gb["pack"]
+                pack = _Packing(pack_keep[0].data_ptr(), pack_keep[1].data_ptr(), pack_keep[2].data_ptr(), pack.rows_packed)
         dt_arr = (C.c_float * steps)(*dts)
         check(_lib.load().f5e_ode_solve_guided(
             C.byref(P.model), C.byref(buf), ptr(y), ptr(mod), P.mod_size, dt_arr, steps, C.byref(guidance), ptr(klen), B, N,
@@ -679,12 +719,15 @@ class CFM(nn.Module):
             None if pack is None else C.byref(pack), stream_ptr()), "f5e_ode_solve_guided")
         del pack_keep
         dit.clear_cache()
-        sampled = y.to(dtype)
+        sampled = y.to(dtype) if (y.dtype != dtype or not self.use_cuda_graph) else y.clone()
         if traj is not None:
             trajectory = torch.cat([y0.unsqueeze(0), traj.to(dtype)], dim=0)
         else:
             trajectory = torch.stack([y0, sampled])
         out = torch.where(cond_mask, cond, sampled)
+        # integer / bool side products of the last solve (tests compare them bit for bit with the reference's)
+        self.last_aux = dict(duration=duration, cond_mask=cond_mask, mask=lens_to_mask(duration) if batch > 1 else None, t=t,
+                             packed_rows=pack is not None)
         if vocoder is not None:
             out = vocoder(out.permute(0, 2, 1))
         return out, trajectory

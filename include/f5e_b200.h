@@ -266,7 +266,9 @@ int f5e_dit_forward(const f5e_dit_model* model, const f5e_dit_buffers* buf, cons
  *   cfg_strength < 1e-5);  y += dt[i] * (pc + (pc - pu) * cfg);  state written back into x_cat for both halves.
  * y: fp32 [batch*n_pad, mel_dim] state (y0 on entry, y(1) on exit).  mod: fp32 [steps, mod_size].  dt_host: HOST
  * float [steps].  traj: optional fp32 [steps, batch*n_pad, mel_dim] (state after each step).  klen: int32
- * [2*batch] (both halves) or NULL.  use_graph != 0 captures the loop into one CUDA graph launch. */
+ * [2*batch] (both halves) or NULL.  use_graph != 0 runs the loop as ONE CUDA graph launch: the instantiated graph is
+ * cached (8 entries, LRU) on every argument it bakes in - pointers, sizes, dt values, the model / layer / buffer structs -
+ * so a caller that keeps its buffers pays capture + instantiation once per shape; no host synchronisation either way. */
 int f5e_ode_solve(const f5e_dit_model* model, const f5e_dit_buffers* buf, float* y, const float* mod, int32_t mod_size,
                   const float* dt_host, int32_t steps, float cfg_strength, const int32_t* klen, int32_t batch,
                   int32_t n_pad, float* traj, int32_t round_bf16, int32_t use_graph, const f5e_dit_packing* pack,
@@ -279,6 +281,10 @@ int f5e_ode_solve_guided(const f5e_dit_model* model, const f5e_dit_buffers* buf,
                          int32_t mod_size, const float* dt_host, int32_t steps, const f5e_guidance* g,
                          const int32_t* klen, int32_t batch, int32_t n_pad, float* traj, int32_t round_bf16,
                          int32_t use_graph, const f5e_dit_packing* pack, void* stream);
+
+/* Destroys every cached Euler-loop graph (after a device synchronise); returns how many there were.  Call it before
+ * freeing buffers or weights a cached graph refers to if the addresses may be reused for something else. */
+int f5e_graph_cache_clear(void);
 
 /* ---------------------------------------------------------------------------------------------------
  * Prompt preparation / chunk assembly around the sampler

@@ -340,8 +340,15 @@ class OracleDiT:
             pn = H if cfg.pe_attn_head is None else cfg.pe_attn_head
             q = torch.cat((apply_rope(q[:, :pn], ang), q[:, pn:]), dim=1)
             k = torch.cat((apply_rope(k[:, :pn], ang), k[:, pn:]), dim=1)
-            am = None if mask is None else mask[:, None, None, :].expand(B, H, N, N)
-            a = F.scaled_dot_product_attention(q, k, v, attn_mask=am)
+            if mask is not None and getattr(self, "attn_backend", "mask") == "flash":
+                # timing arm only (bench.py gpu_baseline): what an eager implementation free to pick the flash SDPA backend
+                # would run - per sample over its valid frames; padded query rows are zeroed by the masked_fill below anyway
+                a = torch.zeros_like(q)
+                for i, L in enumerate(mask.sum(-1).tolist()):
+                    a[i, :, :L] = F.scaled_dot_product_attention(q[i:i + 1, :, :L], k[i:i + 1, :, :L], v[i:i + 1, :, :L])[0]
+            else:
+                am = None if mask is None else mask[:, None, None, :].expand(B, H, N, N)
+                a = F.scaled_dot_product_attention(q, k, v, attn_mask=am)
             a = a.transpose(1, 2).reshape(B, N, H * dh)
             a = _lin(sd, p + ".attn.to_out.0", a)
             if mask is not None:
@@ -379,6 +386,7 @@ def sway_schedule(steps, sway, dtype, device, t_start=0.0):
 @torch.no_grad()
 def cfm_sample(dit: OracleDiT, cond, text, duration, *, ppg=None, lens=None, steps=32, cfg_strength=1.0,
                sway_sampling_coef=None, seed=None, max_duration=4096, no_ref_audio=False, edit_mask=None,
+               duplicate_test=False, t_inter=0.1, vocoder=None,
                y0=None, return_aux=False, mode="cfg", alpha_spk=1.0, alpha_cont=1.0):
     """cond: mel [B, T, 100] (or wave [B, nw]); text: int64 [B, nt] padded with -1.
     Returns (out, trajectory) like the reference; with return_aux also the integer/bool side products.
@@ -407,6 +415,8 @@ def cfm_sample(dit: OracleDiT, cond, text, duration, *, ppg=None, lens=None, ste
         duration = torch.maximum(lens + 1, duration)
     duration = duration.clamp(max=max_duration)
     max_dur = int(duration.amax())
+    if duplicate_test:  # cfm.py:410-412: the prompt repeated right after itself, blended into the noise below
+        test_cond = F.pad(cond, (0, 0, cond_seq_len, max_dur - 2 * cond_seq_len), value=0.0)
     cond = F.pad(cond, (0, 0, 0, max_dur - cond_seq_len), value=0.0)
     if no_ref_audio:
         cond = torch.zeros_like(cond)
@@ -434,7 +444,12 @@ def cfm_sample(dit: OracleDiT, cond, text, duration, *, ppg=None, lens=None, ste
                 torch.manual_seed(seed)
             ys.append(torch.randn(int(dur), cond.shape[-1], device=device, dtype=dtype))
         y0 = torch.nn.utils.rnn.pad_sequence(ys, padding_value=0, batch_first=True)
-    t = sway_schedule(steps, sway_sampling_coef, dtype, device)
+    t_start = 0
+    if duplicate_test:  # cfm.py:460-465
+        t_start = t_inter
+        y0 = (1 - t_start) * y0 + t_start * test_cond
+        steps = int(steps * (1 - t_start))
+    t = sway_schedule(steps, sway_sampling_coef, dtype, device, t_start)
     traj = [y0]
     y = y0
     for i in range(steps):  # torchdiffeq fixed-grid Euler: y1 = y0 + (t1 - t0) * f(t0, y0)
@@ -444,6 +459,8 @@ def cfm_sample(dit: OracleDiT, cond, text, duration, *, ppg=None, lens=None, ste
     dit.clear_cache()
     trajectory = torch.stack(traj)
     out = torch.where(cond_mask, cond, trajectory[-1])
+    if vocoder is not None:  # cfm.py:478-480
+        out = vocoder(out.permute(0, 2, 1))
     if return_aux:
         return out, trajectory, dict(duration=duration, cond_mask=cond_mask, mask=mask, t=t, y0=y0, step_cond=step_cond)
     return out, trajectory

@@ -73,6 +73,65 @@ def case_sample(name, cfg, batch, seed, with_ppg=False):
     return model, sd
 
 
+def _toy_vocoder(mel):
+    """Stand-in for `vocoder=` (cfm.py:478-480 only calls it on out.permute(0, 2, 1)): deterministic, shape-changing."""
+    return mel.flip(1).cumsum(-1)[:, ::7].reshape(mel.shape[0], -1)
+
+
+OPTION_CASES = {  # the sampler options of cfm.py:348-482 that sample_b*.pt do not exercise
+    "edit_mask": dict(edit=True),
+    "no_ref_audio": dict(kw=dict(no_ref_audio=True)),
+    "duplicate_test": dict(kw=dict(duplicate_test=True, t_inter=0.25), steps=8),
+    "vocoder": dict(vocoder=True),
+    "cfg0": dict(kw=dict(cfg_strength=0.0)),
+    "max_duration": dict(kw=dict(max_duration=45)),          # below two of the requested durations
+    "text_longer": dict(long_text=True),                     # a text longer than the requested duration raises it
+    "int_duration_no_lens": dict(int_duration=50, no_lens=True),
+}
+
+
+def case_sample_options(name, cfg, batch, seed):
+    """One fixture holding every option case: same model / inputs, one `sample` call of the reference per option."""
+    model, sd = build_reference(cfg, seed)
+    dit = O.OracleDiT(cfg, sd)
+    g = torch.Generator().manual_seed(seed + 1)
+    ref_len = torch.randint(12, 20, (batch,), generator=g)
+    dur = torch.randint(40, 64, (batch,), generator=g)
+    tlen = torch.randint(5, 15, (batch,), generator=g)
+    cond = torch.randn(batch, int(ref_len.max()), cfg.mel_dim, generator=g)
+    text = torch.full((batch, int(tlen.max())), -1, dtype=torch.long)
+    for i in range(batch):
+        text[i, : tlen[i]] = torch.randint(0, cfg.text_num_embeds, (int(tlen[i]),), generator=g)
+    long_text = torch.randint(0, cfg.text_num_embeds, (batch, 70), generator=g)
+    long_text[1, 52:] = -1
+    edit_mask = torch.ones(batch, int(ref_len.max()), dtype=torch.bool)
+    edit_mask[:, 5:9] = False
+    edit_mask[0, 2] = False
+    fix = dict(cfg=cfg.__dict__, seed=seed, cond=cond, text=text, long_text=long_text, edit_mask=edit_mask, duration_in=dur,
+               lens=ref_len, cases={})
+    for cname, spec in OPTION_CASES.items():
+        kw = dict(steps=spec.get("steps", 4), cfg_strength=2.0, sway_sampling_coef=-1.0, seed=7)
+        kw.update(spec.get("kw", {}))
+        tx = long_text if spec.get("long_text") else text
+        d_in = spec.get("int_duration", dur)
+        ln = None if spec.get("no_lens") else ref_len
+        extra = dict(edit_mask=edit_mask) if spec.get("edit") else {}
+        voc = _toy_vocoder if spec.get("vocoder") else None
+        with torch.no_grad():
+            out, traj = model.sample(cond=cond, text=tx, ppg=None, duration=d_in, lens=ln, vocoder=voc, **extra, **kw)
+        o_out, o_traj, aux = O.cfm_sample(dit, cond, tx, d_in, lens=ln, return_aux=True, vocoder=voc, **extra, **kw)
+        print(f"[{name}/{cname}] oracle vs reference: out max-abs {(o_out - out).abs().max():.2e}; traj rel-L2 {rel(o_traj, traj):.2e} "
+              f"({traj.shape[0] - 1} steps); duration {aux['duration'].tolist()}")
+        assert traj.shape == o_traj.shape
+        c = dict(kw=kw, out=out, n_states=traj.shape[0], duration=aux["duration"], mask=aux["mask"], cond_mask=aux["cond_mask"])
+        if spec.get("vocoder"):
+            c["traj_last"] = traj[-1]       # `out` is the vocoded wave there
+        if "duplicate_test" in kw:
+            c["traj_0"] = traj[0]           # the blended start state (cfm.py:463)
+        fix["cases"][cname] = c
+    torch.save(fix, os.path.join(OUT, name + ".pt"))
+
+
 def case_sample3(name, cfg, batch, seed, mode):
     """CFM.sample_tts / CFM.sample_vc (three-way guidance, cfm.py:93-346) on the PPG-conditioned small model."""
     model, sd = build_reference(cfg, seed)
@@ -231,6 +290,7 @@ if __name__ == "__main__":
     case_sample("sample_b1", SMALL, 1, 200)
     case_sample("sample_b3", SMALL, 3, 201)
     case_sample("sample_b2_ppg", SMALL_PPG, 2, 202, with_ppg=True)
+    case_sample_options("sample_options_b3", SMALL, 3, 205)
     case_sample3("sample_tts_b2", SMALL_PPG, 2, 203, "tts")
     case_sample3("sample_vc_b2", SMALL_PPG, 2, 204, "vc")
     SMALL_PPG_TR = O.DiTConfig(dim=256, depth=2, heads=4, text_dim=64, conv_layers=2, text_num_embeds=50,

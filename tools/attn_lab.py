@@ -38,6 +38,8 @@ def main():
     ap.add_argument("--ragged", action="store_true", help="per-sample key lengths uniform in [npad/3, npad]")
     ap.add_argument("--trace", default="")
     ap.add_argument("--sdpa", action="store_true")
+    ap.add_argument("--sustain", type=float, default=0.0, help="also time the kernel back to back for this many seconds "
+                    "(power-capped clocks, what the DiT step sees) with board power sampled from nvidia-smi")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     _lib.require_device()
@@ -65,6 +67,23 @@ def main():
     flops = 4.0 * 16 * 64 * float((klen.double() ** 2).sum())
     r = dict(variant=os.environ.get("F5E_LIB_SUFFIX", "product"), ms=round(ms, 4), tflops=round(flops / ms / 1e9, 1),
              max_abs_err=round(err, 5), samples=S, npad=N, ragged=a.ragged)
+    if a.sustain > 0:
+        import subprocess
+        import tempfile
+        n = max(20, int(a.sustain * 1e3 / ms))
+        f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        p = subprocess.Popen(["nvidia-smi", "-i", "0", "--query-gpu=power.draw,clocks.sm", "--format=csv,noheader,nounits",
+                              "-lms", "50"], stdout=f, stderr=subprocess.DEVNULL)
+        sus = timeit(lambda: ops.attention(qkv, H, klen=klen, n_pad=N, out=o), iters=n, warm=1)
+        p.terminate()
+        p.wait(timeout=5)
+        rows = [x.strip().split(", ") for x in open(f.name) if x.strip()][8:]
+        os.unlink(f.name)
+        r["sustained_ms"] = round(sus, 4)
+        if rows:
+            r["watts"] = round(sum(float(x[0]) for x in rows) / len(rows), 1)
+            r["sm_mhz"] = sorted(float(x[1]) for x in rows)[len(rows) // 2]
+            r["mj_per_launch"] = round(r["watts"] * sus, 1)
     if a.sdpa:
         q, k, v = qkv.view(S, N, 3, H, 64).permute(2, 0, 3, 1, 4)
         r["sdpa_ms"] = round(timeit(lambda: torch.nn.functional.scaled_dot_product_attention(q, k, v)), 4)
