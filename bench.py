@@ -157,27 +157,61 @@ def measured_peaks():
 # ----------------------------------------------------------------------------------------------------------------------
 # CPU arm: the reference algorithm (oracle port, torch fp32) on the host cores
 # ----------------------------------------------------------------------------------------------------------------------
+def _reference_model(sd_fp32):
+    """The UNMODIFIED reference (oracle/_ref, copied from /root/reference by oracle/make_ref.py at build time) with the bench
+    weights, on the CPU in fp32; None when oracle/_ref has not been made (then the oracle port is timed instead)."""
+    import torch
+
+    try:
+        from oracle.make_ref import import_reference
+
+        CFM, DiT = import_reference()
+    except Exception:
+        return None
+    if CFM is None:
+        return None
+    dit = DiT(**ARCH)
+    missing, unexpected = dit.load_state_dict(sd_fp32, strict=False)
+    assert not unexpected, unexpected
+    model = CFM(transformer=dit, mel_spec_kwargs=dict()).eval()
+    return model.to(torch.float32)
+
+
 def cpu_arm(sd_fp32, w, nfe, budget_s):
     """Times `CFM.sample`'s per-step work for ONE utterance of the workload on the host cores and extrapolates linearly
-    to the full solve (+ the oracle Vocos decode, timed in full).  Returns audio-s/s and a description of the sample."""
+    to the full solve (+ the Vocos decode, timed in full on the oracle's restatement: the `vocos` package is not installed).
+    The sampler is the reference's own code when oracle/_ref exists (kind "reference"), else the oracle port (kind "port").
+    Returns audio-s/s and a description of the sample."""
     import torch
 
     from oracle import f5e_oracle as O
 
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    cfg = O.DiTConfig()
-    dit = O.OracleDiT(cfg, sd_fp32, torch.float32, "cpu")
     i = 0
     ref_len, dur = int(w["ref_len"][i]), int(w["dur"][i])
     mel = O.mel_spectrogram(w["ref_wav"][i: i + 1, : ref_len * HOP]).permute(0, 2, 1)[:, :ref_len]
     text = w["text"][i: i + 1]
     text = text[:, : int((text != -1).sum())]
+    ref_model = _reference_model(sd_fp32)
+    if ref_model is not None:
+        kind = "reference"
+
+        def solve(k):
+            with torch.no_grad():
+                ref_model.sample(cond=mel, text=text, ppg=None, duration=dur, lens=torch.tensor([ref_len]), steps=k, cfg_strength=2.0,
+                                 sway_sampling_coef=-1.0, seed=0)
+    else:
+        kind = "port"
+        dit = O.OracleDiT(O.DiTConfig(), sd_fp32, torch.float32, "cpu")
+
+        def solve(k):
+            O.cfm_sample(dit, mel, text, dur, lens=torch.tensor([ref_len]), steps=k, cfg_strength=2.0, sway_sampling_coef=-1.0, seed=0)
     steps_done, t_used = 0, 0.0
     k = 1
     while True:  # k Euler steps per probe until the budget is used; the per-step cost is what is extrapolated
         t0 = time.perf_counter()
-        O.cfm_sample(dit, mel, text, dur, lens=torch.tensor([ref_len]), steps=k, cfg_strength=2.0, sway_sampling_coef=-1.0, seed=0)
+        solve(k)
         t_used += time.perf_counter() - t0
         steps_done += k
         if t_used >= budget_s or steps_done >= nfe:
@@ -192,9 +226,12 @@ def cpu_arm(sd_fp32, w, nfe, budget_s):
         O.vocos_decode(vsd, m)
         voc_s = time.perf_counter() - t0
     audio = (dur - ref_len) * HOP / SR
-    return dict(value=audio / (total + voc_s), unit=UNIT, cores=cores, kind="port", steps_timed=steps_done,
-                sample=f"oracle port (torch fp32) on {cores} host threads: utterance 0 of the workload ({dur} frames, {ref_len} ref), "
-                       f"{steps_done} of {nfe} Euler steps timed ({t_used:.1f} s) and extrapolated linearly, Vocos decode timed in full"), per_step
+    what = ("the unmodified reference (oracle/_ref: f5_tts.model.CFM.sample, torch fp32)" if kind == "reference"
+            else "oracle port (torch fp32)")
+    return dict(value=audio / (total + voc_s), unit=UNIT, cores=cores, kind=kind, steps_timed=steps_done,
+                sample=f"{what} on {cores} host threads: utterance 0 of the workload ({dur} frames, {ref_len} ref), "
+                       f"{steps_done} of {nfe} Euler steps timed ({t_used:.1f} s) and extrapolated linearly, Vocos decode "
+                       f"(oracle restatement; the vocos package is absent) timed in full"), per_step
 
 
 def reference_weights():
@@ -403,8 +440,9 @@ def eval_set_leg(model, vocoder, dev, rank, world, n_utt, nfe=16):
                      " " + "some generated words " * int(1 + 4 * torch.rand(1, generator=g).item()), None))
     prompts = P.get_inference_prompt(meta, device=dev, infer_batch_size=16 * 1031, num_buckets=200, min_secs=3, max_secs=40)
     E.infer_batches(model, vocoder, prompts[:1], nfe_step=nfe, seed=0)  # warm-up
-    if world > 1:
-        fdist.gather_varlen(torch.ones(1, device=dev, dtype=torch.int64), torch.zeros(1, device=dev), dst=0)
+    if world > 1:  # NCCL builds its peer channels lazily and the allocator has not seen buffers of this size yet: warm both
+        for n in (1, 32 << 20):
+            fdist.gather_varlen(torch.ones(1, device=dev, dtype=torch.int64) * n, torch.zeros(n, device=dev), dst=0)
         dist.barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()

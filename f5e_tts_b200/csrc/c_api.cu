@@ -14,6 +14,7 @@ static EpiParams to_epi(const f5e_epilogue* e, int M) {
   p.rope_inner = e->rope_inner; p.rope_heads = e->rope_heads;
   p.res_f32 = e->residual_f32; p.split3 = e->out_split3; p.row_info = e->row_info;
   p.rope_inv_freq = e->rope_inv_freq;
+  p.ln_rstd = e->ln_rstd; p.ln_a2 = reinterpret_cast<const __nv_bfloat16*>(e->ln_a2);
   return p;
 }
 
@@ -49,6 +50,22 @@ int f5e_norm_mod(const void* x, void* out, int32_t M, int32_t D, const float* mu
   F5E_REQUIRE(x && out && mul && add, "f5e_norm_mod: null argument");
   return norm_mod((cudaStream_t)stream, (const __nv_bfloat16*)x, (__nv_bfloat16*)out, M, D, mul, add, mod_stride,
                   n_pad, plus_one, eps);
+}
+
+int f5e_row_stats(const void* x, float* rstd, void* a2, int32_t M, int32_t D, float eps, void* stream) {
+  F5E_REQUIRE(x && rstd && a2, "f5e_row_stats: null argument");
+  return row_stats((cudaStream_t)stream, (const __nv_bfloat16*)x, rstd, (__nv_bfloat16*)a2, M, D, eps);
+}
+
+int f5e_fold_ln_weights(const f5e_fold_job* jobs_dev, int32_t n_jobs, int32_t total_rows, int32_t D, const float* mod,
+                        void* stream) {
+  F5E_REQUIRE(jobs_dev && mod, "f5e_fold_ln_weights: null argument");
+  return fold_ln_weights((cudaStream_t)stream, reinterpret_cast<const FoldJob*>(jobs_dev), n_jobs, total_rows, D, mod);
+}
+
+int f5e_gather_rows(const void* src, void* dst, const int32_t* row_map, int32_t rows, int32_t C, void* stream) {
+  F5E_REQUIRE(src && dst && row_map && rows > 0 && C % 8 == 0, "f5e_gather_rows: bad arguments");
+  return gather_rows((cudaStream_t)stream, (const __nv_bfloat16*)src, (__nv_bfloat16*)dst, row_map, rows, C);
 }
 
 int f5e_cfg_euler(const float* pred, int32_t ld_pred, float* y, void* x_cat, int32_t ld_cat, float* traj,

@@ -69,6 +69,7 @@ int dwconv7_f32(cudaStream_t st, const float* x, const float* w, const float* b,
 int unfold_mel_split3(cudaStream_t st, const float* mel, long long ld_b, long long ld_c, long long ld_t, const int* t_off,
                       const int* n_frames, int batch, int t_pad, int C, int taps, int kpad, __nv_bfloat16* out);
 int split3(cudaStream_t st, const float* x, long long ld, int M, int K, __nv_bfloat16* out);
+int softmax_split3(cudaStream_t st, const float* logits, int ld, int M, int V, int kpad, __nv_bfloat16* out);
 int vq_select(cudaStream_t st, const float* logits, int ld_logits, const float* x, int ld_x, int dim, const float* W,
               const float* bias, const float* vars, int M, int G, int V, int vd, int combine_groups, float refine_tol,
               long long* targets, void* xq, int xq_bf16, float* sums, int* hist, int* refined, float* perplexity);

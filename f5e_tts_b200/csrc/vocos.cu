@@ -90,6 +90,11 @@ int f5e_vq_quantize(const float* x, int32_t ld_x, int32_t M, int32_t dim, const 
                    refine_tol, reinterpret_cast<long long*>(targets), xq, xq_bf16, prob_sums, hist, n_refined, perplexity);
 }
 
+int f5e_softmax_split3(const float* logits, int32_t ld, int32_t M, int32_t V, int32_t kpad, void* out_bf16, void* stream) {
+  F5E_REQUIRE(logits && out_bf16, "f5e_softmax_split3: null argument");
+  return softmax_split3((cudaStream_t)stream, logits, ld, M, V, kpad, reinterpret_cast<__nv_bfloat16*>(out_bf16));
+}
+
 int f5e_split3(const float* x, int64_t ld, int32_t M, int32_t K, void* out_bf16, void* stream) {
   F5E_REQUIRE(x && out_bf16, "f5e_split3: null argument");
   return split3((cudaStream_t)stream, x, ld, M, K, reinterpret_cast<__nv_bfloat16*>(out_bf16));

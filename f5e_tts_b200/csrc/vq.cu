@@ -132,6 +132,38 @@ vq_perplexity_kernel(const int* __restrict__ hist, const float* __restrict__ sum
   if (threadIdx.x == 0) { out[0] = tot_c; out[1] = tot_p; }
 }
 
+// softmax over the first V columns of every row of fp32 logits [M, ld], written as the 3-term bf16 split [hi | hi | lo]
+// of width kpad (columns >= V zero): the A operand of a following fp32-accurate bf16x3 GEMM.  One warp per row.
+// (PPGModelWapper.ppg_to_target, output_type "map": logit.softmax(-1) @ global_phn_center, ppg/ppg_model.py:113-118)
+__global__ void __launch_bounds__(256)
+softmax_split3_kernel(const float* __restrict__ logits, int ld, int M, int V, int kpad, __nv_bfloat16* __restrict__ out) {
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= M) return;
+  const float* lr = logits + (size_t)row * ld;
+  float mx = -INFINITY;
+  for (int j = lane; j < V; j += 32) mx = fmaxf(mx, lr[j]);
+  mx = warp_max(mx);
+  float se = 0.f;
+  for (int j = lane; j < V; j += 32) se += expf(lr[j] - mx);
+  const float inv = 1.0f / warp_sum(se);
+  __nv_bfloat16* orow = out + (size_t)row * 3 * kpad;
+  for (int j = lane; j < kpad; j += 32) {
+    const float p = j < V ? expf(lr[j] - mx) * inv : 0.f;
+    const __nv_bfloat16 h = __float2bfloat16(p);
+    orow[j] = h;
+    orow[kpad + j] = h;
+    orow[2 * kpad + j] = __float2bfloat16(p - __bfloat162float(h));
+  }
+}
+
+int softmax_split3(cudaStream_t st, const float* logits, int ld, int M, int V, int kpad, __nv_bfloat16* out) {
+  F5E_REQUIRE(M > 0 && V > 0 && kpad >= V && kpad % 8 == 0 && ld >= V, "softmax_split3: bad shape (M=%d V=%d kpad=%d ld=%d)", M, V, kpad, ld);
+  LaunchScope ls(st, PROF_VQ, M, V, -2);
+  softmax_split3_kernel<<<(M + 7) / 8, 256, 0, st>>>(logits, ld, M, V, kpad, out);
+  F5E_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
 int vq_select(cudaStream_t st, const float* logits, int ld_logits, const float* x, int ld_x, int dim, const float* W,
               const float* bias, const float* vars, int M, int G, int V, int vd, int combine_groups, float refine_tol,
               long long* targets, void* xq, int xq_bf16, float* sums, int* hist, int* refined, float* perplexity) {

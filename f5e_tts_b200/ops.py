@@ -18,12 +18,17 @@ def _cuda_bf16(t: torch.Tensor, name: str) -> None:
 
 
 def gemm(a, w, *, bias=None, act=_lib.ACT_NONE, gate=None, gate_stride=0, residual=None, row_len=None, n_pad=0,
-         rope=None, rope_heads=0, rope_inner=0, out=None, out_f32=False, n=None, split3=0):
-    """epilogue(a[M,K] @ w[N,K]^T).  `a`/`w` may be row-strided views (last dim contiguous)."""
+         rope=None, rope_heads=0, rope_inner=0, out=None, out_f32=False, n=None, split3=0, ln_rstd=None, ln_a2=None):
+    """epilogue(a[M,K] @ w[N,K]^T).  `a`/`w` may be row-strided views (last dim contiguous).
+    ln_rstd / ln_a2 (from `row_stats`): LayerNorm folded in - `w` is then the folded weight [N, K + 64] of `fold_ln_weights`
+    and `bias` its `d` vector."""
     _cuda_bf16(a, "a"), _cuda_bf16(w, "w")
     assert a.dim() == 2 and w.dim() == 2 and a.stride(1) == 1 and w.stride(1) == 1
     M, K = a.shape
     N = w.shape[0] if n is None else n
+    if ln_rstd is not None:
+        assert ln_a2 is not None and w.shape[1] == K + 64 and ln_rstd.dtype == torch.float32 and ln_a2.dtype == torch.bfloat16
+        K += 64
     assert w.shape[1] == K
     if out is None:
         out = torch.empty(M, 3 * split3 if split3 else N, device=a.device, dtype=torch.float32 if out_f32 else torch.bfloat16)
@@ -43,6 +48,8 @@ def gemm(a, w, *, bias=None, act=_lib.ACT_NONE, gate=None, gate_stride=0, residu
         assert rope.dtype == torch.float32 and rope.numel() == 32 and rope.is_contiguous()
         ep.rope_inv_freq = rope.data_ptr()
         ep.rope_inner, ep.rope_heads = rope_inner, rope_heads
+    if ln_rstd is not None:
+        ep.ln_rstd, ep.ln_a2 = ln_rstd.data_ptr(), ln_a2.data_ptr()
     for t in (bias, gate):
         assert t is None or t.dtype == torch.float32
     assert row_len is None or row_len.dtype == torch.int32
@@ -176,4 +183,41 @@ def unfold_frames(x, taps):
     B, N, Cc = x.shape
     out = torch.empty(B, N, taps * Cc, device=x.device, dtype=torch.bfloat16)
     check(_lib.load().f5e_unfold_frames(ptr(x), ptr(out), B, N, Cc, taps, stream_ptr()), "f5e_unfold_frames")
+    return out
+
+
+def row_stats(x, eps=1e-6):
+    """LayerNorm statistics of bf16 x [M, D] for the folded path -> (rstd fp32 [M], a2 bf16 [M, 64] = -mean as hi | lo | hi)."""
+    _cuda_bf16(x, "x")
+    assert x.dim() == 2 and x.is_contiguous()
+    M, D = x.shape
+    rstd = torch.empty(M, device=x.device, dtype=torch.float32)
+    a2 = torch.zeros(M, 64, device=x.device, dtype=torch.bfloat16)
+    check(_lib.load().f5e_row_stats(ptr(x), ptr(rstd), ptr(a2), M, D, C.c_float(eps), stream_ptr()), "f5e_row_stats")
+    return rstd, a2
+
+
+def fold_ln_weights(w, bias, scale, shift):
+    """One job of f5e_fold_ln_weights: w bf16 [N, D], bias fp32 [N] or None, scale / shift fp32 [D] ->
+    (wf bf16 [N, D + 64], c fp32 [N], d fp32 [N]) with (LN(x) (1 + scale) + shift) @ w^T + bias == rstd (x . wf - mean c) + d."""
+    from .model import _FoldJob
+
+    _cuda_bf16(w, "w")
+    N, D = w.shape
+    dev = w.device
+    wf = torch.zeros(N, D + 64, device=dev, dtype=torch.bfloat16)
+    c, d = torch.empty(N, device=dev), torch.empty(N, device=dev)
+    mod = torch.cat([scale.float(), shift.float()]).contiguous()
+    job = _FoldJob(w.data_ptr(), 0 if bias is None else bias.data_ptr(), wf.data_ptr(), c.data_ptr(), d.data_ptr(), N, 0, 0, D)
+    jobs = torch.frombuffer(bytearray(bytes(job)), dtype=torch.uint8).to(dev)
+    check(_lib.load().f5e_fold_ln_weights(ptr(jobs), 1, N, D, ptr(mod), stream_ptr()), "f5e_fold_ln_weights")
+    return wf, c, d
+
+
+def gather_rows(src, row_map):
+    _cuda_bf16(src, "src")
+    assert src.dim() == 2 and src.is_contiguous() and row_map.dtype == torch.int32
+    out = torch.empty(row_map.numel(), src.shape[1], device=src.device, dtype=torch.bfloat16)
+    check(_lib.load().f5e_gather_rows(ptr(src), ptr(out), ptr(row_map), row_map.numel(), src.shape[1], stream_ptr()),
+          "f5e_gather_rows")
     return out

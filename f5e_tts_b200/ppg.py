@@ -9,6 +9,7 @@ utterances of different length: every utterance gets the frames a batch-1 call w
 from __future__ import annotations
 
 import math
+import os
 
 import torch
 from torch import nn
@@ -354,14 +355,48 @@ class ASRModel:
         return out * valid.unsqueeze(-1)
 
 
+def _load_table(x, what):
+    """A table given as a tensor / array, or the path the reference loads it from (np.load / pickle, ppg_model.py:82-92)."""
+    if isinstance(x, (str, os.PathLike)):
+        if str(x).endswith(".npy"):
+            import numpy as np
+            x = np.load(x)
+        else:
+            import pickle
+            with open(x, "rb") as f:
+                x = pickle.load(f)
+    if x is None:
+        raise ValueError(f"f5e_tts_b200.PPGModelWapper(output_type='map') needs {what} (a tensor / array or the file the "
+                         "reference loads; the reference's default paths point outside the tree)")
+    return x
+
+
 class PPGModelWapper(object):
-    """ppg/ppg_model.py:59-168 (output_type "ppg"; the "map" variant needs phone-centre tables that live outside the tree).
-    Pass either the reference's `ppg_model_path` + `ppg_config` (train.yaml + checkpoint) or a ready `model`."""
+    """ppg/ppg_model.py:59-168.  Pass either the reference's `ppg_model_path` + `ppg_config` (train.yaml + checkpoint) or a
+    ready `model`.  output_type "map" (softmax over a phone dictionary, then the phone-centre projection, :113-121) takes its
+    two tables as arguments - `global_phn_center` [dict, ppg_dim] and `para_softmax` {'w': [dict, ppg_dim], 'b': [dict]},
+    tensors / arrays or the .npy / pickle paths the reference's keyword arguments of the same names hold."""
 
     def __init__(self, ppg_model_path=None, ppg_config=None, device="cuda", output_type="ppg", map_mix_ratio=1.0,
-                 ppg_frame_length=20, mel_f_shift=10, model: ASRModel | None = None, **_unused):
-        if output_type != "ppg":
-            raise NotImplementedError("f5e_tts_b200.PPGModelWapper: only output_type='ppg' (the 'map' tables are not in the tree)")
+                 ppg_frame_length=20, mel_f_shift=10, model: ASRModel | None = None, global_phn_center=None, para_softmax=None,
+                 global_phn_center_path=None, para_softmax_path=None, **_unused):
+        if output_type not in ("ppg", "map"):
+            raise ValueError(f"f5e_tts_b200.PPGModelWapper: output_type must be 'ppg' or 'map', not {output_type!r}")
+        self._map = None
+        if output_type == "map":
+            center = torch.as_tensor(_load_table(global_phn_center if global_phn_center is not None else global_phn_center_path,
+                                                 "global_phn_center")).float()
+            ps = _load_table(para_softmax if para_softmax is not None else para_softmax_path, "para_softmax")
+            w, b = torch.as_tensor(ps["w"]).float(), torch.as_tensor(ps["b"]).float()
+            V, dim = w.shape
+            assert center.shape == (V, dim) and b.shape == (V,), (center.shape, w.shape, b.shape)
+            from .vocos import split3_weight
+            dev = torch.device(device)
+            kpad = (V + 63) // 64 * 64  # K of the second GEMM, padded to whole 64-column blocks
+            ct = torch.zeros(dim, kpad)
+            ct[:, :V] = center.t()
+            self._map = dict(V=V, dim=dim, kpad=kpad, ldl=(V + 3) // 4 * 4, w3=split3_weight(w.to(dev)), b=b.to(dev).contiguous(),
+                             c3=split3_weight(ct.to(dev)))
         if model is None:
             import yaml
             with open(ppg_config, "r") as fin:
@@ -400,8 +435,31 @@ class PPGModelWapper(object):
             lens = lens.expand(ppg.shape[0])
         own = torch.where(lens >= 3, (lens - 3) // 2 + 1, torch.zeros_like(lens))
         true_len = torch.minimum(ppg_true_len(lens, ppg.shape[1], self.ppg_frame_length, self.mel_f_shift), own)
-        ppg = ppg * (~make_pad_mask(true_len, ppg.shape[1]))[:, :, None]
+        ppg = self.ppg_to_target(ppg, true_len)
         return ppg, true_len
+
+    @torch.no_grad()
+    def ppg_to_target(self, ppg, true_len):
+        """ppg_model.py:108-127: output_type "ppg" masks the padded frames; "map" first projects every frame onto the phone
+        centres: softmax(ppg @ w^T + b) @ global_phn_center, mixed with the raw PPG by map_mix_ratio.  Both GEMMs are the
+        fp32-accurate bf16x3 tcgen05 GEMM, the softmax one warp per frame."""
+        mask = (~make_pad_mask(true_len, ppg.shape[1]))[:, :, None]
+        if self._map is None:
+            return ppg * mask
+        P = self._map
+        B, T, dim = ppg.shape
+        assert dim == P["dim"], (dim, P["dim"])
+        lib, st, M = _lib.load(), stream_ptr(), B * T
+        x = ppg.reshape(M, dim).float().contiguous()
+        a3 = torch.empty(M, 3 * dim, device=x.device, dtype=torch.bfloat16)
+        check(lib.f5e_split3(ptr(x), dim, M, dim, ptr(a3), st), "f5e_split3")
+        logits = ops.gemm(a3, P["w3"], bias=P["b"], out=torch.empty(M, P["ldl"], device=x.device), n=P["V"])
+        p3 = torch.empty(M, 3 * P["kpad"], device=x.device, dtype=torch.bfloat16)
+        check(lib.f5e_softmax_split3(ptr(logits), P["ldl"], M, P["V"], P["kpad"], ptr(p3), st), "f5e_softmax_split3")
+        mapped = ops.gemm(p3, P["c3"], out_f32=True).view(B, T, dim)
+        if self.map_mix_ratio != 1.0:
+            mapped = ppg * (1 - self.map_mix_ratio) + mapped * self.map_mix_ratio
+        return mapped * mask
 
     @torch.no_grad()
     def audio_to_ppg(self, audio, sr=None, lens=None):

@@ -64,6 +64,9 @@ typedef struct f5e_epilogue {
   const float* rope_inv_freq; /* [32] or NULL: interleaved-pair RoPE on the Q and K column blocks; the angles
                               frame * inv_freq[j] are evaluated in the epilogue (x_transformers RotaryEmbedding.inv_freq,
                               reference backbones/dit.py:245, modules.py:470-480) */
+  const float* ln_rstd;    /* [M] or NULL: LayerNorm folded into this GEMM (see f5e_fold_job): v = acc * rstd[row] + bias[col] */
+  const void* ln_a2;       /* bf16 [M, 64], with ln_rstd: A operand of the LAST K block (K = dim + 64), the row's -mean
+                              as (hi, lo, hi, 0 ...); both written by f5e_row_stats */
 } f5e_epilogue;
 
 /* C[M,N] = epilogue(A[M,K] @ W[N,K]^T); bf16 operands, tcgen05 / TMEM fp32 accumulation.
@@ -251,6 +254,16 @@ typedef struct f5e_dit_packing {
   int32_t rows_packed;
 } f5e_dit_packing;
 
+/* The two helper kernels of the folded-LayerNorm path (exported for unit tests; f5e_ode_solve calls them itself).
+ * f5e_row_stats: per row of x (bf16 [M, D], D % 256 == 0): rstd[r] = 1 / sqrt(var + eps) and a2[r, 0..2] = bf16 split of
+ * -mean as (hi, lo, hi), a2[r, 3..63] untouched (zero-initialised by the caller).  F.layer_norm's statistics,
+ * model/modules.py:310-315.  f5e_fold_ln_weights: one launch rewrites W' | c | d of every job from `mod`. */
+int f5e_row_stats(const void* x, float* rstd, void* a2, int32_t M, int32_t D, float eps, void* stream);
+int f5e_fold_ln_weights(const f5e_fold_job* jobs_dev, int32_t n_jobs, int32_t total_rows, int32_t D, const float* mod,
+                        void* stream);
+/* dst[r, :] = src[row_map[r], :] (bf16, C % 8 == 0): the packing step of f5e_dit_packing. */
+int f5e_gather_rows(const void* src, void* dst, const int32_t* row_map, int32_t rows, int32_t C, void* stream);
+
 /* One flow evaluation over `samples` sequences of n_pad frames (DiT.sample after the embeddings:
  * backbones/dit.py:450-470).  mod: fp32 modulation vectors for this time step, laid out
  * [depth][shift_msa|scale_msa|gate_msa|shift_mlp|scale_mlp|gate_mlp][dim] then [scale|shift][dim] of norm_out
@@ -398,6 +411,11 @@ int f5e_vq_quantize(const float* x, int32_t ld_x, int32_t M, int32_t dim, const 
 
 /* fp32 [M, K] -> bf16 [M, 3K] = [hi | hi | lo]: the A operand of a bf16x3 GEMM (test hook / building block). */
 int f5e_split3(const float* x, int64_t ld, int32_t M, int32_t K, void* out_bf16, void* stream);
+
+/* Row softmax over the first V columns of fp32 logits [M, ld] -> bf16 [M, 3 * kpad] as the split [hi | hi | lo] (columns
+ * >= V zero; kpad % 8 == 0): the A operand of the fp32-accurate GEMM with the phone-centre table in
+ * PPGModelWapper.ppg_to_target, output_type "map" (ppg/ppg_model.py:113-118: logit.softmax(-1) @ global_phn_center). */
+int f5e_softmax_split3(const float* logits, int32_t ld, int32_t M, int32_t V, int32_t kpad, void* out_bf16, void* stream);
 
 #ifdef __cplusplus
 }

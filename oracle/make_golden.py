@@ -282,7 +282,32 @@ def case_ppg_conformer(name, causal=False, cnn_norm="batch_norm"):
                os.path.join(OUT, name + ".pt"))
 
 
+def case_ppg_map(name):
+    """PPGModelWapper.ppg_to_target with output_type "map" (ppg_model.py:108-127) of the reference itself; the wrapper's
+    __init__ loads a checkpoint and two tables from paths outside the tree, so the object is built without it."""
+    from f5_tts.ppg.ppg_model import PPGModelWapper
+    from oracle import ppg_oracle as PO
+
+    g = torch.Generator().manual_seed(321)
+    B, T, dim, V = 2, 23, 64, 77
+    ppg = torch.randn(B, T, dim, generator=g)
+    true_len = torch.tensor([23, 17])
+    w, b = torch.randn(V, dim, generator=g) / 4, torch.randn(V, generator=g)
+    center = torch.randn(V, dim, generator=g)
+    out = {}
+    for ratio in (1.0, 0.35):
+        ref = object.__new__(PPGModelWapper)
+        ref.output_type, ref.map_mix_ratio = "map", ratio
+        ref.global_phn_center, ref.para_softmax = center, dict(w=w, b=b)
+        out[ratio] = ref.ppg_to_target(ppg, true_len)
+        mine = PO.ppg_to_target(ppg, true_len, "map", w, b, center, ratio)
+        print(f"[{name}] ratio {ratio}: oracle vs reference max-abs {(mine - out[ratio]).abs().max():.2e}")
+    torch.save(dict(ppg=ppg, true_len=true_len, w=w, b=b, center=center, out_1=out[1.0], out_035=out[0.35]),
+               os.path.join(OUT, name + ".pt"))
+
+
 if __name__ == "__main__":
+    case_ppg_map("ppg_map")
     case_mel("melspec")
     case_vq("vq")
     case_single_eval("dit_eval_small", SMALL, 100)

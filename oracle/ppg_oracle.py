@@ -267,3 +267,17 @@ def get_vc_inference_prompt(metainfo, cfg: ConformerConfig, sd: dict, speed=1.0,
     random.seed(666)
     random.shuffle(prompts_all)
     return prompts_all
+
+
+def ppg_to_target(ppg, true_len, output_type="ppg", para_w=None, para_b=None, phn_center=None, map_mix_ratio=1.0):
+    """PPGModelWapper.ppg_to_target (ppg/ppg_model.py:108-127): mask the padded frames; output_type "map" first projects
+    every frame onto the phone centres: softmax(ppg @ w^T + b) @ global_phn_center, mixed with the raw PPG by map_mix_ratio."""
+    T = ppg.shape[1]
+    keep = (torch.arange(T, device=ppg.device)[None, :] < true_len[:, None])[:, :, None]  # ~make_pad_mask(true_len)
+    if output_type == "map":
+        logit = ppg @ para_w.T + para_b
+        map_ppg = logit.softmax(dim=-1) @ phn_center
+        ret = map_ppg if map_mix_ratio == 1.0 else ppg * (1 - map_mix_ratio) + map_ppg * map_mix_ratio
+    else:
+        ret = ppg
+    return ret * keep

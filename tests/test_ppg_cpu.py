@@ -72,3 +72,18 @@ def test_oracle_conformer_causal_layernorm_matches_reference_golden():
     got = PO.conformer_extract(cfg, sd, fx["feats"])
     rel = ((got - fx["ppg"]).norm() / fx["ppg"].norm()).item()
     assert rel < 1e-5, rel
+
+
+def test_ppg_map_golden():
+    """output_type "map" (ppg_model.py:108-127) of the oracle against the reference's own PPGModelWapper.ppg_to_target."""
+    import os
+
+    import torch
+
+    from oracle import ppg_oracle as PO
+
+    d = torch.load(os.path.join(os.path.dirname(__file__), "golden", "ppg_map.pt"), weights_only=False)
+    for ratio, key in ((1.0, "out_1"), (0.35, "out_035")):
+        got = PO.ppg_to_target(d["ppg"], d["true_len"], "map", d["w"], d["b"], d["center"], ratio)
+        assert torch.allclose(got, d[key], atol=1e-6, rtol=1e-6)
+        assert (got[1, 17:] == 0).all()

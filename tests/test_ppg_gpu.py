@@ -309,3 +309,40 @@ def test_get_vc_inference_prompt_and_eval_loop(cuda_dev):
     assert by_utt[utts[0]].shape == (1, n0) and torch.allclose(by_utt[utts[0]][0], w0, atol=1e-6)
     two = infer_batches(model, voc, got, device=cuda_dev, rank=0, world=2, **kw) + infer_batches(model, voc, got, device=cuda_dev, rank=1, world=2, **kw)
     assert sorted(u for u, _ in two) == sorted(by_utt) and all(torch.equal(w, by_utt[u]) for u, w in two)
+
+
+def test_ppg_map_output(cuda_dev):
+    """PPGModelWapper(output_type="map") with the tables passed as arguments: softmax(ppg @ w^T + b) @ global_phn_center on
+    the fp32-accurate GEMMs + the row-softmax kernel, against the reference-generated fixture (and the oracle at a wider
+    shape); padded frames exactly zero."""
+    import os
+
+    from f5e_tts_b200.ppg import PPGModelWapper
+    from oracle import ppg_oracle as PO
+
+    d = torch.load(os.path.join(os.path.dirname(__file__), "golden", "ppg_map.pt"), weights_only=False)
+    for ratio, key in ((1.0, "out_1"), (0.35, "out_035")):
+        wr = object.__new__(PPGModelWapper)   # the table handling of __init__ without an ASR checkpoint
+        PPGModelWapper.__init__(wr, model=_tiny_asr(cuda_dev), device=cuda_dev, output_type="map", map_mix_ratio=ratio,
+                                global_phn_center=d["center"], para_softmax=dict(w=d["w"], b=d["b"]))
+        got = wr.ppg_to_target(d["ppg"].to(cuda_dev), d["true_len"].to(cuda_dev))
+        assert torch.allclose(got.cpu(), d[key], atol=2e-5, rtol=1e-4), (got.cpu() - d[key]).abs().max()
+        assert (got[1, 17:] == 0).all()
+    g = torch.Generator().manual_seed(5)
+    B, T, dim, V = 3, 470, 256, 601
+    ppg = torch.randn(B, T, dim, generator=g)
+    tl = torch.tensor([470, 300, 1])
+    w, b, c = torch.randn(V, dim, generator=g) / 16, torch.randn(V, generator=g), torch.randn(V, dim, generator=g)
+    wr = object.__new__(PPGModelWapper)
+    PPGModelWapper.__init__(wr, model=_tiny_asr(cuda_dev), device=cuda_dev, output_type="map", global_phn_center=c,
+                            para_softmax=dict(w=w, b=b))
+    got = wr.ppg_to_target(ppg.to(cuda_dev), tl.to(cuda_dev)).cpu()
+    ref = PO.ppg_to_target(ppg.double(), tl, "map", w.double(), b.double(), c.double(), 1.0)
+    assert (got - ref).abs().max() < 5e-5
+    with pytest.raises(ValueError):
+        PPGModelWapper(model=_tiny_asr(cuda_dev), device=cuda_dev, output_type="map")
+
+
+def _tiny_asr(dev):
+    from f5e_tts_b200.ppg import ASRModel
+    return ASRModel(80, output_size=256, attention_heads=4, linear_units=256, num_blocks=1)

@@ -16,7 +16,11 @@ PEAK_TF = 1655.8
 PEAK_GBS = 6546.6
 
 
-def timeit(fn, iters=20, warm=3):
+ITERS, WARM = 20, 3
+
+
+def timeit(fn, iters=None, warm=None):
+    iters, warm = ITERS if iters is None else iters, WARM if warm is None else warm
     for _ in range(warm):
         fn()
     torch.cuda.synchronize()
@@ -34,7 +38,11 @@ def main():
     ap.add_argument("--batch", type=int, default=16)
     ap.add_argument("--npad", type=int, default=1030)
     ap.add_argument("--only", default="")
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--warm", type=int, default=3)
     a = ap.parse_args()
+    global ITERS, WARM
+    ITERS, WARM = a.iters, a.warm
     dev = torch.device("cuda:0")
     _lib.require_device()
     S, N = 2 * a.batch, a.npad
@@ -98,6 +106,8 @@ def main():
         o = torch.empty_like(x)
         ms = timeit(lambda: ops.norm_mod(x, mul, add, out=o))
         rec("norm_mod", ms, bytes_=2.0 * M * D * 2)
+        ms = timeit(lambda: ops.row_stats(x))
+        rec("row_stats", ms, bytes_=1.0 * M * (D * 2 + 4 + 128))
         pred = torch.randn(2, M // 2, 100, device=dev)
         y = torch.randn(M // 2, 100, device=dev)
         xc = torch.zeros(M, 712, device=dev, dtype=torch.bfloat16)
