@@ -89,14 +89,14 @@ def main():
         r["sdpa_ms"] = round(timeit(lambda: torch.nn.functional.scaled_dot_product_attention(q, k, v)), 4)
     if a.trace:
         lib = _lib.load()
-        nblk, nslot = 48, 8
-        buf = torch.zeros(296 * 5 * nblk * nslot, device=dev, dtype=torch.int64)
+        nblk, nslot, nrole, ncta = 48, 8, 10, 148  # roles: softmax warps 0-7 (stream A 0-3, B 4-7), MMA issuers 8 / 9
+        buf = torch.zeros(ncta * nrole * nblk * nslot, device=dev, dtype=torch.int64)
         assert lib.f5e_attention_trace(C.c_void_p(buf.data_ptr())) == 0
         ops.attention(qkv, H, klen=klen, n_pad=N, out=o)
         torch.cuda.synchronize()
         lib.f5e_attention_trace(C.c_void_p(0))
         import numpy as np
-        np.save(a.trace, buf.cpu().numpy().reshape(296, 5, nblk, nslot))
+        np.save(a.trace, buf.cpu().numpy().reshape(ncta, nrole, nblk, nslot))
     print(json.dumps(r), flush=True)
 
 
