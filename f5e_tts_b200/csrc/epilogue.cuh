@@ -34,6 +34,21 @@ struct EpiParams {
                                    // c, c + split3, c + 2*split3 (A operand of a following fp32-accurate bf16x3 GEMM)
 };
 
+// Codebook decision fused into the epilogue of the logit GEMM (gemm.cu, VQ instantiation; vq.cu holds the launcher):
+// the weight is laid out with every group padded to 128 rows (pad bias = -1e30), so an epilogue thread (== one row) sees the
+// whole group of its column half and takes the arg-max straight out of TMEM; no logits are written.
+struct VqEpi {
+  long long* targets;   // [M, G]
+  void* xq;             // [M, G * vd] bf16 or fp32
+  const float* vars;    // [G * V (or V when combine_groups), vd]
+  float* sums;          // [G * V] softmax column sums (prob_perplexity), zeroed by the launcher
+  int* hist;            // [G * V] code histogram (code_perplexity), zeroed by the launcher
+  int2* tie_list;       // [M * G] (row, group) pairs whose top-2 margin is below the tolerance: decided by vq_refine_kernel
+  int* tie_count;       // zeroed by the launcher
+  float refine_tol;
+  int G, V, vd, combine_groups, xq_bf16;
+};
+
 // v: 32 accumulator values for (row, col0 .. col0+31).  M/N are the logical output extents.
 __device__ __forceinline__ void epilogue_chunk(float (&v)[32], int row, int col0, int M, int N,
                                                const EpiParams& p) {

@@ -80,11 +80,13 @@ __device__ __forceinline__ uint4* staging_slot(uint8_t* stage, int r, int j) {
   return reinterpret_cast<uint4*>(stage + r * 128 + ((j ^ (r & 7)) << 4));
 }
 
-template <int BN, int STAGES, int CG>
+// VQ = true: the codebook instantiation (BN = 256 = two groups x 128 padded columns, CG = 1): the epilogue takes the
+// per-row, per-group arg-max, the softmax column sums and the code-vector gather instead of storing anything (see VqEpi).
+template <int BN, int STAGES, int CG, bool VQ = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmA2, int M, int N, int K,
-                 EpiParams ep, int accumulate) {
+                 EpiParams ep, int accumulate, VqEpi vq) {
   using S = GemmSmem<BN, STAGES, CG>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -232,6 +234,91 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16) + acc * BN + half * WCOLS;
+      if constexpr (VQ) {
+        // ---- codebook decision (reference model/modules.py:889-901, 940-943): this thread owns row `row`, group `half` ----
+        const int g = half;
+        if (g < vq.G) {  // warp-uniform
+          const float* bias_g = ep.bias + g * WCOLS;  // padded bias: -1e30 beyond the group's V columns
+          auto load32 = [&](int c, float (&v)[32]) {
+            uint32_t raw[32];
+            tmem_ld_32x32(taddr + c * 32, raw);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+              const float4 b = __ldg(reinterpret_cast<const float4*>(bias_g + c * 32 + i));
+              v[i] = __uint_as_float(raw[i]) + b.x;
+              v[i + 1] = __uint_as_float(raw[i + 1]) + b.y;
+              v[i + 2] = __uint_as_float(raw[i + 2]) + b.z;
+              v[i + 3] = __uint_as_float(raw[i + 3]) + b.w;
+            }
+          };
+          float best = -INFINITY, second = -INFINITY;
+          int bi = 0;
+#pragma unroll 1
+          for (int c = 0; c < WCOLS / 32; ++c) {  // first maximum wins ties: strict > while scanning upwards
+            float v[32];
+            load32(c, v);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              if (v[i] > best) { second = best; best = v[i]; bi = c * 32 + i; }
+              else second = fmaxf(second, v[i]);
+            }
+          }
+          float se = 0.f;
+#pragma unroll 1
+          for (int c = 0; c < WCOLS / 32; ++c) {
+            float v[32];
+            load32(c, v);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) se += __expf(v[i] - best);
+          }
+          const float inv = row < M ? 1.0f / se : 0.f;
+          // softmax column sums over this warp's 32 rows: transpose through the warp's staging block, one column per lane
+          float* stg = reinterpret_cast<float*>(stage_base);
+#pragma unroll 1
+          for (int c = 0; c < WCOLS / 32; ++c) {
+            if (c * 32 >= vq.V) break;
+            float v[32];
+            load32(c, v);
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) stg[lane * 32 + ((i + lane) & 31)] = __expf(v[i] - best) * inv;  // skewed: no bank conflicts
+            __syncwarp();
+            float colsum = 0.f;
+#pragma unroll
+            for (int rr = 0; rr < 32; ++rr) colsum += stg[rr * 32 + ((lane + rr) & 31)];
+            if (c * 32 + lane < vq.V) atomicAdd(vq.sums + g * vq.V + c * 32 + lane, colsum);
+          }
+          const bool tie = row < M && vq.V > 1 && best - second <= vq.refine_tol * fmaxf(1.0f, fabsf(best));
+          if (row < M) {
+            if (tie) {  // a tensor-core rounding could flip this one: vq_refine_kernel decides it in sequential fp32
+              const int slot = atomicAdd(vq.tie_count, 1);
+              vq.tie_list[slot] = make_int2(row, g);
+            } else {
+              vq.targets[(size_t)row * vq.G + g] = bi;
+              atomicAdd(vq.hist + g * vq.V + bi, 1);
+            }
+          }
+          // gather of the selected code vectors, one row at a time with the whole warp (coalesced)
+          const int pick = (row < M && !tie) ? bi : -1;
+#pragma unroll 1
+          for (int rr = 0; rr < 32; ++rr) {
+            const int idx = __shfl_sync(0xffffffffu, pick, rr);
+            if (idx < 0) continue;  // warp-uniform
+            const float* src = vq.vars + (size_t)((vq.combine_groups ? 0 : g * vq.V) + idx) * vq.vd;
+            const size_t o = (size_t)(row0 + rr) * vq.G * vq.vd + (size_t)g * vq.vd;
+            if (vq.xq_bf16) {
+              __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(vq.xq) + o;
+              for (int cidx = lane * 2; cidx < vq.vd; cidx += 64)
+                *reinterpret_cast<uint32_t*>(dst + cidx) = pack_bf16x2(__ldg(src + cidx), __ldg(src + cidx + 1));
+            } else {
+              float* dst = reinterpret_cast<float*>(vq.xq) + o;
+              for (int cidx = lane * 2; cidx < vq.vd; cidx += 64)
+                *reinterpret_cast<float2*>(dst + cidx) = __ldg(reinterpret_cast<const float2*>(src + cidx));
+            }
+          }
+        }
+      } else
 #pragma unroll 1
       for (int cc = 0; cc < WCOLS / 64; ++cc) {
         const int col0 = wcol0 + cc * 64;
@@ -419,9 +506,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
 }
 
-template <int BN, int STAGES, int CG>
+template <int BN, int STAGES, int CG, bool VQ = false>
 static int launch_gemm(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
-                       const CUtensorMap& tmA2, int M, int N, int K, const EpiParams& ep, int accumulate) {
+                       const CUtensorMap& tmA2, int M, int N, int K, const EpiParams& ep, int accumulate,
+                       const VqEpi& vq = VqEpi{}) {
   using S = GemmSmem<BN, STAGES, CG>;
   const int tiles = ((M + GEMM_BM * CG - 1) / (GEMM_BM * CG)) * ((N + BN - 1) / BN);
   const int slots = num_sms() / CG;  // CTAs (CG = 1) or CTA pairs (CG = 2) that can be resident
@@ -439,7 +527,7 @@ static int launch_gemm(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMa
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  F5E_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<BN, STAGES, CG>, tmA, tmB, tmC, tmA2, M, N, K, ep, accumulate));
+  F5E_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<BN, STAGES, CG, VQ>, tmA, tmB, tmC, tmA2, M, N, K, ep, accumulate, vq));
   return 0;
 }
 
@@ -450,6 +538,8 @@ int gemm_configure() {
                                       GemmSmem<256, 5, 2>::TOTAL));
   F5E_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<128, 6, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       GemmSmem<128, 6, 1>::TOTAL));
+  F5E_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<256, 4, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      GemmSmem<256, 4, 1>::TOTAL));
 #if GEMM_NARROW_PAIR
   F5E_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<128, GEMM_NARROW_STAGES, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       GemmSmem<128, GEMM_NARROW_STAGES, 2>::TOTAL));
@@ -519,6 +609,25 @@ int gemm_bf16(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloa
   if (pair) return launch_gemm<256, 5, 2>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
   if (wide && !small) return launch_gemm<256, 4, 1>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
   return launch_gemm<128, 6, 1>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
+}
+
+// Logit GEMM of the codebook (A [M, K] bf16x3-split activations, Wp [256, K] = the projection with every group padded to
+// 128 rows, bias_p [256] with -1e30 on the pad columns) with the decision fused into the epilogue: nothing is stored but
+// targets / x_q / histogram / softmax sums / the near-tie list (VqEpi).
+int gemm_vq(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloat16* Wp, int ldw, const float* bias_p, int M, int K,
+            const VqEpi& vq) {
+  { int rc0 = ensure_configured(); if (rc0) return rc0; }
+  F5E_REQUIRE(M > 0 && K > 0 && K % 8 == 0 && vq.G >= 1 && vq.G <= 2 && vq.V >= 1 && vq.V <= 128 && vq.vd % 2 == 0,
+              "gemm_vq: needs 1-2 groups of at most 128 entries (G=%d V=%d)", vq.G, vq.V);
+  CUtensorMap tmA, tmB;
+  int rc = make_tmap_2d(&tmA, A, 2, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, GEMM_BK, GEMM_BM);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tmB, Wp, 2, (uint64_t)K, (uint64_t)256, (uint64_t)ldw * 2, GEMM_BK, 256);
+  if (rc) return rc;
+  EpiParams ep{};
+  ep.bias = bias_p;
+  ep.n_pad = M;
+  return launch_gemm<256, 4, 1, true>(st, tmA, tmB, tmA /* no output map */, tmA, M, 256, K, ep, 0, vq);
 }
 
 }  // namespace f5e

@@ -24,6 +24,11 @@ int make_tmap_3d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t in
 int gemm_bf16(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloat16* W, int ldw, int M,
               int N, int K, const EpiParams& ep);
 
+int gemm_vq(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloat16* Wp, int ldw, const float* bias_p, int M, int K,
+            const VqEpi& vq);
+int vq_refine(cudaStream_t st, const float* x, int ld_x, int dim, const float* W, const float* bias, const VqEpi& vq,
+              float* perplexity, int M);
+
 int norm_mod(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int M, int D, const float* mul,
              const float* add, int mod_stride, int n_pad, float plus_one, float eps, const int* row_info = nullptr);
 // LayerNorm folded into the next GEMM (elementwise.cu): per-row (mean, rstd) of x; per-step rewrite of the weights

@@ -90,6 +90,30 @@ int f5e_vq_quantize(const float* x, int32_t ld_x, int32_t M, int32_t dim, const 
                    refine_tol, reinterpret_cast<long long*>(targets), xq, xq_bf16, prob_sums, hist, n_refined, perplexity);
 }
 
+int f5e_vq_quantize_fused(const float* x, int32_t ld_x, int32_t M, int32_t dim, const void* w_split3_padded,
+                          const float* bias_padded, const float* w_f32, const float* bias, const float* vars, int32_t groups,
+                          int32_t num_vars, int32_t var_dim, int32_t combine_groups, float refine_tol, void* a_split3,
+                          void* tie_list, int64_t* targets, void* xq, int32_t xq_bf16, float* prob_sums, int32_t* hist,
+                          int32_t* n_refined, float* perplexity, void* stream) {
+  F5E_REQUIRE(x && w_split3_padded && bias_padded && w_f32 && vars && a_split3 && tie_list && targets && xq && prob_sums &&
+                  hist && n_refined,
+              "f5e_vq_quantize_fused: null argument");
+  F5E_REQUIRE(dim % 64 == 0 && groups >= 1 && groups <= 2 && num_vars >= 1 && num_vars <= 128,
+              "f5e_vq_quantize_fused: needs dim %% 64 == 0 and 1-2 groups of at most 128 entries (else f5e_vq_quantize)");
+  cudaStream_t st = (cudaStream_t)stream;
+  F5E_TRY(split3(st, x, ld_x, M, dim, reinterpret_cast<__nv_bfloat16*>(a_split3)));
+  F5E_CUDA_CHECK(cudaMemsetAsync(prob_sums, 0, (size_t)groups * num_vars * sizeof(float), st));
+  F5E_CUDA_CHECK(cudaMemsetAsync(hist, 0, (size_t)groups * num_vars * sizeof(int), st));
+  F5E_CUDA_CHECK(cudaMemsetAsync(n_refined, 0, sizeof(int), st));
+  VqEpi vq{};
+  vq.targets = reinterpret_cast<long long*>(targets); vq.xq = xq; vq.vars = vars; vq.sums = prob_sums; vq.hist = hist;
+  vq.tie_list = reinterpret_cast<int2*>(tie_list); vq.tie_count = n_refined; vq.refine_tol = refine_tol;
+  vq.G = groups; vq.V = num_vars; vq.vd = var_dim; vq.combine_groups = combine_groups; vq.xq_bf16 = xq_bf16;
+  F5E_TRY(gemm_vq(st, reinterpret_cast<const __nv_bfloat16*>(a_split3), 3 * dim, reinterpret_cast<const __nv_bfloat16*>(w_split3_padded),
+                  3 * dim, bias_padded, M, 3 * dim, vq));
+  return vq_refine(st, x, ld_x, dim, w_f32, bias, vq, perplexity, M);
+}
+
 int f5e_softmax_split3(const float* logits, int32_t ld, int32_t M, int32_t V, int32_t kpad, void* out_bf16, void* stream) {
   F5E_REQUIRE(logits && out_bf16, "f5e_softmax_split3: null argument");
   return softmax_split3((cudaStream_t)stream, logits, ld, M, V, kpad, reinterpret_cast<__nv_bfloat16*>(out_bf16));

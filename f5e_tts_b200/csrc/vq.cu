@@ -164,6 +164,59 @@ int softmax_split3(cudaStream_t st, const float* logits, int ld, int M, int V, i
   return 0;
 }
 
+// Near-tie (row, group) pairs the fused epilogue of gemm_vq left undecided: the group's logits recomputed with plain
+// sequential fp32 FMAs (the arithmetic a scalar fp32 implementation performs), then arg-max (first maximum), histogram
+// and code-vector gather.  One warp per pair; the pair count is read on the device (no host round trip).
+__global__ void __launch_bounds__(256)
+vq_refine_kernel(const float* __restrict__ x, int ld_x, int dim, const float* __restrict__ W, const float* __restrict__ bias,
+                 VqEpi vq) {
+  const int lane = threadIdx.x & 31;
+  const int n = *vq.tie_count;
+  for (int e = blockIdx.x * 8 + (threadIdx.x >> 5); e < n; e += gridDim.x * 8) {
+    const int2 rg = vq.tie_list[e];
+    const int row = rg.x, g = rg.y;
+    const float* xr = x + (size_t)row * ld_x;
+    float best = -INFINITY;
+    int bi = 0x7fffffff;
+    for (int j = lane; j < vq.V; j += 32) {
+      const float* wr = W + (size_t)(g * vq.V + j) * dim;
+      float acc = 0.f;
+      for (int k = 0; k < dim; ++k) acc = fmaf(xr[k], wr[k], acc);
+      acc += bias ? bias[g * vq.V + j] : 0.f;
+      if (acc > best) { best = acc; bi = j; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) argmax_pair(best, bi, __shfl_xor_sync(0xffffffffu, best, o), __shfl_xor_sync(0xffffffffu, bi, o));
+    if (lane == 0) {
+      vq.targets[(size_t)row * vq.G + g] = bi;
+      atomicAdd(vq.hist + g * vq.V + bi, 1);
+    }
+    const float* src = vq.vars + (size_t)((vq.combine_groups ? 0 : g * vq.V) + bi) * vq.vd;
+    const size_t o = (size_t)row * vq.G * vq.vd + (size_t)g * vq.vd;
+    if (vq.xq_bf16) {
+      __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(vq.xq) + o;
+      for (int c = lane * 2; c < vq.vd; c += 64) *reinterpret_cast<uint32_t*>(dst + c) = pack_bf16x2(src[c], src[c + 1]);
+    } else {
+      float* dst = reinterpret_cast<float*>(vq.xq) + o;
+      for (int c = lane * 2; c < vq.vd; c += 64) *reinterpret_cast<float2*>(dst + c) = *reinterpret_cast<const float2*>(src + c);
+    }
+  }
+}
+
+int vq_refine(cudaStream_t st, const float* x, int ld_x, int dim, const float* W, const float* bias, const VqEpi& vq,
+              float* perplexity, int M) {
+  {
+    LaunchScope ls(st, PROF_VQ, M, vq.G, -3);
+    vq_refine_kernel<<<64, 256, 0, st>>>(x, ld_x, dim, W, bias, vq);
+  }
+  if (perplexity) {
+    LaunchScope ls(st, PROF_VQ, M, vq.G, -1);
+    vq_perplexity_kernel<<<1, 256, 0, st>>>(vq.hist, vq.sums, M, vq.G, vq.V, perplexity);
+  }
+  F5E_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
 int vq_select(cudaStream_t st, const float* logits, int ld_logits, const float* x, int ld_x, int dim, const float* W,
               const float* bias, const float* vars, int M, int G, int V, int vd, int combine_groups, float refine_tol,
               long long* targets, void* xq, int xq_bf16, float* sums, int* hist, int* refined, float* perplexity) {

@@ -45,6 +45,7 @@ class GumbelVectorQuantizer(nn.Module):
         self.curr_temp = self.max_temp
         self.codebook_indices = None
         self.refine_tol = 1e-4      # top-2 margin below which an index is re-decided in sequential fp32
+        self.fused_decision = True  # arg-max / gather in the logit GEMM's epilogue (1-2 groups of <= 128 entries); False: unfused
         self.last_refined = None    # device int32 scalar: number of such re-decisions in the last call
         self._plan = None
 
@@ -96,7 +97,17 @@ class GumbelVectorQuantizer(nn.Module):
         if self._plan is None:
             dev = self.vars.device
             w = self.weight_proj.weight.detach().float().contiguous()
-            self._plan = dict(w3=split3_weight(w), w=w, b=self.weight_proj.bias.detach().float().contiguous(),
+            b = self.weight_proj.bias.detach().float().contiguous()
+            G, V = self.groups, self.num_vars
+            fused = None
+            if G <= 2 and V <= 128:  # fused decision: every group padded to 128 logit columns (f5e_vq_quantize_fused)
+                wp = torch.zeros(256, w.shape[1], device=w.device)
+                bp = torch.full((256,), -1e30, device=w.device)
+                for g in range(G):
+                    wp[128 * g: 128 * g + V] = w[g * V: (g + 1) * V]
+                    bp[128 * g: 128 * g + V] = b[g * V: (g + 1) * V]
+                fused = (split3_weight(wp), bp.contiguous())
+            self._plan = dict(w3=split3_weight(w), w=w, b=b, fused=fused,
                               vars=self.vars.detach().float().reshape(-1, self.vars.shape[-1]).contiguous(), dev=dev,
                               versions=self._param_versions())
         return self._plan
@@ -120,7 +131,6 @@ class GumbelVectorQuantizer(nn.Module):
         dev = x.device
         ldl = (G * V + 3) // 4 * 4
         a3 = torch.empty(M, 3 * fsz, device=dev, dtype=torch.bfloat16)
-        logits = torch.empty(M, ldl, device=dev, dtype=torch.float32)
         targets = torch.empty(bsz, tsz, G, device=dev, dtype=torch.int64)
         out_bf16 = in_dtype == torch.bfloat16
         xq = torch.empty(bsz, tsz, G * vd, device=dev, dtype=torch.bfloat16 if out_bf16 else torch.float32)
@@ -128,10 +138,19 @@ class GumbelVectorQuantizer(nn.Module):
         hist = torch.empty(G * V, device=dev, dtype=torch.int32)
         refined = torch.empty(1, device=dev, dtype=torch.int32)
         ppl = torch.empty(2, device=dev, dtype=torch.float32)
-        check(_lib.load().f5e_vq_quantize(ptr(xf), fsz, M, fsz, ptr(P["w3"]), ptr(P["w"]), ptr(P["b"]), ptr(P["vars"]), G, V, vd,
-                                          int(self.combine_groups), C.c_float(self.refine_tol), ptr(a3), ptr(logits), ldl,
-                                          ptr(targets), ptr(xq), int(out_bf16), ptr(sums), ptr(hist), ptr(refined), ptr(ppl),
-                                          stream_ptr()), "f5e_vq_quantize")
+        if P["fused"] is not None and self.fused_decision:
+            ties = torch.empty(M * G, 2, device=dev, dtype=torch.int32)
+            check(_lib.load().f5e_vq_quantize_fused(ptr(xf), fsz, M, fsz, ptr(P["fused"][0]), ptr(P["fused"][1]), ptr(P["w"]),
+                                                    ptr(P["b"]), ptr(P["vars"]), G, V, vd, int(self.combine_groups),
+                                                    C.c_float(self.refine_tol), ptr(a3), ptr(ties), ptr(targets), ptr(xq),
+                                                    int(out_bf16), ptr(sums), ptr(hist), ptr(refined), ptr(ppl), stream_ptr()),
+                  "f5e_vq_quantize_fused")
+        else:
+            logits = torch.empty(M, ldl, device=dev, dtype=torch.float32)
+            check(_lib.load().f5e_vq_quantize(ptr(xf), fsz, M, fsz, ptr(P["w3"]), ptr(P["w"]), ptr(P["b"]), ptr(P["vars"]), G, V, vd,
+                                              int(self.combine_groups), C.c_float(self.refine_tol), ptr(a3), ptr(logits), ldl,
+                                              ptr(targets), ptr(xq), int(out_bf16), ptr(sums), ptr(hist), ptr(refined), ptr(ppl),
+                                              stream_ptr()), "f5e_vq_quantize")
         self.last_refined = refined
         if not out_bf16 and in_dtype != torch.float32:
             xq = xq.to(in_dtype)

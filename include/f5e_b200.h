@@ -410,6 +410,20 @@ int f5e_vq_quantize(const float* x, int32_t ld_x, int32_t M, int32_t dim, const 
                     float* perplexity, void* stream);
 
 /* fp32 [M, K] -> bf16 [M, 3K] = [hi | hi | lo]: the A operand of a bf16x3 GEMM (test hook / building block). */
+/* The same quantize call with the decision FUSED into the epilogue of the logit GEMM (north_star (3): "distance GEMM fused
+ * with argmin"): for 1-2 groups of at most 128 entries.  w_split3_padded: bf16 [256, 3*dim], the 3-term split of
+ * weight_proj with every group padded to 128 rows (group g at rows [128 g, 128 g + num_vars), zeros beyond);
+ * bias_padded: fp32 [256], the bias there and -1e30 on the pad rows.  An epilogue thread owns one row and one group: it
+ * takes the arg-max (first maximum) straight out of TMEM, adds the row's softmax to the column sums, and the warp gathers
+ * the code vectors - NO logits are written.  Rows whose top-2 margin is within refine_tol are appended to tie_list
+ * (int32 pairs [M * groups, 2], scratch) and decided by a second small kernel in sequential fp32, exactly like
+ * f5e_vq_quantize; *n_refined (device) is their count.  Indices are bit-identical to f5e_vq_quantize's. */
+int f5e_vq_quantize_fused(const float* x, int32_t ld_x, int32_t M, int32_t dim, const void* w_split3_padded,
+                          const float* bias_padded, const float* w_f32, const float* bias, const float* vars, int32_t groups,
+                          int32_t num_vars, int32_t var_dim, int32_t combine_groups, float refine_tol, void* a_split3,
+                          void* tie_list, int64_t* targets, void* xq, int32_t xq_bf16, float* prob_sums, int32_t* hist,
+                          int32_t* n_refined, float* perplexity, void* stream);
+
 int f5e_split3(const float* x, int64_t ld, int32_t M, int32_t K, void* out_bf16, void* stream);
 
 /* Row softmax over the first V columns of fp32 logits [M, ld] -> bf16 [M, 3 * kpad] as the split [hi | hi | lo] (columns

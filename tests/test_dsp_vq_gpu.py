@@ -168,3 +168,35 @@ def test_vq_near_ties_are_redecided_in_fp32(cuda_dev):
     top2 = logits.view(4, 64, 2, 100).topk(2, -1).values
     margin = (top2[..., 0] - top2[..., 1]) / top2[..., 0].abs().clamp_min(1)
     assert bool((margin[mism] < 1e-5).all())
+
+
+@pytest.mark.parametrize("B,T,groups,num_vars", [(32, 940, 2, 100), (3, 77, 1, 128), (2, 130, 2, 7)])
+def test_vq_fused_decision_equals_unfused(cuda_dev, B, T, groups, num_vars):
+    """north_star (3): arg-max + gather fused into the logit GEMM's epilogue (f5e_vq_quantize_fused, no logits round trip)
+    gives the SAME indices and code vectors as the unfused path (GEMM -> fp32 logits -> vq_select), bit for bit, incl. rows
+    sent through the sequential-fp32 re-decision; the perplexities agree to fp32 summation order."""
+    q, sd = _quantizer(cuda_dev, 512, num_vars, groups, 21)
+    with torch.no_grad():
+        if num_vars > 5:
+            q.weight_proj.weight[4] = q.weight_proj.weight[1]      # exact duplicate rows: ties, first index must win
+    q._plan = None
+    g = torch.Generator().manual_seed(B * T)
+    x = torch.randn(B, T, 512, generator=g).to(cuda_dev)
+    x[0, :8] = q.weight_proj.weight[1].detach() * 0.05
+    assert q.fused_decision and q._get_plan()["fused"] is not None
+    r1 = q(x, produce_targets=True)
+    n1 = int(q.last_refined)
+    q.fused_decision = False
+    r0 = q(x, produce_targets=True)
+    n0 = int(q.last_refined)
+    assert torch.equal(r1["targets"], r0["targets"])
+    assert torch.equal(r1["x"], r0["x"])
+    assert n1 == n0 and (num_vars <= 5 or n1 >= 8)
+    for k in ("code_perplexity", "prob_perplexity"):
+        assert abs(float(r1[k]) - float(r0[k])) <= 1e-4 * abs(float(r0[k])), k
+    # bf16 output path (the DiT feeds bf16 embeddings)
+    q.fused_decision = True
+    rb = q(x.bfloat16(), produce_targets=True)
+    q.fused_decision = False
+    rb0 = q(x.bfloat16(), produce_targets=True)
+    assert rb["x"].dtype == torch.bfloat16 and torch.equal(rb["x"], rb0["x"]) and torch.equal(rb["targets"], rb0["targets"])

@@ -89,7 +89,7 @@ def main():
         r["sdpa_ms"] = round(timeit(lambda: torch.nn.functional.scaled_dot_product_attention(q, k, v)), 4)
     if a.trace:
         lib = _lib.load()
-        nblk, nslot, nrole, ncta = 48, 8, 10, 148  # roles: softmax warps 0-7 (stream A 0-3, B 4-7), MMA issuers 8 / 9
+        nblk, nslot, nrole, ncta = 48, 8, 5, 296  # roles: softmax quarters 0-3, MMA issuer 4
         buf = torch.zeros(ncta * nrole * nblk * nslot, device=dev, dtype=torch.int64)
         assert lib.f5e_attention_trace(C.c_void_p(buf.data_ptr())) == 0
         ops.attention(qkv, H, klen=klen, n_pad=N, out=o)

@@ -83,7 +83,29 @@ def main():
         for i in range(3):
             acc[i] += ev[i].elapsed_time(ev[i + 1]) / a.iters
     tot = sum(acc)
-    print(json.dumps(dict(metric="voice conversion, generated audio seconds per second (PPG extraction + sample_vc + Vocos)",
+    # the codebook quantize call (GumbelVectorQuantizer.forward, modules.py:877-950) on PPG embeddings of this batch's shape:
+    # decision fused into the logit GEMM's epilogue against the unfused path (fp32 logits round trip + vq_select)
+    q = dit.quantizer.float().eval()
+    emb = torch.randn(B, int(gen_frames.max()) + int(ref_len.max()), 512, device=dev)
+    Mq = emb.shape[0] * emb.shape[1]
+    vq_bytes = Mq * (512 * 4 + 512 * 4 + 2 * 8)  # algorithmic: x read, x_q written, two int64 indices per row
+    vq_ms = {}
+    for name, fused in (("fused", True), ("unfused", False)):
+        q.fused_decision = fused
+        for _ in range(3):
+            q.forward_idx(emb)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            q.forward_idx(emb)
+        e1.record()
+        torch.cuda.synchronize()
+        vq_ms[name] = e0.elapsed_time(e1) / 10
+    q.fused_decision = True
+    vq = dict(rows=Mq, groups=2, num_vars=100, ms_fused=vq_ms["fused"], ms_unfused=vq_ms["unfused"], algorithmic_bytes=vq_bytes,
+              gbs_fused=vq_bytes / vq_ms["fused"] / 1e6, frac_hbm_fused=vq_bytes / vq_ms["fused"] / 1e6 / 6558.1,
+              note="includes the host wrapper (allocation of outputs, split3 of the fp32 input, memsets); peak = measured 6558.1 GB/s")
+    print(json.dumps(dict(vq=vq, metric="voice conversion, generated audio seconds per second (PPG extraction + sample_vc + Vocos)",
                           unit="audio-s/s", value=audio_s / (tot / 1e3), ms_per_batch=tot, batch=B, nfe=a.nfe, audio_seconds=audio_s,
                           ms=dict(ppg_extraction=acc[0], sample_vc=acc[1], vocos=acc[2]), ms_per_nfe_step=acc[1] / a.nfe,
                           model="F5E Small PPG + codebook (dim 768, depth 18, 12 heads), three-way guidance (3 x batch)",
