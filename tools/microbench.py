@@ -79,6 +79,10 @@ def main():
                 invc = inv.contiguous()
                 ms = timeit(lambda: ops.gemm(x, w, bias=b, out=o, n_pad=N, rope=invc, rope_heads=16, rope_inner=1024))
                 rec("gemm_qkv_rope_compute", ms, flops=2.0 * M * n * k, M=M, N=n, K=k)
+            if res is not None:  # the residual READ in the epilogue + plain store, instead of the in-place TMA reduce-add
+                r2 = torch.randn(M, n, device=dev).bfloat16()
+                ms = timeit(lambda: ops.gemm(x, w, bias=b, act=act, out=o, residual=r2, gate=gate, n_pad=N))
+                rec(f"gemm_{tag}_residual_read", ms, flops=2.0 * M * n * k, M=M, N=n, K=k)
             if tag in ("qkv", "ff1"):
                 ms = timeit(lambda: ops.gemm(x, w, out=o, n_pad=N))
                 rec(f"gemm_{tag}_plain", ms, flops=2.0 * M * n * k, M=M, N=n, K=k)
@@ -106,8 +110,13 @@ def main():
         o = torch.empty_like(x)
         ms = timeit(lambda: ops.norm_mod(x, mul, add, out=o))
         rec("norm_mod", ms, bytes_=2.0 * M * D * 2)
-        ms = timeit(lambda: ops.row_stats(x))
-        rec("row_stats", ms, bytes_=1.0 * M * (D * 2 + 4 + 128))
+        import ctypes as C
+        lib = _lib.load()
+        rstd = torch.empty(M, device=dev)
+        a2 = torch.zeros(M, 64, device=dev, dtype=torch.bfloat16)
+        st = _lib.stream_ptr()
+        ms = timeit(lambda: lib.f5e_row_stats(_lib.ptr(x), _lib.ptr(rstd), _lib.ptr(a2), M, D, C.c_float(1e-6), st))
+        rec("row_stats", ms, bytes_=1.0 * M * (D * 2 + 4 + 8))
         pred = torch.randn(2, M // 2, 100, device=dev)
         y = torch.randn(M // 2, 100, device=dev)
         xc = torch.zeros(M, 712, device=dev, dtype=torch.bfloat16)
