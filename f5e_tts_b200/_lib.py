@@ -28,6 +28,7 @@ class Epilogue(C.Structure):
         ("rope_inner", C.c_int32), ("rope_heads", C.c_int32),
         ("residual_f32", C.c_int32), ("out_split3", C.c_int32), ("row_info", C.c_void_p),
         ("rope_inv_freq", C.c_void_p), ("ln_rstd", C.c_void_p), ("ln_a2", C.c_void_p),
+        ("stats_out", C.c_void_p), ("stats_slots", C.c_int32),
     ]
 
 

@@ -15,6 +15,7 @@ static EpiParams to_epi(const f5e_epilogue* e, int M) {
   p.res_f32 = e->residual_f32; p.split3 = e->out_split3; p.row_info = e->row_info;
   p.rope_inv_freq = e->rope_inv_freq;
   p.ln_rstd = e->ln_rstd; p.ln_a2 = reinterpret_cast<const __nv_bfloat16*>(e->ln_a2);
+  p.stats_out = reinterpret_cast<float2*>(e->stats_out); p.stats_slots = e->stats_slots;
   return p;
 }
 
@@ -55,6 +56,11 @@ int f5e_norm_mod(const void* x, void* out, int32_t M, int32_t D, const float* mu
 int f5e_row_stats(const void* x, float* rstd, void* a2, int32_t M, int32_t D, float eps, void* stream) {
   F5E_REQUIRE(x && rstd && a2, "f5e_row_stats: null argument");
   return row_stats((cudaStream_t)stream, (const __nv_bfloat16*)x, rstd, (__nv_bfloat16*)a2, M, D, eps);
+}
+
+int f5e_ln_finalize(const float* stats, int32_t slots, int32_t M, int32_t D, float eps, float* rstd, void* a2, void* stream) {
+  F5E_REQUIRE(stats && rstd && a2, "f5e_ln_finalize: null argument");
+  return ln_finalize((cudaStream_t)stream, reinterpret_cast<const float2*>(stats), slots, M, D, eps, rstd, (__nv_bfloat16*)a2);
 }
 
 int f5e_fold_ln_weights(const f5e_fold_job* jobs_dev, int32_t n_jobs, int32_t total_rows, int32_t D, const float* mod,

@@ -78,13 +78,29 @@ static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_d
     row_start = pack->row_start;
     row_len = nullptr;  // there are no padded rows left to zero
   }
+  // Folded path: the out-projection / FF2 GEMMs take the LayerNorm statistics of the rows they produce in their epilogue
+  // (EpiParams::stats_out) whenever they run on the CTA-pair kernel; row_stats then reads the residual stream only once per
+  // evaluation (before the first block) instead of twice per block.
+  // Only FF2 by default: its K = 2 * dim main loop hides the heavier epilogue completely; the out-projection (K = dim) is
+  // epilogue-bound already and slows down by more than the row_stats pass it would save (measured: +12 us per launch).
+#ifndef DIT_FUSE_STATS_OUT
+#define DIT_FUSE_STATS_OUT 0
+#endif
+  const int slots = D / 128;
+  const bool fuse_stats = folded && b->stats_part && D % 256 == 0 && gemm_can_fuse_stats(rows, D);
+  const bool fuse_stats_out = fuse_stats && DIT_FUSE_STATS_OUT;
+  auto block_stats = [&](bool from_gemm) -> int {
+    if (from_gemm)
+      return ln_finalize(st, reinterpret_cast<const float2*>(b->stats_part), slots, rows, D, 1e-6f, b->stats, bfm(b->stats_a));
+    return row_stats(st, bf(xs), b->stats, bfm(b->stats_a), rows, D, 1e-6f);
+  };
   for (int l = 0; l < m->depth; ++l) {
     const f5e_dit_layer& L = m->layers[l];
     const float* ml = mod + (size_t)l * 6 * D;
     const float *shift_msa = ml, *scale_msa = ml + D, *gate_msa = ml + 2 * D;
     const float *shift_mlp = ml + 3 * D, *scale_mlp = ml + 4 * D, *gate_mlp = ml + 5 * D;
     // adaLN-modulated LayerNorm (modules.py:310-315): materialised (norm_mod) or folded into the GEMM (row_stats + W')
-    if (folded) F5E_TRY(row_stats(st, bf(xs), b->stats, bfm(b->stats_a), rows, D, 1e-6f));
+    if (folded) F5E_TRY(block_stats(fuse_stats && l > 0));
     else F5E_TRY(norm_mod(st, bf(xs), bfm(b->xn), rows, D, scale_msa, shift_msa, mod_stride, n_pad, 1.0f, 1e-6f, row_info));
     {  // fused q/k/v projection + RoPE (modules.py:442-480)
       EpiParams ep{};
@@ -104,9 +120,10 @@ static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_d
       EpiParams ep{};
       ep.out = xs; ep.ldo = D; ep.bias = L.b_out; ep.n_pad = n_pad; ep.row_info = row_info; ep.row_len = row_len;
       ep.gate = gate_msa; ep.gate_stride = mod_stride; ep.residual = bf(xs); ep.ldr = D;
+      if (fuse_stats_out) { ep.stats_out = reinterpret_cast<float2*>(b->stats_part); ep.stats_slots = slots; }
       F5E_TRY(gemm_bf16(st, bf(b->attn), inner, bf(L.w_out), inner, rows, D, inner, ep));
     }
-    if (folded) F5E_TRY(row_stats(st, bf(xs), b->stats, bfm(b->stats_a), rows, D, 1e-6f));
+    if (folded) F5E_TRY(block_stats(fuse_stats_out));
     else F5E_TRY(norm_mod(st, bf(xs), bfm(b->xn), rows, D, scale_mlp, shift_mlp, mod_stride, n_pad, 1.0f, 1e-6f, row_info));
     {  // FeedForward (modules.py:342-353) with GELU(tanh) fused, then gate_mlp * ff + residual (:638)
       EpiParams ep{};
@@ -120,6 +137,7 @@ static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_d
       EpiParams e2{};
       e2.out = xs; e2.ldo = D; e2.bias = L.b_ff2; e2.n_pad = n_pad; e2.row_info = row_info;
       e2.gate = gate_mlp; e2.gate_stride = mod_stride; e2.residual = bf(xs); e2.ldr = D;
+      if (fuse_stats && l + 1 < m->depth) { e2.stats_out = reinterpret_cast<float2*>(b->stats_part); e2.stats_slots = slots; }
       F5E_TRY(gemm_bf16(st, bf(b->ff), m->ff_dim, bf(L.w_ff2), m->ff_dim, rows, D, m->ff_dim, e2));
     }
   }

@@ -183,6 +183,40 @@ int row_stats(cudaStream_t st, const __nv_bfloat16* x, float* rstd, __nv_bfloat1
   return 0;
 }
 
+// Partial statistics written by the producing GEMM's epilogue (EpiParams::stats_out: (mean, M2) of 128 columns per slot) ->
+// what the folded GEMM consumes: rstd and the bf16 split of -mean.  Chan's parallel update over equal-sized groups, in a
+// fixed order (deterministic).  One thread per row; 8 slots for dim 1024.
+__global__ void __launch_bounds__(256)
+ln_finalize_kernel(const float2* __restrict__ stats, int slots, int M, float inv_d, float eps, float* __restrict__ rstd_out,
+                   __nv_bfloat16* __restrict__ a2) {
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= M) return;
+  const float2* p = stats + (size_t)row * slots;
+  float mean = 0.f;
+  for (int i = 0; i < slots; ++i) mean += p[i].x;
+  mean /= (float)slots;
+  float m2 = 0.f;
+  for (int i = 0; i < slots; ++i) {
+    const float d = p[i].x - mean;
+    m2 += p[i].y + 128.0f * d * d;
+  }
+  rstd_out[row] = rsqrtf(m2 * inv_d + eps);
+  const __nv_bfloat16 hi = __float2bfloat16(-mean);
+  const __nv_bfloat16 lo = __float2bfloat16(-mean - __bfloat162float(hi));
+  uint2 u;
+  u.x = (uint32_t)__bfloat16_as_ushort(hi) | ((uint32_t)__bfloat16_as_ushort(lo) << 16);
+  u.y = (uint32_t)__bfloat16_as_ushort(hi);
+  *reinterpret_cast<uint2*>(a2 + (size_t)row * 64) = u;
+}
+
+int ln_finalize(cudaStream_t st, const float2* stats, int slots, int M, int D, float eps, float* rstd, __nv_bfloat16* a2) {
+  F5E_REQUIRE(stats && rstd && a2 && M > 0 && slots > 0 && slots * 128 == D, "ln_finalize: bad arguments (slots=%d D=%d)", slots, D);
+  LaunchScope ls(st, PROF_NORM, M, D, 3);
+  ln_finalize_kernel<<<(M + 255) / 256, 256, 0, st>>>(stats, slots, M, 1.0f / (float)D, eps, rstd, a2);
+  F5E_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
 // one warp per weight row; `jobs` (device) lists the matrices of every layer: rows [row0, row0 + N) of the launch
 __global__ void __launch_bounds__(256)
 fold_ln_weights_kernel(const FoldJob* __restrict__ jobs, int n_jobs, int total_rows, int D, const float* __restrict__ mod) {

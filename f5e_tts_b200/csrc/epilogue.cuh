@@ -30,6 +30,10 @@ struct EpiParams {
   const int* row_info;             // [M] or null: (sample << 16 | frame) per row, for PACKED rows (valid frames of all
                                    // samples back to back, no padding); replaces the row / n_pad arithmetic
   int res_f32;                     // residual is fp32 [M, ldr] instead of bf16
+  float2* stats_out;               // [M, stats_slots] or null (gemm_bf16, CTA-pair kernel, x += gate * branch only): the residual is
+  int stats_slots;                 // READ (TMA-staged) instead of reduce-added, and every epilogue thread writes the (mean, M2)
+                                   // of its 128 NEW output columns: slot = column / 128.  ln_finalize turns them into rstd / a2
+                                   // of the next folded LayerNorm, so row_stats never re-reads the residual stream.
   int split3;                      // > 0: bf16 output written as the 3-term split [hi | hi | lo] at columns
                                    // c, c + split3, c + 2*split3 (A operand of a following fp32-accurate bf16x3 GEMM)
 };

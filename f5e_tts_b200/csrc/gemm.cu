@@ -82,7 +82,9 @@ __device__ __forceinline__ uint4* staging_slot(uint8_t* stage, int r, int j) {
 
 // VQ = true: the codebook instantiation (BN = 256 = two groups x 128 padded columns, CG = 1): the epilogue takes the
 // per-row, per-group arg-max, the softmax column sums and the code-vector gather instead of storing anything (see VqEpi).
-template <int BN, int STAGES, int CG, bool VQ = false>
+// STATS = true (CG = 2 only): x += gate * (acc + bias) with the LayerNorm statistics of the new rows taken on the way
+// (EpiParams::stats_out).
+template <int BN, int STAGES, int CG, bool VQ = false, bool STATS = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmA2, int M, int N, int K,
@@ -95,6 +97,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* ld_bar = reinterpret_cast<uint64_t*>(smem + S::BAR_OFFSET + 128);  // STATS: 2 per epilogue warp (residual tiles)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -120,6 +123,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_init(&tfull_bar[i], 1);
       mbar_init(&tempty_bar[i], GEMM_EPI_WARPS * CG);  // the leader's barrier collects the epilogue warps of both CTAs
     }
+    if (STATS)
+      for (int i = 0; i < 2 * GEMM_EPI_WARPS; ++i) mbar_init(&ld_bar[i], 1);
     mbar_fence_init();
   }
   if (warp == 1) {
@@ -207,7 +212,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       staging_acquire<S::NBUF>(lane);
     };
     int acc = 0;
-    uint32_t acc_phase = 0;
+    uint32_t acc_phase = 0, ld_phase = 0;
     for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
       const int m_blk = tile / n_blocks, n_blk = tile - m_blk * n_blocks;
       const int row0 = m_blk * TILE_M + rank * GEMM_BM + quarter * 32;
@@ -231,10 +236,88 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const float frame_f = (float)frame;
       const float* gate = ep.gate ? ep.gate + (ep.gate_stride ? (size_t)sample * ep.gate_stride : 0) : nullptr;
 
+      if constexpr (STATS) {
+        // The residual tiles of this warp's 32 rows x 128 columns travel (TMA, same map and swizzle as the store) while the
+        // main loop of the tile still runs.  Both staging blocks must be free: every earlier bulk store has read them.
+        __syncwarp();
+        if (elect_one()) {
+          tma_store_wait_read<0>();
+          uint64_t* lb = &ld_bar[(warp - 2) * 2];
+#pragma unroll
+          for (int cc = 0; cc < 2; ++cc) {
+            mbar_expect_tx(&lb[cc], GEMM_STAGING_BYTES);
+            tma_load_2d(stage_base + cc * GEMM_STAGING_BYTES, &tmC, &lb[cc], wcol0 + cc * 64, row0);
+          }
+        }
+      }
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16) + acc * BN + half * WCOLS;
-      if constexpr (VQ) {
+      if constexpr (STATS) {
+        static_assert(!STATS || (CG == 2 && BN == 256), "the statistics epilogue needs two staging blocks per warp");
+        float cmean[2], cm2[2];
+#pragma unroll 1
+        for (int cc = 0; cc < 2; ++cc) {
+          const int col0 = wcol0 + cc * 64;
+          float v[64];
+          {
+            uint32_t r0[32], r1[32];
+            tmem_ld_32x32(taddr + cc * 64, r0);
+            tmem_ld_32x32(taddr + cc * 64 + 32, r1);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) { v[i] = __uint_as_float(r0[i]); v[32 + i] = __uint_as_float(r1[i]); }
+          }
+#pragma unroll
+          for (int i = 0; i < 64; i += 4) {
+            float4 b = ep.bias ? __ldg(reinterpret_cast<const float4*>(ep.bias + col0 + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float4 gt = gate ? __ldg(reinterpret_cast<const float4*>(gate + col0 + i)) : make_float4(1.f, 1.f, 1.f, 1.f);
+            v[i] = row_masked ? 0.f : (v[i] + b.x) * gt.x;
+            v[i + 1] = row_masked ? 0.f : (v[i + 1] + b.y) * gt.y;
+            v[i + 2] = row_masked ? 0.f : (v[i + 2] + b.z) * gt.z;
+            v[i + 3] = row_masked ? 0.f : (v[i + 3] + b.w) * gt.w;
+          }
+          uint8_t* buf = stage_base + cc * GEMM_STAGING_BYTES;
+          mbar_wait(&ld_bar[(warp - 2) * 2 + cc], ld_phase);
+          // new row = bf16(old + branch); the statistics are those of the ROUNDED values, taken in the same pass as shifted
+          // sums (shift = the chunk's first value: sum d, sum d^2 with d = y - shift lose nothing to cancellation)
+          float shift = 0.f, s1 = 0.f, s2 = 0.f;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            uint4* slot = staging_slot(buf, lane, j);
+            const uint4 r = *slot;
+            const float2 a0 = unpack_bf16x2(r.x), a1 = unpack_bf16x2(r.y), a2 = unpack_bf16x2(r.z), a3 = unpack_bf16x2(r.w);
+            uint4 o;
+            o.x = pack_bf16x2(a0.x + v[8 * j], a0.y + v[8 * j + 1]);
+            o.y = pack_bf16x2(a1.x + v[8 * j + 2], a1.y + v[8 * j + 3]);
+            o.z = pack_bf16x2(a2.x + v[8 * j + 4], a2.y + v[8 * j + 5]);
+            o.w = pack_bf16x2(a3.x + v[8 * j + 6], a3.y + v[8 * j + 7]);
+            *slot = o;
+            const float2 y0 = unpack_bf16x2(o.x), y1 = unpack_bf16x2(o.y), y2 = unpack_bf16x2(o.z), y3 = unpack_bf16x2(o.w);
+            if (j == 0) shift = y0.x;
+            const float d[8] = {y0.x - shift, y0.y - shift, y1.x - shift, y1.y - shift, y2.x - shift, y2.y - shift, y3.x - shift, y3.y - shift};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              s1 += d[i];
+              s2 = fmaf(d[i], d[i], s2);
+            }
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (elect_one()) {
+            tma_store_2d(&tmC, buf, col0, row0);
+            tma_store_commit();
+          }
+          cmean[cc] = shift + s1 * (1.0f / 64.0f);
+          cm2[cc] = fmaxf(s2 - s1 * s1 * (1.0f / 64.0f), 0.f);
+        }
+        ld_phase ^= 1;
+        if (row < M) {  // two equal halves: Chan's update with n0 = n1 = 64
+          const float d = cmean[1] - cmean[0];
+          ep.stats_out[(size_t)row * ep.stats_slots + (wcol0 >> 7)] =
+              make_float2(0.5f * (cmean[0] + cmean[1]), cm2[0] + cm2[1] + 32.0f * d * d);
+        }
+      } else if constexpr (VQ) {
         // ---- codebook decision (reference model/modules.py:889-901, 940-943): this thread owns row `row`, group `half` ----
         const int g = half;
         if (g < vq.G) {  // warp-uniform
@@ -506,7 +589,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
 }
 
-template <int BN, int STAGES, int CG, bool VQ = false>
+template <int BN, int STAGES, int CG, bool VQ = false, bool STATS = false>
 static int launch_gemm(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
                        const CUtensorMap& tmA2, int M, int N, int K, const EpiParams& ep, int accumulate,
                        const VqEpi& vq = VqEpi{}) {
@@ -527,8 +610,14 @@ static int launch_gemm(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMa
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  F5E_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<BN, STAGES, CG, VQ>, tmA, tmB, tmC, tmA2, M, N, K, ep, accumulate, vq));
+  F5E_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<BN, STAGES, CG, VQ, STATS>, tmA, tmB, tmC, tmA2, M, N, K, ep, accumulate, vq));
   return 0;
+}
+
+// True when gemm_bf16 runs this shape on the CTA-pair kernel, the only one whose epilogue can take the LayerNorm statistics
+// (two staging blocks per warp for the TMA-staged residual tiles).
+bool gemm_can_fuse_stats(int M, int N) {
+  return GEMM_PAIR && N > 128 && N % 256 == 0 && !GEMM_NARROW_PAIR && ((M + 255) / 256) * (N / 256) >= num_sms() / 2;
 }
 
 int gemm_configure() {
@@ -540,6 +629,8 @@ int gemm_configure() {
                                       GemmSmem<128, 6, 1>::TOTAL));
   F5E_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<256, 4, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       GemmSmem<256, 4, 1>::TOTAL));
+  F5E_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<256, 5, 2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      GemmSmem<256, 5, 2>::TOTAL));
 #if GEMM_NARROW_PAIR
   F5E_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<128, GEMM_NARROW_STAGES, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       GemmSmem<128, GEMM_NARROW_STAGES, 2>::TOTAL));
@@ -573,6 +664,12 @@ int gemm_bf16(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloa
   }
   // CTA pairs when there are enough 256-row tiles to fill the 74 pairs; each CTA then loads a 128-row half of the W tile
   const bool pair = wide && GEMM_PAIR && ((M + 255) / 256) * ((N + 255) / 256) >= num_sms() / 2;
+  if (ep.stats_out) {
+    F5E_REQUIRE(gemm_can_fuse_stats(M, N) && alias && !ep.out_f32 && ep.act == ACT_NONE && !ep.rope_inv_freq && !ep.ln_rstd &&
+                    ep.stats_slots == N / 128,
+                "gemm_bf16: stats_out needs the CTA-pair kernel (gemm_can_fuse_stats), x += gate * branch in place, bf16, no "
+                "activation / RoPE / folded LayerNorm, stats_slots == N / 128");
+  }
 #if GEMM_NARROW_PAIR
   auto wave_eff = [&](int bn) {
     const long long t = (long long)((M + 255) / 256) * ((N + bn - 1) / bn);
@@ -606,6 +703,7 @@ int gemm_bf16(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloa
 #if GEMM_NARROW_PAIR
   if (narrow) return launch_gemm<128, GEMM_NARROW_STAGES, 2>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
 #endif
+  if (pair && ep.stats_out) return launch_gemm<256, 5, 2, false, true>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, 0);
   if (pair) return launch_gemm<256, 5, 2>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
   if (wide && !small) return launch_gemm<256, 4, 1>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);
   return launch_gemm<128, 6, 1>(st, tmA, tmB, tmC, tmA2, M, N, K, ep, alias ? 1 : 0);

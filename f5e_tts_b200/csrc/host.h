@@ -24,6 +24,9 @@ int make_tmap_3d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t in
 int gemm_bf16(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloat16* W, int ldw, int M,
               int N, int K, const EpiParams& ep);
 
+bool gemm_can_fuse_stats(int M, int N);
+// (mean, M2) partials of gemm_bf16's stats_out ([M, slots], 128 columns each) -> rstd [M] and a2 [M, 64] of the folded LayerNorm
+int ln_finalize(cudaStream_t st, const float2* stats, int slots, int M, int D, float eps, float* rstd, __nv_bfloat16* a2);
 int gemm_vq(cudaStream_t st, const __nv_bfloat16* A, int lda, const __nv_bfloat16* Wp, int ldw, const float* bias_p, int M, int K,
             const VqEpi& vq);
 int vq_refine(cudaStream_t st, const float* x, int ld_x, int dim, const float* W, const float* bias, const VqEpi& vq,

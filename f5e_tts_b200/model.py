@@ -47,7 +47,8 @@ class _Model(C.Structure):
 
 
 class _Buffers(C.Structure):
-    _fields_ = [(n, C.c_void_p) for n in ("x_cat", "h0", "h1", "x", "xn", "qkv", "attn", "ff", "pred", "stats", "stats_a")]
+    _fields_ = [(n, C.c_void_p) for n in ("x_cat", "h0", "h1", "x", "xn", "qkv", "attn", "ff", "pred", "stats", "stats_a",
+                                          "stats_part")]
 
 
 class _Packing(C.Structure):  # f5e_dit_packing
@@ -350,7 +351,8 @@ class DiT(nn.Module):
             t = dict(x_cat=torch.zeros(rows, self.in_dim, device=dev, dtype=torch.bfloat16), h0=mk(D), h1=mk(D), x=mk(D),
                      xn=mk(D), qkv=mk(3 * inner), attn=torch.zeros(rows, inner, device=dev, dtype=torch.bfloat16),
                      ff=mk(D * self.ff_mult), pred=mk(self.mel_dim, torch.float32), stats=mk(1, torch.float32),
-                     stats_a=torch.zeros(rows, 64, device=dev, dtype=torch.bfloat16))
+                     stats_a=torch.zeros(rows, 64, device=dev, dtype=torch.bfloat16),
+                     stats_part=mk(max(1, D // 128) * 2, torch.float32))
             b = _Buffers(**{k: v.data_ptr() for k, v in t.items()})
             if self._gbuf:  # cached graphs refer to the workspace being replaced
                 _lib.load().f5e_graph_cache_clear()

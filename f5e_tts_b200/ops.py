@@ -18,7 +18,8 @@ def _cuda_bf16(t: torch.Tensor, name: str) -> None:
 
 
 def gemm(a, w, *, bias=None, act=_lib.ACT_NONE, gate=None, gate_stride=0, residual=None, row_len=None, n_pad=0,
-         rope=None, rope_heads=0, rope_inner=0, out=None, out_f32=False, n=None, split3=0, ln_rstd=None, ln_a2=None):
+         rope=None, rope_heads=0, rope_inner=0, out=None, out_f32=False, n=None, split3=0, ln_rstd=None, ln_a2=None,
+         stats_out=None):
     """epilogue(a[M,K] @ w[N,K]^T).  `a`/`w` may be row-strided views (last dim contiguous).
     ln_rstd / ln_a2 (from `row_stats`): LayerNorm folded in - `w` is then the folded weight [N, K + 64] of `fold_ln_weights`
     and `bias` its `d` vector."""
@@ -50,6 +51,9 @@ def gemm(a, w, *, bias=None, act=_lib.ACT_NONE, gate=None, gate_stride=0, residu
         ep.rope_inner, ep.rope_heads = rope_inner, rope_heads
     if ln_rstd is not None:
         ep.ln_rstd, ep.ln_a2 = ln_rstd.data_ptr(), ln_a2.data_ptr()
+    if stats_out is not None:  # fp32 [M, N / 128, 2]: LayerNorm statistics of the rows this GEMM produces (x += ... in place)
+        assert stats_out.dtype == torch.float32 and stats_out.shape == (M, N // 128, 2) and stats_out.is_contiguous()
+        ep.stats_out, ep.stats_slots = stats_out.data_ptr(), N // 128
     for t in (bias, gate):
         assert t is None or t.dtype == torch.float32
     assert row_len is None or row_len.dtype == torch.int32
@@ -221,3 +225,12 @@ def gather_rows(src, row_map):
     check(_lib.load().f5e_gather_rows(ptr(src), ptr(out), ptr(row_map), row_map.numel(), src.shape[1], stream_ptr()),
           "f5e_gather_rows")
     return out
+
+
+def ln_finalize(stats, D, eps=1e-6):
+    """(mean, M2) partials [M, D / 128, 2] of gemm(..., stats_out=) -> (rstd [M], a2 [M, 64]) as `row_stats` returns them."""
+    M, slots, _ = stats.shape
+    rstd = torch.empty(M, device=stats.device, dtype=torch.float32)
+    a2 = torch.zeros(M, 64, device=stats.device, dtype=torch.bfloat16)
+    check(_lib.load().f5e_ln_finalize(ptr(stats), slots, M, D, C.c_float(eps), ptr(rstd), ptr(a2), stream_ptr()), "f5e_ln_finalize")
+    return rstd, a2

@@ -67,6 +67,11 @@ typedef struct f5e_epilogue {
   const float* ln_rstd;    /* [M] or NULL: LayerNorm folded into this GEMM (see f5e_fold_job): v = acc * rstd[row] + bias[col] */
   const void* ln_a2;       /* bf16 [M, 64], with ln_rstd: A operand of the LAST K block (K = dim + 64), the row's -mean
                               as (hi, lo, hi, 0 ...); both written by f5e_row_stats */
+  float* stats_out;        /* fp32 [M, stats_slots, 2] or NULL: for x += gate * (acc + bias) IN PLACE (residual == out, bf16) on the
+                              CTA-pair kernel (M * N large enough: >= 74 tiles of 256 x 256, N % 256 == 0): the residual tile is
+                              read (TMA-staged) instead of reduce-added and every epilogue thread writes the (mean, M2) of its
+                              128 NEW output columns; f5e_ln_finalize turns the slots into ln_rstd / ln_a2 */
+  int32_t stats_slots;     /* N / 128 */
 } f5e_epilogue;
 
 /* C[M,N] = epilogue(A[M,K] @ W[N,K]^T); bf16 operands, tcgen05 / TMEM fp32 accumulation.
@@ -240,6 +245,9 @@ typedef struct f5e_dit_buffers {   /* caller-allocated scratch, rows = samples *
   float* pred;    /* fp32 [rows, mel_dim]                                                          */
   float* stats;   /* fp32 [rows] rstd of the folded-LayerNorm path; NULL when fold_jobs is NULL                    */
   void* stats_a;  /* bf16 [rows, 64], ZERO-initialised by the caller: (-mean_hi, -mean_lo, -mean_hi, 0 ...) per row */
+  float* stats_part; /* fp32 [rows, dim / 128, 2] or NULL: (mean, M2) partials written by the epilogues of the out-projection /
+                      * FF2 GEMMs of the folded path (they then take the next LayerNorm's statistics from the rows they
+                      * produce, and the residual stream is not re-read for them); NULL = one row_stats pass per norm */
 } f5e_dit_buffers;
 
 /* Optional row packing: after the (unmasked, hence padded-layout) ConvPositionEmbedding nothing but the key-masked
@@ -259,6 +267,8 @@ typedef struct f5e_dit_packing {
  * -mean as (hi, lo, hi), a2[r, 3..63] untouched (zero-initialised by the caller).  F.layer_norm's statistics,
  * model/modules.py:310-315.  f5e_fold_ln_weights: one launch rewrites W' | c | d of every job from `mod`. */
 int f5e_row_stats(const void* x, float* rstd, void* a2, int32_t M, int32_t D, float eps, void* stream);
+/* stats [M, slots, 2] written through f5e_epilogue.stats_out (slots * 128 == D) -> the same rstd / a2 f5e_row_stats gives. */
+int f5e_ln_finalize(const float* stats, int32_t slots, int32_t M, int32_t D, float eps, float* rstd, void* a2, void* stream);
 int f5e_fold_ln_weights(const f5e_fold_job* jobs_dev, int32_t n_jobs, int32_t total_rows, int32_t D, const float* mod,
                         void* stream);
 /* dst[r, :] = src[row_map[r], :] (bf16, C % 8 == 0): the packing step of f5e_dit_packing. */

@@ -299,3 +299,40 @@ def test_row_movers(cuda_dev):
     xp = torch.nn.functional.pad(x, (0, 0, taps // 2, taps // 2))
     ref = torch.stack([xp[:, t:t + N] for t in range(taps)], dim=2).reshape(B, N, taps * Cc)   # column tap * C + c
     assert torch.equal(u, ref)
+
+
+@pytest.mark.parametrize("M,K", [(30536, 1024), (19077, 2048)])
+def test_gemm_fused_layernorm_statistics(cuda_dev, M, K):
+    """The out-projection / FF2 form x += gate * (a @ w^T + b) on the CTA-pair kernel with the LayerNorm statistics of the NEW
+    rows taken in the epilogue (residual tile TMA-staged instead of the reduce-add): the result against fp32 torch, and
+    ln_finalize(stats) against row_stats of the stored result (same rounded values -> same statistics to fp32 round-off),
+    including rows whose mean is far from zero."""
+    from f5e_tts_b200 import ops
+    N = 1024
+    g = torch.Generator(device="cuda").manual_seed(M + K)
+    a = torch.randn(M, K, device=cuda_dev, generator=g).bfloat16()
+    w = (torch.randn(N, K, device=cuda_dev, generator=g) / math.sqrt(K)).bfloat16()
+    b = torch.randn(N, device=cuda_dev, generator=g)
+    gate = torch.randn(N, device=cuda_dev, generator=g)
+    x0 = torch.randn(M, N, device=cuda_dev, generator=g)
+    x0[::5] += 30.0
+    x0 = x0.bfloat16()
+    lens = torch.tensor([M - 1000], device=cuda_dev, dtype=torch.int32)   # the last 1000 rows are "padded": branch zeroed
+    valid = (torch.arange(M, device=cuda_dev) < M - 1000)[:, None]
+    ref = x0.float() + gate * torch.where(valid, a.float() @ w.float().t() + b, torch.zeros(1, device=cuda_dev))
+    x = x0.clone()
+    stats = torch.empty(M, N // 128, 2, device=cuda_dev)
+    out = ops.gemm(a, w, bias=b, gate=gate, residual=x, out=x, row_len=lens, n_pad=M, stats_out=stats)
+    assert out.data_ptr() == x.data_ptr()
+    assert rel_l2(x, ref) < 4e-3
+    err = (x.float() - ref).abs()
+    assert (err <= 0.008 * ref.abs().clamp_min(1.0)).all()   # ONE rounding now (the reduce-add path has two)
+    rstd, a2 = ops.ln_finalize(stats, N)
+    rstd_ref, a2_ref = ops.row_stats(x)
+    assert torch.allclose(rstd, rstd_ref, rtol=1e-4, atol=0)
+    mean, mean_ref = -(a2[:, 0].float() + a2[:, 1].float()), -(a2_ref[:, 0].float() + a2_ref[:, 1].float())
+    assert torch.allclose(mean, mean_ref, rtol=1e-5, atol=1e-5)
+    # and the unfused (reduce-add) path gives the same rows to one bf16 ulp
+    x2 = x0.clone()
+    ops.gemm(a, w, bias=b, gate=gate, residual=x2, out=x2, row_len=lens, n_pad=M)
+    assert rel_l2(x2, x) < 3e-3

@@ -195,3 +195,47 @@ def test_config2_exact_every_step(cuda_dev):
         json.dump(dict(config="BASELINE configs[1]: F5TTS_v1_Base depth 22, batch 16, 850-1030 frames, nfe 32, cfg 2, sway -1; "
                               "ODE state vs the fp32 oracle over the valid frames of all 16 utterances",
                        bar=f"product <= {K_TOL} x oracle-bf16 + 5e-3 (rel-L2), + 5e-2 (max-abs)", steps=table), f, indent=1)
+
+
+def test_cached_graph_reuse_and_invalidation(cuda_dev):
+    """use_cuda_graph: the instantiated Euler-loop graph is cached on everything it bakes in (dit.cu) and `model.py` keeps the
+    solve's buffers per shape.  A replay must see THIS call's inputs, a changed weight, and another shape - each compared bit
+    for bit with the stream path."""
+    from f5e_tts_b200 import _lib
+    cfg = SMALL
+    model, sd = build(cfg, 61, cuda_dev)
+    g = torch.Generator().manual_seed(62)
+
+    def inputs(B, n_ref, n_dur, n_txt):
+        ref_len = torch.randint(n_ref - 10, n_ref, (B,), generator=g).to(cuda_dev)
+        dur = torch.randint(n_dur - 40, n_dur, (B,), generator=g).to(cuda_dev)
+        cond = torch.randn(B, n_ref, cfg.mel_dim, generator=g).to(cuda_dev)
+        text = torch.randint(0, cfg.text_num_embeds, (B, n_txt), generator=g).to(cuda_dev)
+        return cond, text, dur, ref_len
+
+    def run(graph, inp, seed):
+        model.use_cuda_graph = graph
+        cond, text, dur, ref_len = inp
+        out, traj = model.sample(cond, text, None, dur, lens=ref_len, steps=6, cfg_strength=2.0, sway_sampling_coef=-1.0, seed=seed)
+        return out.clone(), traj.clone()
+
+    a, b, c = inputs(2, 60, 240, 25), inputs(2, 60, 240, 25), inputs(3, 50, 180, 20)
+    b = (b[0], b[1], a[2], a[3])  # same durations as `a`: the same solve shape and packing, different contents
+    ref = {k: run(False, v, s) for k, (v, s) in dict(a=(a, 3), b=(b, 4), c=(c, 5)).items()}
+    _lib.load().f5e_graph_cache_clear()
+    for key, inp, seed in (("a", a, 3), ("a", a, 3), ("b", b, 4), ("c", c, 5), ("a", a, 3), ("b", b, 4)):
+        out, traj = run(True, inp, seed)
+        assert torch.equal(out, ref[key][0]) and torch.equal(traj, ref[key][1]), key
+    # a weight updated in place (EMA copy, hot-swapped checkpoint): plan and graphs must follow
+    with torch.no_grad():
+        model.transformer.transformer_blocks[0].ff.ff["2"].bias.add_(0.5)
+    out_g, _ = run(True, a, 3)
+    out_s, _ = run(False, a, 3)
+    assert torch.equal(out_g, out_s) and not torch.equal(out_g, ref["a"][0])
+    # a parent-level load_state_dict (what the reference's load_checkpoint does) restores the old weights
+    missing, unexpected = model.load_state_dict({"transformer." + k: v for k, v in sd.items()}, strict=False)
+    assert not unexpected
+    model.to(torch.bfloat16)
+    out_g, _ = run(True, a, 3)
+    assert torch.equal(out_g, ref["a"][0])
+    assert _lib.load().f5e_graph_cache_clear() >= 1
