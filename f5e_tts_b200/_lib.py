@@ -59,18 +59,33 @@ def load():
     global _lib
     if _lib is not None:
         return _lib
+    from . import build as _build
+
+    build_error = None
     if os.environ.get("F5E_NO_BUILD") != "1":
         try:
-            from . import build as _build
-
             _build.build()
-        except Exception as e:  # the prebuilt .so may still be usable (GPU box without nvcc)
+        except Exception as e:  # the prebuilt .so may still be usable (a box without nvcc); its stamp is checked below
+            build_error = e
             if not _LIB_PATH.exists():
                 raise RuntimeError(f"libf5e_b200.so is missing and could not be built: {e}") from e
     if not _LIB_PATH.exists():
         raise RuntimeError(f"{_LIB_PATH} not found; run `python -m f5e_tts_b200.build`")
     lib = C.CDLL(str(_LIB_PATH))
     lib.f5e_last_error.restype = C.c_char_p
+    # A stale or half-built library must not run silently: its embedded stamp has to match the sources beside it
+    # (developer variants built with F5E_LIB_SUFFIX / F5E_NVCC_FLAGS carry their own flags and are exempt).
+    if not _SUFFIX and os.environ.get("F5E_ALLOW_STALE") != "1":
+        try:
+            lib.f5e_build_stamp.restype = C.c_char_p
+            have = lib.f5e_build_stamp().decode()
+        except AttributeError:
+            have = "missing"
+        want = _build.source_stamp()
+        if have != want:
+            raise RuntimeError(f"{_LIB_PATH} was built from other sources or flags (stamp {have[:12]} != {want[:12]})"
+                               + (f" and rebuilding failed: {build_error}" if build_error else "")
+                               + "; run `python -m f5e_tts_b200.build --force` (F5E_ALLOW_STALE=1 overrides)")
     lib.f5e_launch_count.restype = C.c_int64
     lib.f5e_prof_end.restype = C.c_int64
     _lib = lib

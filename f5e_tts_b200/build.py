@@ -36,13 +36,18 @@ def _stamp() -> str:
     return h.hexdigest()
 
 
+def source_stamp() -> str:
+    """Hash of the sources + flags a current library was built from (compare with the library's f5e_build_stamp())."""
+    return _stamp()
+
+
 def build(force: bool = False, verbose: bool = False) -> Path:
     stamp_file = HERE / "csrc" / (".build_stamp" + ("_" + SUFFIX if SUFFIX else ""))
     stamp = _stamp()
     if not force and LIB.exists() and stamp_file.exists() and stamp_file.read_text() == stamp:
         return LIB
     if not Path(NVCC).exists():
-        if LIB.exists():  # GPU box without the sources changed: use the shipped library
+        if LIB.exists():  # no compiler here: the shipped library is all there is; _lib.load() checks its embedded stamp
             return LIB
         raise RuntimeError(f"nvcc not found at {NVCC} and no prebuilt {LIB}")
     objdir = HERE / ("build_" + SUFFIX if SUFFIX else "build")
@@ -51,6 +56,8 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     def compile_one(src: Path) -> Path:
         obj = objdir / (src.stem + ".o")
         cmd = [NVCC, *FLAGS, "-c", str(src), "-o", str(obj)]
+        if src.name == "c_api.cu":  # f5e_build_stamp(): lets the loader tell a stale library from a current one
+            cmd.insert(1, f'-DF5E_BUILD_STAMP="{stamp}"')
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         r = subprocess.run(cmd, capture_output=True, text=True)

@@ -22,6 +22,10 @@ static EpiParams to_epi(const f5e_epilogue* e, int M) {
 extern "C" {
 
 const char* f5e_last_error(void) { return last_error(); }
+#ifndef F5E_BUILD_STAMP
+#define F5E_BUILD_STAMP "unstamped"
+#endif
+const char* f5e_build_stamp(void) { return F5E_BUILD_STAMP; }
 int f5e_version(void) { return 100; }
 
 int f5e_check_device(void) {

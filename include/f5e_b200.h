@@ -21,6 +21,9 @@ extern "C" {
 #endif
 
 const char* f5e_last_error(void);
+/* sha256 over the sources and compiler flags this library was built from (f5e_tts_b200/build.py); the ctypes loader
+ * refuses a library whose stamp differs from the sources next to it. */
+const char* f5e_build_stamp(void);
 /* 0 when the current device is compute capability 10.x, else an error (message says what it is). */
 int f5e_check_device(void);
 int f5e_version(void);

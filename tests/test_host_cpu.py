@@ -187,3 +187,14 @@ def test_epilogue_struct_matches_header_and_docs():
     assert doc_fields == hdr
     g = _header_struct_fields("f5e_guidance")
     assert [n for n, _ in g] == [n for n, _ in _lib.Guidance._fields_]
+
+
+def test_library_stamp_matches_sources():
+    """The loaded library carries the hash of the sources / flags it was built from; `_lib.load()` refuses a stale one."""
+    import ctypes as C
+
+    from f5e_tts_b200 import _lib, build
+
+    lib = _lib.load()
+    lib.f5e_build_stamp.restype = C.c_char_p
+    assert lib.f5e_build_stamp().decode() == build.source_stamp()
