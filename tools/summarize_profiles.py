@@ -86,7 +86,7 @@ def full():
         except (KeyError, ValueError):
             pass
         out.append("")
-    open(os.path.join(ROOT, "profiles", f"{tag}_kernels.md"), "w").write("\n".join(out) + "\n")
+    open(os.path.join(ROOT, "profiles", f"{tag}_full.md"), "w").write("\n".join(out) + "\n")
     tj = {k: sum(v) / len(v) for k, v in traffic.items()}
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp) and not re.fullmatch(r"r\d+", tag):  # side captures (e.g. r01ppg) add to the table, never replace it

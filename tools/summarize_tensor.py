@@ -9,7 +9,9 @@ import re
 import sys
 
 LABELS = ["gemm qkv (+bias)", "gemm qkv + RoPE epilogue", "gemm qkv plain", "gemm out (+gate, residual reduce-add)",
-          "gemm ff1 (+tanh-GELU)", "gemm ff1 plain", "gemm ff2 (+gate, residual reduce-add)", "gemm in_proj (K = 712)",
+          "gemm out, residual READ in the epilogue (scalar loads: the path the fused statistics replaced by a TMA-staged tile)",
+          "gemm ff1 (+tanh-GELU)", "gemm ff1 plain", "gemm ff2 (+gate, residual reduce-add)",
+          "gemm ff2, residual READ in the epilogue", "gemm in_proj (K = 712)",
           "gemm proj_out (N = 100, fp32 out)", "attention", "conv_pos", "norm_mod", "row_stats"]
 
 
@@ -45,7 +47,8 @@ def main():
           "FRACTIONS; the `events` column is the same kernel timed with CUDA events in the plain run just before.\n")
     print("| kernel | launch | us (ncu) | GHz | UMMA instr | tensor pipe busy | XU busy | DRAM MB | events: us, TFLOP/s or GB/s |")
     print("|---|---|---:|---:|---:|---:|---:|---:|---|")
-    ev_keys = ["gemm_qkv", "gemm_qkv_rope_compute", "gemm_qkv_plain", "gemm_out", "gemm_ff1", "gemm_ff1_plain", "gemm_ff2", "gemm_in_proj",
+    ev_keys = ["gemm_qkv", "gemm_qkv_rope_compute", "gemm_qkv_plain", "gemm_out", "gemm_out_residual_read", "gemm_ff1", "gemm_ff1_plain",
+               "gemm_ff2", "gemm_ff2_residual_read", "gemm_in_proj",
                "gemm_proj_out", "attention", "conv_pos", "norm_mod", "row_stats"]
     for gi, (short, ms) in enumerate(groups):
         m = ms[-1]
