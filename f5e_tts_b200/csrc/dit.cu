@@ -78,6 +78,8 @@ static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_d
     row_start = pack->row_start;
     row_len = nullptr;  // there are no padded rows left to zero
   }
+  if (m->w_long_skip)  // the residual of the long skip: the stream as it enters the blocks (h1 is free after the convs)
+    F5E_CUDA_CHECK(cudaMemcpyAsync(b->h1, xs, (size_t)rows * D * sizeof(__nv_bfloat16), cudaMemcpyDeviceToDevice, st));
   // Folded path: the out-projection / FF2 GEMMs take the LayerNorm statistics of the rows they produce in their epilogue
   // (EpiParams::stats_out) whenever they run on the CTA-pair kernel; row_stats then reads the residual stream only once per
   // evaluation (before the first block) instead of twice per block.
@@ -105,7 +107,8 @@ static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_d
     {  // fused q/k/v projection + RoPE (modules.py:442-480)
       EpiParams ep{};
       ep.out = b->qkv; ep.ldo = 3 * inner; ep.bias = L.b_qkv; ep.n_pad = n_pad; ep.row_info = row_info;
-      if (m->rope_heads > 0) {
+      const bool qk_norm = L.q_norm_w != nullptr;  // then RMSNorm and the rotation run as one in-place pass after the GEMM
+      if (m->rope_heads > 0 && !qk_norm) {
         ep.rope_inv_freq = m->rope_inv_freq; ep.rope_inner = inner; ep.rope_heads = m->rope_heads;
       }
       if (folded) {
@@ -115,6 +118,9 @@ static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_d
         F5E_TRY(gemm_bf16(st, bf(b->xn), D, bf(L.w_qkv), D, rows, 3 * inner, D, ep));
       }
     }
+    if (L.q_norm_w)
+      F5E_TRY(qk_norm_rope(st, bfm(b->qkv), 3 * inner, rows, inner, m->heads, L.q_norm_w, L.k_norm_w, 1e-6f,
+                           m->rope_heads > 0 ? m->rope_inv_freq : nullptr, m->rope_heads, n_pad, row_info));
     F5E_TRY(attention(st, bf(b->qkv), 3 * inner, bfm(b->attn), inner, klen, samples, n_pad, m->heads, 0.125f, row_start, rows));
     {  // to_out + masked_fill + gate_msa * attn + residual (modules.py:494-501, :634)
       EpiParams ep{};
@@ -140,6 +146,16 @@ static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_d
       if (fuse_stats && l + 1 < m->depth) { e2.stats_out = reinterpret_cast<float2*>(b->stats_part); e2.stats_slots = slots; }
       F5E_TRY(gemm_bf16(st, bf(b->ff), m->ff_dim, bf(L.w_ff2), m->ff_dim, rows, D, m->ff_dim, e2));
     }
+  }
+  if (m->w_long_skip) {  // x = W[:, :D] x + W[:, D:] residual  (Linear(2 dim -> dim, no bias) over the concatenation)
+    const __nv_bfloat16* W = bf(m->w_long_skip);
+    EpiParams e1{};
+    e1.out = b->xn; e1.ldo = D; e1.n_pad = n_pad;
+    F5E_TRY(gemm_bf16(st, bf(b->h1), D, W + D, 2 * D, rows, D, D, e1));
+    EpiParams e2{};
+    e2.out = b->h1; e2.ldo = D; e2.n_pad = n_pad; e2.residual = bf(b->xn); e2.ldr = D;
+    F5E_TRY(gemm_bf16(st, bf(xs), D, W, 2 * D, rows, D, D, e2));
+    xs = b->h1;
   }
   // AdaLayerNorm_Final (chunk order scale, shift: modules.py:331-336) + proj_out (dit.py:469-470)
   const float* mf = mod + (size_t)m->depth * 6 * D;
@@ -216,6 +232,7 @@ int f5e_ode_solve_guided(const f5e_dit_model* model, const f5e_dit_buffers* buf,
     for (int l = 0; l < model->depth; ++l) {
       const f5e_dit_layer& L = model->layers[l];
       F5E_REQUIRE(L.wf_qkv && L.c_qkv && L.d_qkv && L.wf_ff1 && L.c_ff1 && L.d_ff1, "f5e_ode_solve: layer %d lacks fold scratch", l);
+      F5E_REQUIRE((L.q_norm_w == nullptr) == (L.k_norm_w == nullptr), "f5e_ode_solve: layer %d has only one of q_norm / k_norm", l);
     }
   }
   auto enqueue = [&](cudaStream_t es) -> int {

@@ -217,6 +217,54 @@ int ln_finalize(cudaStream_t st, const float2* stats, int slots, int M, int D, f
   return 0;
 }
 
+// qk_norm = "rms_norm" (reference model/modules.py:391-398, 463-467; RMSNorm.forward :282-294): RMSNorm over dim_head with a
+// learned weight on every head of Q and K, BEFORE the rotary embedding.  No shipped config turns it on, so it is a small
+// in-place pass over the Q and K column blocks of the QKV GEMM's output (the GEMM then runs without its RoPE epilogue and
+// the rotation happens here): one warp per (row, q|k, head), a lane holds one interleaved RoPE pair.
+__global__ void __launch_bounds__(256)
+qk_norm_rope_kernel(__nv_bfloat16* __restrict__ qkv, int ld, int rows, int inner, int heads, const float* __restrict__ qw,
+                    const float* __restrict__ kw, float eps, const float* __restrict__ inv_freq, int rope_heads, int n_pad,
+                    const int* __restrict__ row_info) {
+  const int lane = threadIdx.x & 31;
+  const long long total = (long long)rows * 2 * heads;
+  for (long long it = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); it < total; it += (long long)gridDim.x * 8) {
+    const int head = (int)(it % heads), which = (int)((it / heads) & 1), row = (int)(it / (2 * heads));
+    __nv_bfloat16* p = qkv + (size_t)row * ld + which * inner + head * 64 + 2 * lane;
+    float2 v = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(p));
+    const float ms = warp_sum(v.x * v.x + v.y * v.y) * (1.0f / 64.0f);
+    const float r = rsqrtf(ms + eps);
+    const float* w = which ? kw : qw;
+    v.x = v.x * r * __ldg(w + 2 * lane);
+    v.y = v.y * r * __ldg(w + 2 * lane + 1);
+    if (inv_freq && head < rope_heads) {  // same angle evaluation as the GEMM epilogue (gemm.cu)
+      const int frame = row_info ? (__ldg(row_info + row) & 0xffff) : row % n_pad;
+      const float x = (float)frame * __ldg(inv_freq + lane);
+      const float k = rintf(x * 0.15915494309189535f);
+      float a = fmaf(k, -6.2831854820251465f, x);
+      a = fmaf(k, 1.7484555e-7f, a);
+      float sn, cs;
+      asm("sin.approx.ftz.f32 %0, %1;" : "=f"(sn) : "f"(a));
+      asm("cos.approx.ftz.f32 %0, %1;" : "=f"(cs) : "f"(a));
+      const float x0 = v.x, x1 = v.y;
+      v.x = x0 * cs - x1 * sn;
+      v.y = x1 * cs + x0 * sn;
+    }
+    *reinterpret_cast<uint32_t*>(p) = pack_bf16x2(v.x, v.y);
+  }
+}
+
+int qk_norm_rope(cudaStream_t st, __nv_bfloat16* qkv, int ld, int rows, int inner, int heads, const float* qw, const float* kw,
+                 float eps, const float* inv_freq, int rope_heads, int n_pad, const int* row_info) {
+  F5E_REQUIRE(qkv && qw && kw && rows > 0 && inner == heads * 64 && ld % 2 == 0 && n_pad > 0, "qk_norm_rope: bad arguments");
+  const long long total = (long long)rows * 2 * heads;
+  long long grid = (total + 7) / 8;
+  if (grid > num_sms() * 16) grid = num_sms() * 16;
+  LaunchScope ls(st, PROF_NORM, rows, inner, 4);
+  qk_norm_rope_kernel<<<(int)grid, 256, 0, st>>>(qkv, ld, rows, inner, heads, qw, kw, eps, inv_freq, rope_heads, n_pad, row_info);
+  F5E_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
 // one warp per weight row; `jobs` (device) lists the matrices of every layer: rows [row0, row0 + N) of the launch
 __global__ void __launch_bounds__(256)
 fold_ln_weights_kernel(const FoldJob* __restrict__ jobs, int n_jobs, int total_rows, int D, const float* __restrict__ mod) {

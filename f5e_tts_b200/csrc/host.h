@@ -48,6 +48,8 @@ int fold_ln_weights(cudaStream_t st, const FoldJob* jobs_dev, int n_jobs, int to
 int guided_euler(cudaStream_t st, const float* pred, int ld_pred, float* y, __nv_bfloat16* x_cat, int ld_cat,
                  float* traj, int rows, int C, float dt, int branches, float c0, float c1, int round_bf16,
                  const int* row_map = nullptr, int rows_state = 0);
+int qk_norm_rope(cudaStream_t st, __nv_bfloat16* qkv, int ld, int rows, int inner, int heads, const float* qw, const float* kw,
+                 float eps, const float* inv_freq, int rope_heads, int n_pad, const int* row_info);
 int gather_rows(cudaStream_t st, const __nv_bfloat16* src, __nv_bfloat16* dst, const int* row_map, int rows, int C);
 // o[rows, inner] = softmax(q k^T * scale, keys < klen[sample]) v over qkv[rows, 3*inner] (Q|K|V column blocks)
 // row_start (optional): first row of every sample when the rows are PACKED (valid frames only); total_rows = rows of qkv

@@ -29,7 +29,7 @@ _SOLVE_LOCK = threading.RLock()
 # ---- ctypes mirrors of include/f5e_b200.h ------------------------------------------------------------
 class _Layer(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("w_qkv", "b_qkv", "w_out", "b_out", "w_ff1", "b_ff1", "w_ff2", "b_ff2",
-                                          "wf_qkv", "c_qkv", "d_qkv", "wf_ff1", "c_ff1", "d_ff1")]
+                                          "wf_qkv", "c_qkv", "d_qkv", "wf_ff1", "c_ff1", "d_ff1", "q_norm_w", "k_norm_w")]
 
 
 class _FoldJob(C.Structure):  # f5e_fold_job
@@ -43,7 +43,7 @@ class _Model(C.Structure):
         ("w_in", C.c_void_p), ("b_in", C.c_void_p), ("w_conv1", C.c_void_p), ("b_conv1", C.c_void_p),
         ("w_conv2", C.c_void_p), ("b_conv2", C.c_void_p), ("layers", C.POINTER(_Layer)),
         ("w_proj", C.c_void_p), ("b_proj", C.c_void_p), ("rope_inv_freq", C.c_void_p), ("fold_jobs", C.c_void_p), ("fold_n_jobs", C.c_int32), ("fold_rows", C.c_int32),
-        ("isolate_samples", C.c_int32)]
+        ("w_long_skip", C.c_void_p), ("isolate_samples", C.c_int32)]
 
 
 class _Buffers(C.Structure):
@@ -108,13 +108,21 @@ class _Holder(nn.Module):
             setattr(self, k, v)
 
 
+class _RMSNormWeight(nn.Module):  # parameter container of model/modules.py:275-280 (the arithmetic is qk_norm_rope_kernel)
+    def __init__(self, dim):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(dim))
+
+
 class _Block(nn.Module):  # model/modules.py:610-625
-    def __init__(self, dim, heads, dim_head, ff_mult):
+    def __init__(self, dim, heads, dim_head, ff_mult, qk_norm=None):
         super().__init__()
         inner = heads * dim_head
         self.attn_norm = _Holder(linear=nn.Linear(dim, dim * 6))
         self.attn = _Holder(to_q=nn.Linear(dim, inner), to_k=nn.Linear(dim, inner), to_v=nn.Linear(dim, inner),
                             to_out=_seq({0: nn.Linear(inner, dim)}))
+        if qk_norm == "rms_norm":  # modules.py:394-396
+            self.attn.q_norm, self.attn.k_norm = _RMSNormWeight(dim_head), _RMSNormWeight(dim_head)
         self.ff = _Holder(ff=_seq({0: _seq({0: nn.Linear(dim, dim * ff_mult)}), 2: nn.Linear(dim * ff_mult, dim)}))
 
 
@@ -138,8 +146,8 @@ class DiT(nn.Module):
         super().__init__()
         if dim_head != 64:
             raise NotImplementedError("f5e_tts_b200: the attention kernel is specialised for dim_head=64")
-        if qk_norm is not None or long_skip_connection:
-            raise NotImplementedError("f5e_tts_b200: qk_norm / long_skip_connection are not on the F5E inference path")
+        if qk_norm not in (None, "rms_norm"):
+            raise ValueError(f"Unimplemented qk_norm: {qk_norm}")  # as the reference (modules.py:397-398)
         if dim % 256 or (dim // 16) % 16 or dim // 16 > 64:
             raise NotImplementedError(f"f5e_tts_b200: dim={dim} unsupported (need dim % 256 == 0 and dim/16 in 16..64)")
         text_dim = mel_dim if text_dim is None else text_dim
@@ -183,7 +191,9 @@ class DiT(nn.Module):
             0: nn.Conv1d(dim, dim, 31, groups=16, padding=15), 2: nn.Conv1d(dim, dim, 31, groups=16, padding=15)})))
         self.rotary_embed = _Holder()
         self.rotary_embed.register_buffer("inv_freq", 1.0 / (10000 ** (torch.arange(0, dim_head, 2).float() / dim_head)))
-        self.transformer_blocks = nn.ModuleList([_Block(dim, heads, dim_head, ff_mult) for _ in range(depth)])
+        self.qk_norm = qk_norm
+        self.transformer_blocks = nn.ModuleList([_Block(dim, heads, dim_head, ff_mult, qk_norm) for _ in range(depth)])
+        self.long_skip_connection = nn.Linear(dim * 2, dim, bias=False) if long_skip_connection else None  # dit.py:264
         self.norm_out = _Holder(linear=nn.Linear(dim, dim * 2))
         self.proj_out = nn.Linear(dim, mel_dim)
         self.text_cond = self.text_uncond = None
@@ -258,6 +268,8 @@ class DiT(nn.Module):
             layers[l].w_out, layers[l].b_out = K(bf(a.to_out["0"].weight)), K(f32(a.to_out["0"].bias))
             layers[l].w_ff1, layers[l].b_ff1 = K(bf(blk.ff.ff["0"]["0"].weight)), K(f32(blk.ff.ff["0"]["0"].bias))
             layers[l].w_ff2, layers[l].b_ff2 = K(bf(blk.ff.ff["2"].weight)), K(f32(blk.ff.ff["2"].bias))
+            if self.qk_norm == "rms_norm":
+                layers[l].q_norm_w, layers[l].k_norm_w = K(f32(a.q_norm.weight)), K(f32(a.k_norm.weight))
             mod_w.append(blk.attn_norm.linear.weight)
             mod_b.append(blk.attn_norm.linear.bias)
         # folded-LayerNorm path of the Euler loop (include/f5e_b200.h: f5e_fold_job): per-step rewritten QKV / FF1 weights
@@ -295,6 +307,8 @@ class DiT(nn.Module):
         m.w_conv2, m.b_conv2 = K(ops.pack_conv_pos_weight(c["2"].weight.detach().to(dev))), K(f32(c["2"].bias))
         m.layers = C.cast(layers, C.POINTER(_Layer))
         m.w_proj, m.b_proj = K(bf(self.proj_out.weight)), K(f32(self.proj_out.bias))
+        if self.long_skip_connection is not None:
+            m.w_long_skip = K(bf(self.long_skip_connection.weight))
         m.rope_inv_freq = K(f32(self.rotary_embed.inv_freq))  # angles are evaluated in the QKV epilogue
         P.layers, P.model = layers, m
         # text embedder

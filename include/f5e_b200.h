@@ -201,6 +201,9 @@ typedef struct f5e_dit_layer {     /* one DiTBlock (model/modules.py:610-641); w
    * columns carry the row sum) and their fp32 column vectors c (row sums) and d (bias). */
   void* wf_qkv;  float* c_qkv;  float* d_qkv;
   void* wf_ff1;  float* c_ff1;  float* d_ff1;
+  /* qk_norm = "rms_norm" (model/modules.py:391-398, 463-467): fp32 [64] weights of attn.q_norm / attn.k_norm, both NULL = off.
+   * RMSNorm over dim_head on every head of Q and K before the rotary embedding. */
+  const float* q_norm_w;  const float* k_norm_w;
 } f5e_dit_layer;
 
 /* One entry of the DEVICE-resident job list of the folded-LayerNorm path.  In the Euler loop every sample shares the
@@ -229,6 +232,8 @@ typedef struct f5e_dit_model {
   const float* rope_inv_freq;                 /* rotary_embed.inv_freq [32] fp32 (NULL only when rope_heads == 0) */
   const f5e_fold_job* fold_jobs;              /* DEVICE array [fold_n_jobs] (2 per layer: QKV, FF1) or NULL = no folding */
   int32_t fold_n_jobs, fold_rows;             /* fold_rows = sum of N over the jobs */
+  const void* w_long_skip;                    /* long_skip_connection.weight bf16 [dim, 2 * dim] or NULL (backbones/dit.py:264,
+                                               * 456-467): x = W @ cat(x_after_blocks, x_before_blocks) ahead of norm_out */
   int32_t isolate_samples;                    /* != 0 (needs klen): frames >= klen[s] are ZEROED at the inputs of both
                                                * ConvPositionEmbedding convs, so a sample's result does not depend on
                                                * what it is batched with (a padded batch then equals the per-sample

@@ -39,6 +39,8 @@ class DiTConfig:
     text_mask_padding: bool = True
     conv_layers: int = 4
     pe_attn_head: int | None = None
+    qk_norm: str | None = None          # "rms_norm": RMSNorm(dim_head) on q and k before RoPE (modules.py:391-398, 463-467)
+    long_skip_connection: bool = False  # Linear(2 dim -> dim, no bias) over cat(x, x_before_the_blocks) (dit.py:264, 456-467)
     use_ppg: bool = False
     ppg_dim: int = 256
     use_codebook: bool = False
@@ -141,6 +143,11 @@ def make_state_dict(cfg: DiTConfig, seed: int = 1234, device="cpu", zero_init_st
         lin(p + ".attn.to_out.0", D, inner)
         lin(p + ".ff.ff.0.0", D * cfg.ff_mult, D)
         lin(p + ".ff.ff.2", D, D * cfg.ff_mult)
+        if cfg.qk_norm == "rms_norm":  # the reference initialises these to ones; random so that a wrong weight shows
+            sd[p + ".attn.q_norm.weight"] = 1.0 + 0.3 * torch.randn(cfg.dim_head, generator=g)
+            sd[p + ".attn.k_norm.weight"] = 1.0 + 0.3 * torch.randn(cfg.dim_head, generator=g)
+    if cfg.long_skip_connection:
+        sd["long_skip_connection.weight"] = torch.randn(D, 2 * D, generator=g) / (2 * D) ** 0.5
     lin("norm_out.linear", 2 * D, D, std=zero_init_std)
     lin("proj_out", cfg.mel_dim, D, std=zero_init_std)
     return {k: v.to(device) for k, v in sd.items()}
@@ -329,6 +336,7 @@ class OracleDiT:
         ang = rope_angles(N, cfg.dim_head, x.device)
         H, dh = cfg.heads, cfg.dim_head
         ts = F.silu(t)
+        residual = h  # dit.py:456-457 (used only with long_skip_connection)
         for l in range(cfg.depth):
             p = f"transformer_blocks.{l}"
             emb = _lin(sd, p + ".attn_norm.linear", ts)
@@ -337,6 +345,9 @@ class OracleDiT:
             q = _lin(sd, p + ".attn.to_q", nrm).view(B, N, H, dh).transpose(1, 2)
             k = _lin(sd, p + ".attn.to_k", nrm).view(B, N, H, dh).transpose(1, 2)
             v = _lin(sd, p + ".attn.to_v", nrm).view(B, N, H, dh).transpose(1, 2)
+            if cfg.qk_norm == "rms_norm":  # modules.py:463-467, RMSNorm.forward :282-294 (F.rms_norm over dim_head)
+                q = F.rms_norm(q, (dh,), weight=sd[p + ".attn.q_norm.weight"], eps=1e-6)
+                k = F.rms_norm(k, (dh,), weight=sd[p + ".attn.k_norm.weight"], eps=1e-6)
             pn = H if cfg.pe_attn_head is None else cfg.pe_attn_head
             q = torch.cat((apply_rope(q[:, :pn], ang), q[:, pn:]), dim=1)
             k = torch.cat((apply_rope(k[:, :pn], ang), k[:, pn:]), dim=1)
@@ -359,6 +370,8 @@ class OracleDiT:
             h = h + gate_mlp.unsqueeze(1) * ff
             if taps is not None and l == 0:
                 taps["block0"] = h
+        if cfg.long_skip_connection:  # dit.py:466-467
+            h = F.linear(torch.cat((h, residual), dim=-1), sd["long_skip_connection.weight"])
         emb = _lin(sd, "norm_out.linear", ts)
         scale, shift = torch.chunk(emb, 2, dim=1)
         h = F.layer_norm(h, (cfg.dim,), eps=1e-6) * (1 + scale)[:, None, :] + shift[:, None, :]

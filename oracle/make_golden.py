@@ -35,7 +35,8 @@ def build_reference(cfg: O.DiTConfig, seed: int):
                      weight_proj_factor=1)
     dit = DiT(dim=cfg.dim, depth=cfg.depth, heads=cfg.heads, ff_mult=cfg.ff_mult, mel_dim=cfg.mel_dim,
               text_num_embeds=cfg.text_num_embeds, text_dim=cfg.text_dim, text_mask_padding=cfg.text_mask_padding,
-              conv_layers=cfg.conv_layers, pe_attn_head=cfg.pe_attn_head, ppg_config=ppg_config, cb_config=cb_config)
+              conv_layers=cfg.conv_layers, pe_attn_head=cfg.pe_attn_head, qk_norm=cfg.qk_norm,
+              long_skip_connection=cfg.long_skip_connection, ppg_config=ppg_config, cb_config=cb_config)
     sd = O.make_state_dict(cfg, seed)
     missing, unexpected = dit.load_state_dict(sd, strict=False)
     missing = [k for k in missing if "num_batches_tracked" not in k and "inv_freq" not in k]
@@ -306,8 +307,12 @@ def case_ppg_map(name):
                os.path.join(OUT, name + ".pt"))
 
 
+SMALL_QKN = O.DiTConfig(dim=256, depth=2, heads=4, text_dim=64, conv_layers=2, text_num_embeds=50, qk_norm="rms_norm",
+                        long_skip_connection=True, pe_attn_head=2)
+
 if __name__ == "__main__":
     case_ppg_map("ppg_map")
+    case_single_eval("dit_eval_small_qknorm_skip", SMALL_QKN, 103)
     case_mel("melspec")
     case_vq("vq")
     case_single_eval("dit_eval_small", SMALL, 100)

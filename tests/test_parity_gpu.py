@@ -29,7 +29,8 @@ def build(cfg, seed, dev):
                      temp_decay=0.999, groups=cfg.cb_groups, combine_groups=False, weight_proj_depth=1, weight_proj_factor=1)
     dit = DiT(dim=cfg.dim, depth=cfg.depth, heads=cfg.heads, ff_mult=cfg.ff_mult, mel_dim=cfg.mel_dim,
               text_num_embeds=cfg.text_num_embeds, text_dim=cfg.text_dim, text_mask_padding=cfg.text_mask_padding,
-              conv_layers=cfg.conv_layers, pe_attn_head=cfg.pe_attn_head, ppg_config=ppg_config, cb_config=cb_config)
+              conv_layers=cfg.conv_layers, pe_attn_head=cfg.pe_attn_head, qk_norm=cfg.qk_norm,
+              long_skip_connection=cfg.long_skip_connection, ppg_config=ppg_config, cb_config=cb_config)
     missing, unexpected = dit.load_state_dict(sd, strict=False)
     assert not unexpected and all("num_batches_tracked" in k or "inv_freq" in k for k in missing), (missing, unexpected)
     model = CFM(dit, ppg_config=ppg_config, cb_config=cb_config).to(dev).to(torch.bfloat16)
@@ -56,7 +57,13 @@ PPG_TR = O.DiTConfig(dim=512, depth=2, heads=8, text_dim=256, conv_layers=2, tex
                      pe_attn_head=1, use_ppg=True, ppg_dim=256, ppg_transformer=True, ppg_nhead=4, ppg_ff=512, ppg_layers=2)
 
 
+# qk_norm="rms_norm" (modules.py:391-398, 463-467) + long_skip_connection (dit.py:264, 456-467) + partial-head RoPE
+QKN_SKIP = O.DiTConfig(dim=512, depth=3, heads=8, text_dim=256, conv_layers=2, text_num_embeds=50, qk_norm="rms_norm",
+                       long_skip_connection=True, pe_attn_head=3)
+
+
 @pytest.mark.parametrize("cfg,B,N,lens", [(SMALL, 1, 200, None), (SMALL, 3, 333, [333, 150, 290]),
+                                           (QKN_SKIP, 1, 200, None), (QKN_SKIP, 3, 333, [333, 150, 290]),
                                            (SMALL_PPG, 2, 260, [260, 131]), (BASE2, 2, 300, [300, 177]),
                                            (PPG_TR, 2, 260, [260, 131]),
                                            (BASE2, 2, 2812, [2812, 1903])])  # BASELINE configs[4] length (30 s utterances)
@@ -79,7 +86,7 @@ def test_dit_eval_vs_oracle(cuda_dev, cfg, B, N, lens):
             assert e_got <= K_TOL * e_ref + 5e-3, (i, e_got, e_ref)
 
 
-@pytest.mark.parametrize("cfg,B", [(SMALL, 1), (SMALL, 3), (SMALL_PPG, 2), (PPG_TR, 2)])
+@pytest.mark.parametrize("cfg,B", [(SMALL, 1), (SMALL, 3), (SMALL_PPG, 2), (PPG_TR, 2), (QKN_SKIP, 3)])
 def test_cfm_sample_vs_oracle(cuda_dev, cfg, B):
     model, sd = build(cfg, 17, cuda_dev)
     g = torch.Generator().manual_seed(18)
@@ -251,3 +258,4 @@ def test_concurrent_callers_take_turns(cuda_dev):
         together = list(ex.map(run, jobs))
     for a, b in zip(alone, together):
         assert torch.equal(a, b)
+
