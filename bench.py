@@ -55,7 +55,7 @@ def parse():
     ap.add_argument("--cpu-budget-s", type=float, default=15.0)
     ap.add_argument("--no-extras", action="store_true", help="skip gpu_baseline / latency / eval_set")
     ap.add_argument("--eval-utterances", type=int, default=1088)
-    ap.add_argument("--pack", type=int, default=-1, help="CFM.pack_valid_rows: -1 default (only where exact), 0 never, 1 always")
+    ap.add_argument("--pack", type=int, default=-1, help="CFM.pack_valid_rows: -1 default (exact: padded rows kept, attention sub-block skipped on them), 0 padded layout, 1 drop padded rows")
     return ap.parse_args()
 
 
@@ -629,7 +629,8 @@ def run_b200(a, rank, local_rank, world):
                                   "inside the timed region",
                          gather_ms_per_step=(statistics.mean(g_ms) if g_ms else 0.0)),
                 gpu_launches=int(launches),
-                pack_valid_rows=bool(model.last_aux["packed_rows"]),
+                pack_valid_rows=("drop" if model.last_aux["dropped_padded_rows"] else
+                                 "split (exact)" if model.last_aux["packed_rows"] else "off"),
                 roofline=dict(bound="tensor", kernel="gemm_bf16_kernel (DiT block qkv/out/ff1/ff2)", achieved=gm["achieved"],
                               peak=peak_tf, unit="TFLOP/s", frac=gm["frac"], traffic=traffic.get("gemm_bf16_kernel"),
                               peak_source=peak_src, launches=gm["launches"], avg_launch_ms=gm["avg_launch_ms"],

@@ -65,18 +65,22 @@ static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_d
   }
   // Everything up to here runs on the padded [samples, n_pad] layout (the reference's unmasked convolution sees the
   // padded frames).  From here on no op mixes frames except attention, which masks padded keys: with a packing the 22
-  // blocks run on the valid frames only (rows = sum of klen), padded query rows are never computed.
+  // blocks run on a permuted row order, valid frames first.  `rows` row-local work (norms, feed-forward), `rows_att`
+  // rows of attention-side work (QKV, attention, out-projection): the reference zeroes that branch on padded rows, so
+  // skipping it there leaves them exactly as they are.  A dropping packing (rows_total == 0) has rows == rows_att.
   void* xs = b->x;  // residual stream
   const int* row_info = nullptr;
   const int* row_start = nullptr;
   const int* row_len = klen;
+  int rows_att = rows;
   if (pack) {
-    F5E_TRY(gather_rows(st, bf(b->x), bfm(b->h0), pack->row_map, pack->rows_packed, D));
+    rows = pack->rows_total > 0 ? pack->rows_total : pack->rows_packed;
+    rows_att = pack->rows_packed;
+    F5E_TRY(gather_rows(st, bf(b->x), bfm(b->h0), pack->row_map, rows, D));
     xs = b->h0;
-    rows = pack->rows_packed;
     row_info = pack->row_info;
     row_start = pack->row_start;
-    row_len = nullptr;  // there are no padded rows left to zero
+    row_len = nullptr;  // the out-projection never touches a padded row
   }
   if (m->w_long_skip)  // the residual of the long skip: the stream as it enters the blocks (h1 is free after the convs)
     F5E_CUDA_CHECK(cudaMemcpyAsync(b->h1, xs, (size_t)rows * D * sizeof(__nv_bfloat16), cudaMemcpyDeviceToDevice, st));
@@ -90,7 +94,7 @@ static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_d
 #endif
   const int slots = D / 128;
   const bool fuse_stats = folded && b->stats_part && D % 256 == 0 && gemm_can_fuse_stats(rows, D);
-  const bool fuse_stats_out = fuse_stats && DIT_FUSE_STATS_OUT;
+  const bool fuse_stats_out = fuse_stats && DIT_FUSE_STATS_OUT && rows_att == rows;
   auto block_stats = [&](bool from_gemm) -> int {
     if (from_gemm)
       return ln_finalize(st, reinterpret_cast<const float2*>(b->stats_part), slots, rows, D, 1e-6f, b->stats, bfm(b->stats_a));
@@ -113,21 +117,21 @@ static int dit_forward_impl(cudaStream_t st, const f5e_dit_model* m, const f5e_d
       }
       if (folded) {
         ep.ln_rstd = b->stats; ep.ln_a2 = bf(b->stats_a); ep.bias = L.d_qkv;
-        F5E_TRY(gemm_bf16(st, bf(xs), D, bf(L.wf_qkv), D + 64, rows, 3 * inner, D + 64, ep));
+        F5E_TRY(gemm_bf16(st, bf(xs), D, bf(L.wf_qkv), D + 64, rows_att, 3 * inner, D + 64, ep));
       } else {
-        F5E_TRY(gemm_bf16(st, bf(b->xn), D, bf(L.w_qkv), D, rows, 3 * inner, D, ep));
+        F5E_TRY(gemm_bf16(st, bf(b->xn), D, bf(L.w_qkv), D, rows_att, 3 * inner, D, ep));
       }
     }
     if (L.q_norm_w)
-      F5E_TRY(qk_norm_rope(st, bfm(b->qkv), 3 * inner, rows, inner, m->heads, L.q_norm_w, L.k_norm_w, 1e-6f,
+      F5E_TRY(qk_norm_rope(st, bfm(b->qkv), 3 * inner, rows_att, inner, m->heads, L.q_norm_w, L.k_norm_w, 1e-6f,
                            m->rope_heads > 0 ? m->rope_inv_freq : nullptr, m->rope_heads, n_pad, row_info));
-    F5E_TRY(attention(st, bf(b->qkv), 3 * inner, bfm(b->attn), inner, klen, samples, n_pad, m->heads, 0.125f, row_start, rows));
+    F5E_TRY(attention(st, bf(b->qkv), 3 * inner, bfm(b->attn), inner, klen, samples, n_pad, m->heads, 0.125f, row_start, rows_att));
     {  // to_out + masked_fill + gate_msa * attn + residual (modules.py:494-501, :634)
       EpiParams ep{};
       ep.out = xs; ep.ldo = D; ep.bias = L.b_out; ep.n_pad = n_pad; ep.row_info = row_info; ep.row_len = row_len;
       ep.gate = gate_msa; ep.gate_stride = mod_stride; ep.residual = bf(xs); ep.ldr = D;
       if (fuse_stats_out) { ep.stats_out = reinterpret_cast<float2*>(b->stats_part); ep.stats_slots = slots; }
-      F5E_TRY(gemm_bf16(st, bf(b->attn), inner, bf(L.w_out), inner, rows, D, inner, ep));
+      F5E_TRY(gemm_bf16(st, bf(b->attn), inner, bf(L.w_out), inner, rows_att, D, inner, ep));
     }
     if (folded) F5E_TRY(block_stats(fuse_stats_out));
     else F5E_TRY(norm_mod(st, bf(xs), bfm(b->xn), rows, D, scale_mlp, shift_mlp, mod_stride, n_pad, 1.0f, 1e-6f, row_info));
@@ -184,6 +188,8 @@ static int check_pack(const f5e_dit_packing* p, const int* klen, int samples, in
   F5E_REQUIRE(klen != nullptr, "dit: a row packing needs klen");
   F5E_REQUIRE(p->row_map && p->row_info && p->row_start, "dit: null packing array");
   F5E_REQUIRE(p->rows_packed > 0 && p->rows_packed <= samples * n_pad, "dit: rows_packed=%d out of range", p->rows_packed);
+  F5E_REQUIRE(p->rows_total == 0 || p->rows_total == p->rows_packed || p->rows_total == samples * n_pad,
+              "dit: rows_total=%d must be 0, rows_packed or samples * n_pad = %d", p->rows_total, samples * n_pad);
   F5E_REQUIRE(n_pad <= 65535, "dit: packed rows need n_pad <= 65535");
   return 0;
 }
@@ -222,9 +228,12 @@ int f5e_ode_solve_guided(const f5e_dit_model* model, const f5e_dit_buffers* buf,
   F5E_TRY(check_pack(pack, klen, samples, n_pad));
   F5E_REQUIRE(!pack || pack->rows_packed % nb == 0, "f5e_ode_solve: every guidance branch must pack to the same rows");
   // packed: pred holds the valid frames back to back, branch after branch; row_map[0 .. rows_upd) maps the first
-  // branch onto the padded state rows
+  // branch onto the padded state rows.  A split packing appends the padded frames the same way (rows_tail per branch).
   const int rows_upd = pack ? pack->rows_packed / nb : rows_state;
   const int* upd_map = pack ? pack->row_map : nullptr;
+  const int rows_tail_all = pack && pack->rows_total > pack->rows_packed ? pack->rows_total - pack->rows_packed : 0;
+  F5E_REQUIRE(rows_tail_all % nb == 0, "f5e_ode_solve: every guidance branch must pad to the same rows");
+  const int rows_tail = rows_tail_all / nb;
   // every sample shares the time step here, so the LayerNorms can be folded into the QKV / FF1 GEMMs
   const bool folded = model->fold_jobs != nullptr;
   if (folded) {
@@ -245,6 +254,10 @@ int f5e_ode_solve_guided(const f5e_dit_model* model, const f5e_dit_buffers* buf,
       float* tr = traj ? traj + (size_t)i * rows_state * model->mel_dim : nullptr;
       F5E_TRY(guided_euler(es, buf->pred, model->mel_dim, y, (__nv_bfloat16*)buf->x_cat, model->in_dim, tr, rows_upd,
                            model->mel_dim, dt_host[i], nb, g->c0, g->c1, round_bf16, upd_map, rows_state));
+      if (rows_tail > 0)
+        F5E_TRY(guided_euler(es, buf->pred + (size_t)pack->rows_packed * model->mel_dim, model->mel_dim, y,
+                             (__nv_bfloat16*)buf->x_cat, model->in_dim, tr, rows_tail, model->mel_dim, dt_host[i], nb, g->c0,
+                             g->c1, round_bf16, upd_map + pack->rows_packed, rows_state));
     }
     return 0;
   };

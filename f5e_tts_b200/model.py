@@ -52,21 +52,28 @@ class _Buffers(C.Structure):
 
 
 class _Packing(C.Structure):  # f5e_dit_packing
-    _fields_ = [("row_map", C.c_void_p), ("row_info", C.c_void_p), ("row_start", C.c_void_p), ("rows_packed", C.c_int32)]
+    _fields_ = [("row_map", C.c_void_p), ("row_info", C.c_void_p), ("row_start", C.c_void_p), ("rows_packed", C.c_int32),
+                ("rows_total", C.c_int32)]
 
 
-def make_packing(klen: torch.Tensor, n_pad: int):
+def make_packing(klen: torch.Tensor, n_pad: int, keep_padded: bool = False):
     """Row packing of `samples` sequences with klen[s] valid frames each (include/f5e_b200.h: f5e_dit_packing).
+    keep_padded: the padded frames follow the valid ones (the exact, "split" form) instead of being dropped.
     Integer index plumbing in torch; returns (struct, tensors to keep alive)."""
     klen = klen.to(torch.int64)
     S = klen.numel()
     frame = torch.arange(n_pad, device=klen.device)
     valid = frame[None, :] < klen[:, None]                                   # [S, n_pad]
     sample = torch.arange(S, device=klen.device)[:, None].expand(S, n_pad)
-    row_map = (sample * n_pad + frame[None, :])[valid].to(torch.int32).contiguous()
-    row_info = ((sample << 16) | frame[None, :])[valid].to(torch.int32).contiguous()
+    rm, ri = sample * n_pad + frame[None, :], (sample << 16) | frame[None, :]
+    row_map, row_info = rm[valid], ri[valid]
+    rows_packed = int(row_map.numel())
+    if keep_padded:
+        row_map, row_info = torch.cat([row_map, rm[~valid]]), torch.cat([row_info, ri[~valid]])
+    row_map, row_info = row_map.to(torch.int32).contiguous(), row_info.to(torch.int32).contiguous()
     row_start = (torch.cumsum(klen, 0) - klen).to(torch.int32).contiguous()
-    pk = _Packing(row_map.data_ptr(), row_info.data_ptr(), row_start.data_ptr(), int(row_map.numel()))
+    pk = _Packing(row_map.data_ptr(), row_info.data_ptr(), row_start.data_ptr(), rows_packed,
+                  int(row_map.numel()) if keep_padded else 0)
     return pk, (row_map, row_info, row_start)
 
 
@@ -525,12 +532,15 @@ class CFM(nn.Module):
         self.use_cuda_graph = False       # capture the whole Euler loop in one CUDA graph launch
         self.store_trajectory = True      # False: return only [y0, y1] instead of steps+1 states
         self.emulate_lowp_state = False   # True: round the ODE state to bf16 every step like a bf16 reference run
-        # batch > 1: run the DiT blocks on the valid frames only (padding costs no FLOPs).  The state of PADDED frames is
-        # then frozen at y0 = 0, whereas the reference's padded frames evolve with every Euler step and leak through the two
-        # unmasked k=31 ConvPositionEmbedding convs into the last <= 30 valid frames of every shorter sample.
-        # None (default) = pack only where that is exact: `isolate_samples` (padded frames never reach a valid one) or a
-        # batch whose samples all have the same length.  True = always pack (throughput knob; the deviation is confined to
-        # those tail frames and measured in tests/test_parity_gpu.py::test_packed_rows_tail_deviation), False = never.
+        # batch > 1: the DiT blocks run on a permuted row order with the valid frames first (f5e_dit_packing).
+        # None (default) = always exact.  The reference's padded frames evolve with every Euler step and leak through the two
+        #   unmasked k=31 ConvPositionEmbedding convs into the last <= 30 valid frames of every shorter sample,
+        #   so they are kept: they follow the valid rows and skip only the attention sub-block, whose result the reference
+        #   masks to zero on them (bit-identical to the padded layout, no QKV / out-projection FLOPs on padding).  Where no
+        #   padded frame can reach a valid one (`isolate_samples`, or equal lengths) they are dropped altogether.
+        # True = always drop them (throughput knob; their state is then frozen at y0 = 0, the deviation is confined to those
+        #   tail frames and measured in tests/test_sampler_options_gpu.py::test_packed_rows_tail_deviation).
+        # False = the padded layout everywhere.
         self.pack_valid_rows = None
         # True: a sample's result does not depend on what it is batched with - padded frames are zeroed at the inputs of
         # the ConvPositionEmbedding convs and the text / PPG embedders run per sample at the sample's own length, so a
@@ -694,16 +704,19 @@ class CFM(nn.Module):
         klen = duration.to(torch.int32).repeat(nb).contiguous() if batch > 1 else None
         # batch > 1: the DiT blocks run on the valid frames only (no FLOPs on padding)
         want_pack = self.pack_valid_rows
+        keep_padded = False
         if want_pack is None:
-            want_pack = isolate or bool((duration == max_duration).all())
-        pack, pack_keep = (make_packing(klen, N) if (klen is not None and want_pack) else (None, None))
+            want_pack = True
+            keep_padded = not (isolate or bool((duration == max_duration).all()))
+        pack, pack_keep = (make_packing(klen, N, keep_padded) if (klen is not None and want_pack) else (None, None))
+        drops_rows = pack is not None and not keep_padded
         y = y0.float().contiguous()
         traj = None
-        if self.store_trajectory:  # a packed solve writes the valid rows only: padded rows keep y0 there (zeros)
-            traj = (torch.zeros if pack is not None else torch.empty)(steps, B, N, md, device=y.device, dtype=torch.float32)
+        if self.store_trajectory:  # a dropping packing writes the valid rows only: padded rows keep y0 there (zeros)
+            traj = (torch.zeros if drops_rows else torch.empty)(steps, B, N, md, device=y.device, dtype=torch.float32)
         if self.use_cuda_graph:
             # the cached graph bakes every address in: keep the solve's buffers per shape and copy this call's values in
-            gk = (S, N, steps, traj is not None, None if pack is None else pack.rows_packed, klen is None)
+            gk = (S, N, steps, traj is not None, None if pack is None else (pack.rows_packed, pack.rows_total), klen is None)
             gb = dit._gbuf.get(gk)
             if gb is None:
                 if len(dit._gbuf) >= 4:
@@ -717,7 +730,7 @@ class CFM(nn.Module):
             gb["mod"].copy_(mod)
             y, mod = gb["y"], gb["mod"]
             if traj is not None:
-                if pack is not None:
+                if drops_rows:
                     gb["traj"].zero_()
                 traj = gb["traj"]
             if klen is not None:
@@ -727,7 +740,8 @@ class CFM(nn.Module):
                 for dst, src in zip(gb["pack"], pack_keep):
                     dst.copy_(src)
                 pack_keep = gb["pack"]
-                pack = _Packing(pack_keep[0].data_ptr(), pack_keep[1].data_ptr(), pack_keep[2].data_ptr(), pack.rows_packed)
+                pack = _Packing(pack_keep[0].data_ptr(), pack_keep[1].data_ptr(), pack_keep[2].data_ptr(), pack.rows_packed,
+                                    pack.rows_total)
         dt_arr = (C.c_float * steps)(*dts)
         check(_lib.load().f5e_ode_solve_guided(
             C.byref(P.model), C.byref(buf), ptr(y), ptr(mod), P.mod_size, dt_arr, steps, C.byref(guidance), ptr(klen), B, N,
@@ -743,7 +757,7 @@ class CFM(nn.Module):
         out = torch.where(cond_mask, cond, sampled)
         # integer / bool side products of the last solve (tests compare them bit for bit with the reference's)
         self.last_aux = dict(duration=duration, cond_mask=cond_mask, mask=lens_to_mask(duration) if batch > 1 else None, t=t,
-                             packed_rows=pack is not None)
+                             packed_rows=pack is not None, dropped_padded_rows=drops_rows)
         if vocoder is not None:
             out = vocoder(out.permute(0, 2, 1))
         return out, trajectory

@@ -259,15 +259,27 @@ typedef struct f5e_dit_buffers {   /* caller-allocated scratch, rows = samples *
 } f5e_dit_buffers;
 
 /* Optional row packing: after the (unmasked, hence padded-layout) ConvPositionEmbedding nothing but the key-masked
- * attention mixes frames, so the DiT blocks can run on the VALID frames only.  rows_packed = sum of klen;
- * row_map[r] = row of packed row r in the padded [samples * n_pad] layout, row_info[r] = sample << 16 | frame,
- * row_start[s] = first packed row of sample s.  With a packing, buf->pred holds [rows_packed, mel_dim] (packed), and in
- * f5e_ode_solve the first half of row_map addresses the state rows.  NULL = padded layout everywhere. */
+ * attention mixes frames, so the DiT blocks can run on a PERMUTED row order with the valid frames first.
+ * rows_packed = sum of klen; row_map[r] = row of packed row r in the padded [samples * n_pad] layout,
+ * row_info[r] = sample << 16 | frame, row_start[s] = first packed row of sample s.
+ * Two forms:
+ *   rows_total == 0 (or == rows_packed): the padded frames are DROPPED.  Exact when no padded frame can reach a valid one
+ *     (isolate_samples = 1, or all klen equal); otherwise the padded frames of the state stay at their initial value instead
+ *     of evolving, which the reference's unmasked convolutions leak into the last ~30 valid frames of the shorter samples.
+ *   rows_total == samples * n_pad: row_map / row_info list the valid rows first (sample after sample) and then the padded
+ *     rows (sample after sample).  The attention sub-block (QKV projection, attention, out-projection: its result on a
+ *     padded row is masked to zero by the reference, modules.py:499-501, so the row is unchanged) runs on the first
+ *     rows_packed rows only; the row-local ops (LayerNorm, feed-forward, final norm + projection) on all of them.
+ *     Bit-identical to the padded layout, without the attention-side GEMM FLOPs on padding.
+ * With a packing, buf->pred holds [rows_total or rows_packed, mel_dim] in packed order, and in f5e_ode_solve the first
+ * 1 / branches of the valid part (and of the padded part) of row_map addresses the state rows.
+ * NULL = padded layout everywhere. */
 typedef struct f5e_dit_packing {
   const int32_t* row_map;
   const int32_t* row_info;
   const int32_t* row_start;
   int32_t rows_packed;
+  int32_t rows_total;
 } f5e_dit_packing;
 
 /* The two helper kernels of the folded-LayerNorm path (exported for unit tests; f5e_ode_solve calls them itself).
