@@ -154,7 +154,21 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const CUtensorMap* ta = from_a2 ? &tmA2 : &tmA;
           const int ka = from_a2 ? 0 : kb * GEMM_BK;
           if (CG == 2) {  // both CTAs' bytes complete on the leader's barrier
+#if defined(GEMM_DUP_A) || defined(GEMM_DUP_B)  // energy experiment: one operand tile fetched twice (same bytes, same slot)
+#ifdef GEMM_DUP_A
+            constexpr uint32_t DUP_BYTES = S::A_BYTES;
+#else
+            constexpr uint32_t DUP_BYTES = S::STAGE_BYTES - S::A_BYTES;
+#endif
+            if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * (S::STAGE_BYTES + DUP_BYTES));
+#ifdef GEMM_DUP_A
+            tma_load_2d_2cta(sa, ta, &full_bar[stage], ka, m_blk * TILE_M + rank * GEMM_BM);
+#else
+            tma_load_2d_2cta(sb, &tmB, &full_bar[stage], kb * GEMM_BK, n_blk * BN + rank * (BN / 2));
+#endif
+#else
             if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * S::STAGE_BYTES);
+#endif
             tma_load_2d_2cta(sa, ta, &full_bar[stage], ka, m_blk * TILE_M + rank * GEMM_BM);
             tma_load_2d_2cta(sb, &tmB, &full_bar[stage], kb * GEMM_BK, n_blk * BN + rank * (BN / 2));
           } else {

@@ -73,6 +73,7 @@ def probe(name, fn, seconds, work=None):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--seconds", type=float, default=2.0)
+    ap.add_argument("--only-gemm", action="store_true", help="the four block GEMMs only (+ zero-operand variants)")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     _lib.require_device()
@@ -92,8 +93,13 @@ def main():
         res = o if tag in ("out", "ff2") else None
         gate = torch.randn(n, device=dev) if res is not None else None
         probe(f"gemm_{tag}", lambda: ops.gemm(x, w, bias=b, act=act, out=o, residual=res, gate=gate, n_pad=N), a.seconds, 2.0 * M * n * k)
-        if tag == "qkv":
+        if tag == "qkv" and not a.only_gemm:
             probe("cublas_qkv", lambda: torch.matmul(x, w.t()), a.seconds, 2.0 * M * n * k)
+        if a.only_gemm and tag in ("qkv", "ff2"):  # how much of the energy is data-dependent switching: all-zero activations
+            x0 = torch.zeros_like(x)
+            probe(f"gemm_{tag}_zeroA", lambda: ops.gemm(x0, w, bias=b, act=act, out=o, residual=res, gate=gate, n_pad=N), a.seconds, 2.0 * M * n * k)
+    if a.only_gemm:
+        return
     qkv = torch.randn(M, 3 * D, device=dev).bfloat16()
     o = torch.empty(M, D, device=dev, dtype=torch.bfloat16)
     klen = torch.full((S,), N, device=dev, dtype=torch.int32)
