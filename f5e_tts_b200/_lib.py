@@ -88,6 +88,7 @@ def load():
                                + "; run `python -m f5e_tts_b200.build --force` (F5E_ALLOW_STALE=1 overrides)")
     lib.f5e_launch_count.restype = C.c_int64
     lib.f5e_prof_end.restype = C.c_int64
+    lib.f5e_grn_static_scratch_floats.restype = C.c_int64
     _lib = lib
     return lib
 

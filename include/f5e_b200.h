@@ -182,6 +182,19 @@ int f5e_dwconv7(const void* x_bf16, const float* w, const float* b, void* out_bf
  * (slab partial sums, added in a fixed order: bit-reproducible wherever the buffers live). */
 int f5e_grn(const void* x_bf16, const float* gamma, const float* beta, void* out_bf16, float* scratch, int32_t samples,
             int32_t n_pad, int32_t C, void* stream);
+/* f5e_grn without a scratch argument and without any allocation (no counterpart in the reference; added
+ * for callers that may not call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  The slab partials live in a file-scope __device__ array of csrc/grn_static.cu: F5E_GRN_STATIC_MAX_FLOATS
+ * floats = 4 MiB, held by every GPU that loads the library until the process exits.  Same kernels, same results (bit for bit)
+ * as f5e_grn.  Returns -1 with a clear f5e_last_error() when samples * ceil(n_pad / 64) * C (= f5e_grn_static_scratch_floats)
+ * exceeds the limit: use f5e_grn then.  Every call shares the array: calls that overlap on the GPU (two streams, or two
+ * threads without ordering) RACE - serialise them.  Nothing in the array needs clearing between calls (every partial read
+ * is written first by the same call).  The first call on a device looks the array's address up (cudaGetSymbolAddress; with
+ * CUDA's lazy module loading the driver materialises the array at that moment): make one call outside any stream capture. */
+#define F5E_GRN_STATIC_MAX_FLOATS (1 << 20)
+int f5e_grn_static(const void* x_bf16, const float* gamma, const float* beta, void* out_bf16, int32_t samples,
+                   int32_t n_pad, int32_t C, void* stream);
+int64_t f5e_grn_static_scratch_floats(int32_t samples, int32_t n_pad, int32_t C);
 
 /* out[s, n, tap*C + c] = x[s, n + tap - taps/2, c] (zero outside the sample): turns the dense k=5 Conv1d of
  * PPGEmbedding (backbones/dit.py:124-135) into one GEMM with K = taps*C. */
