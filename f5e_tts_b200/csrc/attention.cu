@@ -138,6 +138,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __res
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
+  pdl_wait();     // programmatic dependent launch: the prologue above may overlap the tail of the QKV GEMM
+  pdl_trigger();
 
   if (warp == ATT_WARP_TMA) {
     if (elect_one()) {
@@ -420,14 +422,13 @@ int attention(cudaStream_t st, const __nv_bfloat16* qkv, int ld_qkv, __nv_bfloat
   F5E_REQUIRE(total < (1ll << 30), "attention: too many work items");
   const int grid = (int)(total < 2 * num_sms() ? total : 2 * num_sms());
   LaunchScope ls(st, PROF_ATTN, samples, n_pad, heads);
+  const float sl2 = scale * 1.4426950408889634f;
   if (key_bias)
-    attention_kernel<true><<<grid, ATT_THREADS, ATT_SMEM_TOTAL, st>>>(tm, out, ldo, klen, row_start, n_pad, inner, heads,
-                                                                      qtiles, (int)total, scale * 1.4426950408889634f,
-                                                                      key_bias, ld_bias);
+    F5E_CUDA_CHECK(launch_pdl(attention_kernel<true>, dim3(grid), dim3(ATT_THREADS), ATT_SMEM_TOTAL, st, tm, out, ldo, klen,
+                              row_start, n_pad, inner, heads, qtiles, (int)total, sl2, key_bias, ld_bias));
   else
-    attention_kernel<false><<<grid, ATT_THREADS, ATT_SMEM_TOTAL, st>>>(tm, out, ldo, klen, row_start, n_pad, inner, heads,
-                                                                       qtiles, (int)total, scale * 1.4426950408889634f,
-                                                                       nullptr, 0);
+    F5E_CUDA_CHECK(launch_pdl(attention_kernel<false>, dim3(grid), dim3(ATT_THREADS), ATT_SMEM_TOTAL, st, tm, out, ldo, klen,
+                              row_start, n_pad, inner, heads, qtiles, (int)total, sl2, (const float*)nullptr, 0));
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -38,6 +38,17 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// Programmatic dependent launch (sm_90+): a kernel launched with the programmatic-stream-serialization attribute may become
+// resident while its predecessor in the stream still runs.  pdl_wait() blocks until the predecessor grid has COMPLETED and
+// its memory is visible: every thread executes it before its first global-memory access (a no-op without the attribute).
+// pdl_trigger() lets the successor's CTAs be scheduled as soon as every CTA of this grid has issued it (or exited).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#ifdef F5E_PDL_NO_TRIGGER  // experiment: dependents are released when every CTA has exited (no early residency)
+__device__ __forceinline__ void pdl_trigger() {}
+#else
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#endif
+
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred = 0;
   asm volatile(

@@ -69,6 +69,8 @@ conv_pos_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
+  pdl_wait();  // programmatic dependent launch: the prologue above touches no global memory
+  pdl_trigger();
 
   if (warp == 0) {
     if (elect_one()) {  // see gemm.cu: elect.sync lets the compiler issue UTMALDG / UTCHMMA without a serialisation loop
@@ -188,7 +190,8 @@ int conv_pos(cudaStream_t st, const __nv_bfloat16* x, const __nv_bfloat16* wp, i
   const int tiles = samples * ((n_pad + CV_PAIR - 1) / CV_PAIR) * groups;
   const int grid = tiles < num_sms() ? tiles : num_sms();
   LaunchScope ls(st, PROF_CONV, samples, n_pad, dim);
-  conv_pos_kernel<<<grid, CV_THREADS, CV_SMEM_TOTAL, st>>>(tmX, tmX32, tmW, samples, n_pad, dim, cpg, ep);
+  F5E_CUDA_CHECK(launch_pdl(conv_pos_kernel, dim3(grid), dim3(CV_THREADS), CV_SMEM_TOTAL, st, tmX, tmX32, tmW, samples, n_pad, dim,
+                            cpg, ep));
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

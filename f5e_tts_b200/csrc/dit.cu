@@ -14,6 +14,9 @@ using namespace f5e;
   } while (0)
 
 static_assert(sizeof(f5e_fold_job) == sizeof(FoldJob), "f5e_fold_job must mirror FoldJob");
+#ifndef F5E_PDL_MAX_ROWS
+#define F5E_PDL_MAX_ROWS 6144
+#endif
 
 // ---- cache of instantiated Euler-loop graphs (f5e_ode_solve_guided, use_graph != 0) ----------------------------------
 namespace {
@@ -32,6 +35,7 @@ struct GraphEntry {
   uint64_t key, key2;
   cudaGraphExec_t exec;
   uint64_t last_use;
+  long long launches;  // kernel nodes (counted while capturing): every replay adds them to f5e_launch_count
 };
 constexpr size_t GRAPH_CACHE_ENTRIES = 8;
 std::mutex g_graph_mu;
@@ -244,7 +248,13 @@ int f5e_ode_solve_guided(const f5e_dit_model* model, const f5e_dit_buffers* buf,
       F5E_REQUIRE((L.q_norm_w == nullptr) == (L.k_norm_w == nullptr), "f5e_ode_solve: layer %d has only one of q_norm / k_norm", l);
     }
   }
+  // Small solves (the batch-1 shape of infer_cli.py: ~160 launches of 5-25 us per NFE step): programmatic dependent launch,
+  // every kernel's prologue and launch latency under the tail of its predecessor (2.36 -> 1.99 ms per NFE step on the stream,
+  // 2.01 -> 1.93 in the graph).  Large solves lose 2 % to it (config 2: 17.5 -> 17.9 ms), hence the threshold.
+  constexpr int PDL_MAX_ROWS = F5E_PDL_MAX_ROWS;
+  const bool use_pdl = (pack ? (pack->rows_total > 0 ? pack->rows_total : pack->rows_packed) : samples * n_pad) < PDL_MAX_ROWS;
   auto enqueue = [&](cudaStream_t es) -> int {
+    PdlScope pdl(use_pdl);
     for (int i = 0; i < steps; ++i) {
       const float* mod_i = mod + (size_t)i * mod_size;
       if (folded)
@@ -284,6 +294,7 @@ int f5e_ode_solve_guided(const f5e_dit_model* model, const f5e_dit_buffers* buf,
     if (e.key == key.h && e.key2 == key.h2) {
       e.last_use = ++g_graph_clock;
       F5E_CUDA_CHECK(cudaGraphLaunch(e.exec, st));
+      add_launches(e.launches);
       return 0;
     }
   // Capture on a private stream (the caller's may be the legacy default stream, which cannot be captured);
@@ -297,7 +308,9 @@ int f5e_ode_solve_guided(const f5e_dit_model* model, const f5e_dit_buffers* buf,
     cudaStreamDestroy(cap);
     F5E_CUDA_CHECK(ce);
   }
+  const long long launches0 = launch_count();
   int rc = enqueue(cap);
+  const long long launches = launch_count() - launches0;  // (other threads' launches in between would be miscounted: accounting only)
   ce = cudaStreamEndCapture(cap, &graph);
   cudaStreamDestroy(cap);
   if (rc) {
@@ -316,7 +329,7 @@ int f5e_ode_solve_guided(const f5e_dit_model* model, const f5e_dit_buffers* buf,
     cudaGraphExecDestroy(g_graphs[lru].exec);
     g_graphs.erase(g_graphs.begin() + (long)lru);
   }
-  g_graphs.push_back(GraphEntry{key.h, key.h2, exec, ++g_graph_clock});
+  g_graphs.push_back(GraphEntry{key.h, key.h2, exec, ++g_graph_clock, launches});
   F5E_CUDA_CHECK(cudaGraphLaunch(exec, st));
   return 0;
 }

@@ -18,6 +18,8 @@ norm_mod_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__
                 const float* __restrict__ mul, const float* __restrict__ add, int mod_stride, int n_pad,
                 float plus_one, float eps, const int* __restrict__ row_info) {
   constexpr int D = CH * 256;
+  pdl_wait();  // programmatic dependent launch: nothing above touches global memory
+  pdl_trigger();
   const int lane = threadIdx.x & 31;
   const int wstride = gridDim.x * (NM_THREADS / 32);
   int row = blockIdx.x * (NM_THREADS / 32) + (threadIdx.x >> 5);
@@ -98,7 +100,8 @@ int norm_mod(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, int M,
   LaunchScope ls(st, PROF_NORM, M, D, 0);
 #define F5E_NM(CH)                                                                                                    \
   case CH:                                                                                                            \
-    norm_mod_kernel<CH><<<grid, NM_THREADS, 0, st>>>(x, out, M, mul, add, mod_stride, n_pad, plus_one, eps, row_info); \
+    F5E_CUDA_CHECK(launch_pdl(norm_mod_kernel<CH>, dim3(grid), dim3(NM_THREADS), 0, st, x, out, M, mul, add, mod_stride,   \
+                              n_pad, plus_one, eps, row_info));                                                       \
     break;
   switch (D / 256) {
     F5E_NM(1) F5E_NM(2) F5E_NM(3) F5E_NM(4) F5E_NM(5) F5E_NM(6) F5E_NM(7) F5E_NM(8)
@@ -127,6 +130,8 @@ __global__ void __launch_bounds__(NM_THREADS)
 row_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ rstd_out, __nv_bfloat16* __restrict__ a2, int M,
                  float eps) {
   constexpr int D = CH * 256;
+  pdl_wait();  // programmatic dependent launch: nothing above touches global memory
+  pdl_trigger();
   const int lane = threadIdx.x & 31;
   const int wstride = gridDim.x * (NM_THREADS / 32);
   for (int row = blockIdx.x * (NM_THREADS / 32) + (threadIdx.x >> 5); row < M; row += wstride) {
@@ -173,7 +178,7 @@ int row_stats(cudaStream_t st, const __nv_bfloat16* x, float* rstd, __nv_bfloat1
   LaunchScope ls(st, PROF_NORM, M, D, 1);
 #define F5E_RS(CH)                                                                              \
   case CH:                                                                                      \
-    row_stats_kernel<CH><<<grid, NM_THREADS, 0, st>>>(x, rstd, a2, M, eps); \
+    F5E_CUDA_CHECK(launch_pdl(row_stats_kernel<CH>, dim3(grid), dim3(NM_THREADS), 0, st, x, rstd, a2, M, eps)); \
     break;
   switch (D / 256) {
     F5E_RS(1) F5E_RS(2) F5E_RS(3) F5E_RS(4) F5E_RS(5) F5E_RS(6) F5E_RS(7) F5E_RS(8)
@@ -189,6 +194,8 @@ int row_stats(cudaStream_t st, const __nv_bfloat16* x, float* rstd, __nv_bfloat1
 __global__ void __launch_bounds__(256)
 ln_finalize_kernel(const float2* __restrict__ stats, int slots, int M, float inv_d, float eps, float* __restrict__ rstd_out,
                    __nv_bfloat16* __restrict__ a2) {
+  pdl_wait();  // programmatic dependent launch: nothing above touches global memory
+  pdl_trigger();
   const int row = blockIdx.x * blockDim.x + threadIdx.x;
   if (row >= M) return;
   const float2* p = stats + (size_t)row * slots;
@@ -212,7 +219,8 @@ ln_finalize_kernel(const float2* __restrict__ stats, int slots, int M, float inv
 int ln_finalize(cudaStream_t st, const float2* stats, int slots, int M, int D, float eps, float* rstd, __nv_bfloat16* a2) {
   F5E_REQUIRE(stats && rstd && a2 && M > 0 && slots > 0 && slots * 128 == D, "ln_finalize: bad arguments (slots=%d D=%d)", slots, D);
   LaunchScope ls(st, PROF_NORM, M, D, 3);
-  ln_finalize_kernel<<<(M + 255) / 256, 256, 0, st>>>(stats, slots, M, 1.0f / (float)D, eps, rstd, a2);
+  F5E_CUDA_CHECK(launch_pdl(ln_finalize_kernel, dim3((M + 255) / 256), dim3(256), 0, st, stats, slots, M, 1.0f / (float)D, eps,
+                            rstd, a2));
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -227,6 +235,8 @@ qk_norm_rope_kernel(__nv_bfloat16* __restrict__ qkv, int ld, int rows, int inner
                     const int* __restrict__ row_info) {
   const int lane = threadIdx.x & 31;
   const long long total = (long long)rows * 2 * heads;
+  pdl_wait();  // programmatic dependent launch: nothing above touches global memory
+  pdl_trigger();
   for (long long it = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); it < total; it += (long long)gridDim.x * 8) {
     const int head = (int)(it % heads), which = (int)((it / heads) & 1), row = (int)(it / (2 * heads));
     __nv_bfloat16* p = qkv + (size_t)row * ld + which * inner + head * 64 + 2 * lane;
@@ -260,7 +270,8 @@ int qk_norm_rope(cudaStream_t st, __nv_bfloat16* qkv, int ld, int rows, int inne
   long long grid = (total + 7) / 8;
   if (grid > num_sms() * 16) grid = num_sms() * 16;
   LaunchScope ls(st, PROF_NORM, rows, inner, 4);
-  qk_norm_rope_kernel<<<(int)grid, 256, 0, st>>>(qkv, ld, rows, inner, heads, qw, kw, eps, inv_freq, rope_heads, n_pad, row_info);
+  F5E_CUDA_CHECK(launch_pdl(qk_norm_rope_kernel, dim3((int)grid), dim3(256), 0, st, qkv, ld, rows, inner, heads, qw, kw, eps,
+                            inv_freq, rope_heads, n_pad, row_info));
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -268,6 +279,8 @@ int qk_norm_rope(cudaStream_t st, __nv_bfloat16* qkv, int ld, int rows, int inne
 // one warp per weight row; `jobs` (device) lists the matrices of every layer: rows [row0, row0 + N) of the launch
 __global__ void __launch_bounds__(256)
 fold_ln_weights_kernel(const FoldJob* __restrict__ jobs, int n_jobs, int total_rows, int D, const float* __restrict__ mod) {
+  pdl_wait();  // programmatic dependent launch: nothing above touches global memory
+  pdl_trigger();
   const int lane = threadIdx.x & 31;
   const int grow = blockIdx.x * 8 + (threadIdx.x >> 5);
   if (grow >= total_rows) return;
@@ -317,7 +330,8 @@ fold_ln_weights_kernel(const FoldJob* __restrict__ jobs, int n_jobs, int total_r
 int fold_ln_weights(cudaStream_t st, const FoldJob* jobs_dev, int n_jobs, int total_rows, int D, const float* mod) {
   F5E_REQUIRE(jobs_dev && n_jobs > 0 && total_rows > 0 && D % 256 == 0, "fold_ln_weights: bad arguments");
   LaunchScope ls(st, PROF_NORM, total_rows, D, 2);
-  fold_ln_weights_kernel<<<(total_rows + 7) / 8, 256, 0, st>>>(jobs_dev, n_jobs, total_rows, D, mod);
+  F5E_CUDA_CHECK(launch_pdl(fold_ln_weights_kernel, dim3((total_rows + 7) / 8), dim3(256), 0, st, jobs_dev, n_jobs, total_rows, D,
+                            mod));
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -334,6 +348,8 @@ __global__ void __launch_bounds__(256)
 guided_euler_kernel(const float* __restrict__ pred, int ld_pred, float* __restrict__ y,
                     __nv_bfloat16* __restrict__ x_cat, int ld_cat, float* __restrict__ traj, int rows, int C,
                     float dt, float c0, float c1, int round_bf16, const int* __restrict__ row_map, int rows_state) {
+  pdl_wait();  // programmatic dependent launch: nothing above touches global memory
+  pdl_trigger();
   const int quads = C >> 2;  // C % 4 == 0
   const long long total = (long long)rows * quads;
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
@@ -386,11 +402,14 @@ int guided_euler(cudaStream_t st, const float* pred, int ld_pred, float* y, __nv
   LaunchScope ls(st, PROF_ELEM, rows, C, 0);
   const int rs = row_map ? rows_state : rows;
   if (branches == 1)
-    guided_euler_kernel<1><<<grid, 256, 0, st>>>(pred, ld_pred, y, x_cat, ld_cat, traj, rows, C, dt, c0, c1, round_bf16, row_map, rs);
+    F5E_CUDA_CHECK(launch_pdl(guided_euler_kernel<1>, dim3(grid), dim3(256), 0, st, pred, ld_pred, y, x_cat, ld_cat, traj, rows, C, dt,
+                              c0, c1, round_bf16, row_map, rs));
   else if (branches == 2)
-    guided_euler_kernel<2><<<grid, 256, 0, st>>>(pred, ld_pred, y, x_cat, ld_cat, traj, rows, C, dt, c0, c1, round_bf16, row_map, rs);
+    F5E_CUDA_CHECK(launch_pdl(guided_euler_kernel<2>, dim3(grid), dim3(256), 0, st, pred, ld_pred, y, x_cat, ld_cat, traj, rows, C, dt,
+                              c0, c1, round_bf16, row_map, rs));
   else
-    guided_euler_kernel<3><<<grid, 256, 0, st>>>(pred, ld_pred, y, x_cat, ld_cat, traj, rows, C, dt, c0, c1, round_bf16, row_map, rs);
+    F5E_CUDA_CHECK(launch_pdl(guided_euler_kernel<3>, dim3(grid), dim3(256), 0, st, pred, ld_pred, y, x_cat, ld_cat, traj, rows, C, dt,
+                              c0, c1, round_bf16, row_map, rs));
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

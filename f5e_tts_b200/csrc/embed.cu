@@ -241,6 +241,8 @@ int unfold_frames(cudaStream_t st, const __nv_bfloat16* x, __nv_bfloat16* out, i
 __global__ void __launch_bounds__(256)
 gather_rows_kernel(const __nv_bfloat16* __restrict__ src, __nv_bfloat16* __restrict__ dst, const int* __restrict__ row_map,
                    int rows, int C) {
+  pdl_wait();  // programmatic dependent launch (common.cuh)
+  pdl_trigger();
   const int vec = C / 8;
   const long long total = (long long)rows * vec;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -255,7 +257,7 @@ int gather_rows(cudaStream_t st, const __nv_bfloat16* src, __nv_bfloat16* dst, c
   int grid = (int)((total + 255) / 256);
   if (grid > num_sms() * 16) grid = num_sms() * 16;
   LaunchScope ls(st, PROF_ELEM, rows, C, 10);
-  gather_rows_kernel<<<grid, 256, 0, st>>>(src, dst, row_map, rows, C);
+  F5E_CUDA_CHECK(launch_pdl(gather_rows_kernel, dim3(grid), dim3(256), 0, st, src, dst, row_map, rows, C));
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -136,6 +136,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
+  // Programmatic dependent launch: everything above (barriers, TMEM, descriptor prefetch) touched no global memory and may
+  // have run under the tail of the previous kernel; from here on its results are needed.
+  pdl_wait();
+  pdl_trigger();
 
   if (warp == 0) {
     if (elect_one()) {  // elect.sync, not `lane == 0`: the compiler then knows ONE thread is active and issues
@@ -617,13 +621,15 @@ static int launch_gemm(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMa
   cfg.blockDim = dim3(GEMM_THREADS);
   cfg.dynamicSmemBytes = S::TOTAL;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CG;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
   F5E_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<BN, STAGES, CG, VQ, STATS>, tmA, tmB, tmC, tmA2, M, N, K, ep, accumulate, vq));
   return 0;
 }

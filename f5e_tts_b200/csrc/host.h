@@ -95,6 +95,33 @@ const char* last_error();
 // class is enabled (f5e_prof_begin), brackets the launch with a CUDA event pair on the launching stream.
 enum ProfClass : int { PROF_GEMM = 1, PROF_ATTN = 2, PROF_CONV = 4, PROF_NORM = 8, PROF_ELEM = 16, PROF_DSP = 32,
                        PROF_VQ = 64 };
+// Programmatic dependent launch of the Euler-loop kernels (common.cuh: pdl_wait / pdl_trigger): on inside a PdlScope(true)
+// of the calling thread (dit.cu opens one for small solves); F5E_PDL=0 / 1 in the environment (read once) forces it.
+bool pdl_enabled();
+struct PdlScope {
+  explicit PdlScope(bool on);
+  ~PdlScope();
+  bool prev;
+};
+// <<<grid, block, smem, st>>> with the programmatic-stream-serialization attribute when pdl_enabled().  ONLY for kernels
+// whose every thread calls pdl_wait() before its first global-memory access.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
+long long launch_count();         // kernels enqueued so far (f5e_launch_count)
+void add_launches(long long n);   // a replayed CUDA graph accounts for the kernels it holds
 struct LaunchScope {
   LaunchScope(cudaStream_t st, int cls, long long a = 0, long long b = 0, long long c = 0);
   ~LaunchScope();

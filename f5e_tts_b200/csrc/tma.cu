@@ -2,6 +2,7 @@
 // (resolved at run time so the library does not link against libcuda directly).
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <atomic>
 #include <mutex>
 #include <vector>
@@ -30,6 +31,21 @@ int num_sms() {
   }
   return n;
 }
+
+// Programmatic dependent launch: F5E_PDL=0 / 1 in the environment forces it off / on; otherwise it is on inside a PdlScope
+// that asks for it (dit.cu: solves below PDL_MAX_ROWS rows, where the kernels are short enough for their prologues and the
+// launch latency to matter; at config-2 size it costs 2 %, measured).
+static int pdl_mode() {
+  static const int mode = [] {
+    const char* e = getenv("F5E_PDL");
+    return e ? (e[0] != '0' ? 1 : 0) : -1;
+  }();
+  return mode;
+}
+static thread_local bool g_pdl_scope = false;
+bool pdl_enabled() { return pdl_mode() == 1 || (pdl_mode() < 0 && g_pdl_scope); }
+PdlScope::PdlScope(bool on) : prev(g_pdl_scope) { g_pdl_scope = on; }
+PdlScope::~PdlScope() { g_pdl_scope = prev; }
 
 int ensure_configured() {
   static std::mutex mu;
@@ -133,6 +149,8 @@ LaunchScope::LaunchScope(cudaStream_t s, int cls, long long a, long long b, long
   g_prof.push_back(r);
   rec = (int)g_prof.size() - 1;
 }
+long long launch_count() { return g_launches.load(std::memory_order_relaxed); }
+void add_launches(long long n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 LaunchScope::~LaunchScope() {
   if (rec < 0) return;
   std::lock_guard<std::mutex> lk(g_prof_mu);

@@ -226,9 +226,14 @@ def test_cached_graph_reuse_and_invalidation(cuda_dev):
     b = (b[0], b[1], a[2], a[3])  # same durations as `a`: the same solve shape and packing, different contents
     ref = {k: run(False, v, s) for k, (v, s) in dict(a=(a, 3), b=(b, 4), c=(c, 5)).items()}
     _lib.load().f5e_graph_cache_clear()
+    counts = {}
     for key, inp, seed in (("a", a, 3), ("a", a, 3), ("b", b, 4), ("c", c, 5), ("a", a, 3), ("b", b, 4)):
+        n0 = _lib.load().f5e_launch_count()
         out, traj = run(True, inp, seed)
+        counts.setdefault(key, []).append(_lib.load().f5e_launch_count() - n0)
         assert torch.equal(out, ref[key][0]) and torch.equal(traj, ref[key][1]), key
+    # a replayed graph accounts for the kernels it holds (bench.py's gpu_launches): capture and replays count alike
+    assert len(set(counts["a"])) == 1 and counts["a"][0] > 6 * 20 and counts["b"] == counts["a"][:2], counts
     # a weight updated in place (EMA copy, hot-swapped checkpoint): plan and graphs must follow
     with torch.no_grad():
         model.transformer.transformer_blocks[0].ff.ff["2"].bias.add_(0.5)
