@@ -421,7 +421,7 @@ def latency_leg(model, vocoder, dev, nfe):
                 audio_s_per_s=(940 - 315) * HOP / SR / (best / 1e3))
 
 
-def eval_set_leg(model, vocoder, dev, rank, world, n_utt, nfe=16):
+def eval_set_leg(model, vocoder, dev, rank, world, n_utt, nfe=16, batch_frames=32 * 1031, num_buckets=60):
     """BASELINE configs[3]: a Seed-TTS-test-en shaped synthetic set (n_utt utterances of 3-15 s, NFE 16) - a FIXED total
     sharded over the ranks (strong scaling) through evaluate.split_batches (LPT on the modelled cost), then the ONE
     exchange of the path: lengths + one padded NCCL gather of the waveforms to rank 0."""
@@ -439,7 +439,7 @@ def eval_set_leg(model, vocoder, dev, rank, world, n_utt, nfe=16):
         wave = 0.05 * torch.randn(1, int(secs * 16000), generator=g)
         meta.append((f"u{i}", "reference transcript of the prompt audio.", (wave, 16000),
                      " " + "some generated words " * int(1 + 4 * torch.rand(1, generator=g).item()), None))
-    prompts = P.get_inference_prompt(meta, device=dev, infer_batch_size=16 * 1031, num_buckets=200, min_secs=3, max_secs=40)
+    prompts = P.get_inference_prompt(meta, device=dev, infer_batch_size=batch_frames, num_buckets=num_buckets, min_secs=3, max_secs=40)
     E.infer_batches(model, vocoder, prompts[:1], nfe_step=nfe, seed=0)  # warm-up
     if world > 1:  # NCCL builds its peer channels lazily and the allocator has not seen buffers of this size yet: warm both
         for n in (1, 32 << 20):
