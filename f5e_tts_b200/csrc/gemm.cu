@@ -629,7 +629,7 @@ static int launch_gemm(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMa
   attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = pdl_enabled() ? 2 : 1;
+  cfg.numAttrs = pdl_enabled(true) ? 2 : 1;
   F5E_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<BN, STAGES, CG, VQ, STATS>, tmA, tmB, tmC, tmA2, M, N, K, ep, accumulate, vq));
   return 0;
 }

@@ -97,7 +97,7 @@ enum ProfClass : int { PROF_GEMM = 1, PROF_ATTN = 2, PROF_CONV = 4, PROF_NORM = 
                        PROF_VQ = 64 };
 // Programmatic dependent launch of the Euler-loop kernels (common.cuh: pdl_wait / pdl_trigger): on inside a PdlScope(true)
 // of the calling thread (dit.cu opens one for small solves); F5E_PDL=0 / 1 in the environment (read once) forces it.
-bool pdl_enabled();
+bool pdl_enabled(bool heavy = false);  // heavy: GEMM / attention / conv_pos (tcgen05 kernels with a TMEM prologue)
 struct PdlScope {
   explicit PdlScope(bool on);
   ~PdlScope();
@@ -116,7 +116,7 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cfg.numAttrs = pdl_enabled(smem > 48 * 1024) ? 1 : 0;  // the heavy kernels are the ones with opt-in shared memory
   return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 

@@ -35,15 +35,18 @@ int num_sms() {
 // Programmatic dependent launch: F5E_PDL=0 / 1 in the environment forces it off / on; otherwise it is on inside a PdlScope
 // that asks for it (dit.cu: solves below PDL_MAX_ROWS rows, where the kernels are short enough for their prologues and the
 // launch latency to matter; at config-2 size it costs 2 %, measured).
-static int pdl_mode() {
+static int pdl_mode() {  // -1 auto, 0 off, 1 on, 2 light kernels only, 3 heavy kernels only (2 / 3: experiments)
   static const int mode = [] {
     const char* e = getenv("F5E_PDL");
-    return e ? (e[0] != '0' ? 1 : 0) : -1;
+    return e ? (e[0] >= '0' && e[0] <= '3' ? e[0] - '0' : 1) : -1;
   }();
   return mode;
 }
 static thread_local bool g_pdl_scope = false;
-bool pdl_enabled() { return pdl_mode() == 1 || (pdl_mode() < 0 && g_pdl_scope); }
+bool pdl_enabled(bool heavy) {
+  const int m = pdl_mode();
+  return m == 1 || (m == 2 && !heavy) || (m == 3 && heavy) || (m < 0 && g_pdl_scope);
+}
 PdlScope::PdlScope(bool on) : prev(g_pdl_scope) { g_pdl_scope = on; }
 PdlScope::~PdlScope() { g_pdl_scope = prev; }
 
