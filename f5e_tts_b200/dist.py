@@ -13,6 +13,7 @@ from __future__ import annotations
 
 from dataclasses import dataclass
 
+
 import torch
 import torch.distributed as dist
 
@@ -105,29 +106,40 @@ def gather_padded(t: torch.Tensor, dst: int = 0):
 def gather_varlen(lens: torch.Tensor, payload: torch.Tensor, dst: int = 0):
     """Ragged gather: `payload` is the concatenation along dim 0 of this rank's items (item i has lens[i] rows, any trailing
     shape).  On `dst` returns (all_lens [sum items], all_payload [sum rows, ...]) in rank order; elsewhere (None, None).
-    Lengths travel first (all_gather of the item counts and row totals), then ONE padded gather of the payload."""
+    Lengths travel first (one all_gather of the item counts and row totals, one of the padded length lists), then every
+    rank's payload goes STRAIGHT to its place in the result with one batched send / receive: no padding, no staging copy
+    (the padded gather + concatenation this replaces spent 60 of its 70 ms at 613 MB allocating and copying)."""
     world = _world()
     if world == 1:
         return lens, payload
     rank = dist.get_rank()
     dev = payload.device
+    payload = payload.contiguous()
     meta = torch.tensor([lens.numel(), payload.shape[0]], device=dev, dtype=torch.int64)
     metas = torch.empty(world * 2, device=dev, dtype=torch.int64)
     dist.all_gather_into_tensor(metas, meta)
     metas_h = metas.view(world, 2).cpu()
-    max_items, max_rows = int(metas_h[:, 0].max()), int(metas_h[:, 1].max())
-    lens_p = torch.zeros(max_items, device=dev, dtype=torch.int64)
+    items, rows = [int(v) for v in metas_h[:, 0]], [int(v) for v in metas_h[:, 1]]
+    lens_p = torch.zeros(max(max(items), 1), device=dev, dtype=torch.int64)
     lens_p[: lens.numel()] = lens.to(dev)
-    pay_p = torch.zeros((max_rows,) + tuple(payload.shape[1:]), device=dev, dtype=payload.dtype)
-    pay_p[: payload.shape[0]] = payload
+    all_lens = torch.empty(world * lens_p.numel(), device=dev, dtype=torch.int64)
+    dist.all_gather_into_tensor(all_lens, lens_p)
+    ops, out_p = [], None
     if rank == dst:
-        all_lens = torch.empty(world, max_items, device=dev, dtype=torch.int64)
-        all_pay = torch.empty((world,) + tuple(pay_p.shape), device=dev, dtype=payload.dtype)
-        dist.gather(lens_p, list(all_lens.unbind(0)), dst=dst)
-        dist.gather(pay_p, list(all_pay.unbind(0)), dst=dst)
-        out_l = torch.cat([all_lens[r, : int(metas_h[r, 0])] for r in range(world)])
-        out_p = torch.cat([all_pay[r, : int(metas_h[r, 1])] for r in range(world)])
-        return out_l, out_p
-    dist.gather(lens_p, None, dst=dst)
-    dist.gather(pay_p, None, dst=dst)
-    return None, None
+        out_p = torch.empty((sum(rows),) + tuple(payload.shape[1:]), device=dev, dtype=payload.dtype)
+        off = 0
+        for r in range(world):
+            if r == rank:
+                out_p[off: off + rows[r]] = payload
+            elif rows[r] > 0:
+                ops.append(dist.P2POp(dist.irecv, out_p[off: off + rows[r]], r))
+            off += rows[r]
+    elif rows[rank] > 0:
+        ops.append(dist.P2POp(dist.isend, payload, dst))
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+    if rank != dst:
+        return None, None
+    all_lens = all_lens.view(world, -1)
+    return torch.cat([all_lens[r, : items[r]] for r in range(world)]), out_p

@@ -42,11 +42,14 @@ def split_batches(prompts_all, rank: int, world: int, split: str = "lpt") -> lis
 @torch.no_grad()
 def infer_batches(model, vocoder, prompts_all, *, nfe_step=32, cfg_strength=2.0, sway_sampling_coef=-1.0,
                   no_ref_audio=False, seed=None, target_rms=0.1, rank=0, world=1, split="lpt", sink=None, device=None,
-                  sampler="sample", sampler_kwargs=None):
+                  sampler="sample", sampler_kwargs=None, keep_on_device=False):
     """Solve this rank's batches.  Returns [(utt, wave fp32 [1, n] on the CPU)] (or whatever `sink(utt, wave, sr)`
     returned, when a sink is given).  sampler: "sample" (eval_infer_batch.py), "sample_tts" (eval_infer_batch_tts.py:
     alpha_spk / alpha_txt in sampler_kwargs instead of cfg_strength), "sample_vc" (eval_infer_batch_vc.py: batches from
-    pipeline.get_vc_inference_prompt carry the padded PPG where the text list is; alpha_spk / alpha_ppg in sampler_kwargs)."""
+    pipeline.get_vc_inference_prompt carry the padded PPG where the text list is; alpha_spk / alpha_ppg in sampler_kwargs).
+    keep_on_device: the waves stay on the GPU (no D2H copy and no host synchronisation per batch): for callers that gather the
+    shards over NCCL first and copy to the host once (dist.gather_varlen), instead of the reference's per-utterance file
+    writes from CPU tensors (eval_infer_batch.py:208-218)."""
     dev = torch.device(device) if device is not None else model.device
     out = []
     for bi in split_batches(prompts_all, rank, world, split):
@@ -73,7 +76,9 @@ def infer_batches(model, vocoder, prompts_all, *, nfe_step=32, cfg_strength=2.0,
         rms = torch.stack([torch.as_tensor(r, dtype=torch.float32) for r in ref_rms_list]).to(dev)
         # `if ref_rms < target_rms: wave = wave * ref_rms / target_rms` (eval_infer_batch.py:214-215), per row
         scaled = waves * rms[:, None] / target_rms
-        waves = torch.where((rms < target_rms)[:, None], scaled, waves).cpu()
+        waves = torch.where((rms < target_rms)[:, None], scaled, waves)
+        if not keep_on_device:
+            waves = waves.cpu()
         for i, utt in enumerate(utts):
             w = waves[i: i + 1, : (n_frames[i] - 1) * HOP_LENGTH]
             out.append(sink(utt, w, TARGET_SAMPLE_RATE) if sink is not None else (utt, w))

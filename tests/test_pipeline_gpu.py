@@ -162,6 +162,10 @@ def test_eval_loop_vs_oracle(cuda_dev):
     # two "ranks" in one process: together they cover every utterance exactly once
     got = dict(E.infer_batches(model, voc, prompts, rank=0, world=2, **kw) + E.infer_batches(model, voc, prompts, rank=1, world=2, **kw))
     assert sorted(got) == sorted(m[0] for m in meta)
+    # keep_on_device (no per-batch D2H / host sync: what bench.py's eval-set leg gathers over NCCL): same bits, on the GPU
+    on_dev = dict(E.infer_batches(model, voc, prompts, keep_on_device=True, **kw))
+    for utt, w in got.items():
+        assert on_dev[utt].is_cuda and w.device.type == "cpu" and torch.equal(on_dev[utt].cpu(), w), utt
     # oracle: same prompts, texts as UTF-8 byte ids (vocab_char_map None), fp32 and bf16
     oprompts = [(u, [float(r) for r in rms], mels.cpu(), rl, tl, [list(t.encode("utf-8")) for t in txt])
                 for u, rms, mels, rl, tl, txt in prompts]
