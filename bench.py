@@ -423,7 +423,7 @@ def latency_leg(model, vocoder, dev, nfe):
 
 def eval_set_leg(model, vocoder, dev, rank, world, n_utt, nfe=16, batch_frames=32 * 1031, num_buckets=60):
     """BASELINE configs[3]: a Seed-TTS-test-en shaped synthetic set (n_utt utterances of 3-15 s, NFE 16) - a FIXED total
-    sharded over the ranks (strong scaling) through evaluate.split_batches (LPT on the modelled cost), then the ONE
+    sharded over the ranks (strong scaling) through evaluate.split_batches ("dynamic": a shared counter), then the ONE
     exchange of the path: lengths + one padded NCCL gather of the waveforms to rank 0."""
     import torch
     import torch.distributed as dist
@@ -453,7 +453,8 @@ def eval_set_leg(model, vocoder, dev, rank, world, n_utt, nfe=16, batch_frames=3
         dist.barrier()  # a common start: the job's wall time is the slowest rank's time from here to the end of the gather
     t0 = t_start = time.perf_counter()
     # the shard's waves stay on the device; ONE exchange (lengths + a padded NCCL gather to rank 0) and ONE copy to the host
-    res = E.infer_batches(model, vocoder, prompts, nfe_step=nfe, seed=0, rank=rank, world=world, split="lpt", keep_on_device=True)
+    res = E.infer_batches(model, vocoder, prompts, nfe_step=nfe, seed=0, rank=rank, world=world, split="dynamic",
+                          keep_on_device=True)  # batches drawn from one shared counter, dearest first (evaluate._DynamicBatches)
     lens = torch.tensor([x.shape[-1] for _, x in res], device=dev)
     payload = torch.cat([x.reshape(-1) for _, x in res]) if res else torch.zeros(0, device=dev)
     torch.cuda.synchronize()
@@ -485,7 +486,7 @@ def eval_set_leg(model, vocoder, dev, rank, world, n_utt, nfe=16, batch_frames=3
                          f"NCCL to rank 0 and copied to pinned host memory once (gather_ms)",
                 scaling="strong", n_gpus=world, generated_audio_s=audio, audio_s_per_s=audio / float(tmax[1]), wall_s=float(tmax[1]),
                 solve_s_max_over_ranks=float(tmax[0]), per_rank_busy_s=[round(b, 3) for b in busy],
-                lpt_imbalance=max(busy) / mean_busy if mean_busy > 0 else None, gather_ms=1e3 * (float(tmax[1]) - float(tmax[0])),  # what the exchange + D2H add behind the slowest rank's solve
+                lpt_imbalance=max(busy) / mean_busy if mean_busy > 0 else None, split="dynamic (shared counter)", gather_ms=1e3 * (float(tmax[1]) - float(tmax[0])),  # what the exchange + D2H add behind the slowest rank's solve
                 gather_bytes=int(tsum[3]) * 4, timing="host wall clock around synchronised regions (the rank's batches; then gather + "
                                                       "D2H), max over ranks")
 

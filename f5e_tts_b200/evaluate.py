@@ -18,7 +18,8 @@ TARGET_SAMPLE_RATE, HOP_LENGTH = 24000, 256
 def split_batches(prompts_all, rank: int, world: int, split: str = "lpt") -> list:
     """Indices of the batches rank `rank` solves.  "reference": contiguous chunks like accelerate's
     split_between_processes (the first len % world ranks get one more); "lpt": longest-processing-time on the modelled
-    cost sum(a N + b N^2) of each batch (dist.utterance_cost), deterministic, identical on every rank."""
+    cost sum(a N + b N^2) of each batch (dist.utterance_cost), deterministic, identical on every rank; "dynamic": an
+    iterator that draws from a counter shared by the ranks (_DynamicBatches; needs an initialised process group)."""
     n = len(prompts_all)
     if world <= 1:
         return list(range(n))
@@ -26,8 +27,10 @@ def split_batches(prompts_all, rank: int, world: int, split: str = "lpt") -> lis
         base, extra = divmod(n, world)
         start = rank * base + min(rank, extra)
         return list(range(start, start + base + (1 if rank < extra else 0)))
+    if split == "dynamic":
+        return _DynamicBatches(prompts_all)
     if split != "lpt":
-        raise ValueError(f"split must be 'lpt' or 'reference', not {split!r}")
+        raise ValueError(f"split must be 'lpt', 'dynamic' or 'reference', not {split!r}")
     cost = [sum(fdist.utterance_cost(d) for d in p[4]) for p in prompts_all]
     order = sorted(range(n), key=lambda i: (-cost[i], i))
     load, mine = [0.0] * world, []
@@ -37,6 +40,33 @@ def split_batches(prompts_all, rank: int, world: int, split: str = "lpt") -> lis
         if r == rank:
             mine.append(i)
     return sorted(mine)
+
+
+_dynamic_calls = 0
+
+
+class _DynamicBatches:
+    """split="dynamic": the ranks draw batch indices from ONE shared counter (an atomic add on the process group's
+    rendezvous store, ~0.1 ms per batch), most expensive batch first.  A static plan cannot know that the GPUs of a box differ by
+    a few per cent or that a rank was delayed; with the counter every rank stays busy until the list is empty.  Which rank solves
+    a batch does not change its result.  Every rank must iterate the same sequence of infer_batches calls (the counter's key
+    is the call number)."""
+
+    def __init__(self, prompts_all):
+        import torch.distributed as dist
+        global _dynamic_calls
+        cost = [sum(fdist.utterance_cost(d) for d in p[4]) for p in prompts_all]
+        self.order = sorted(range(len(prompts_all)), key=lambda i: (-cost[i], i))
+        self.store = dist.distributed_c10d._get_default_store()
+        self.key = f"f5e_tts_b200/dynamic_batches/{_dynamic_calls}"
+        _dynamic_calls += 1
+
+    def __iter__(self):
+        while True:
+            k = self.store.add(self.key, 1) - 1
+            if k >= len(self.order):
+                return
+            yield self.order[k]
 
 
 @torch.no_grad()

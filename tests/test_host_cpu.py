@@ -128,6 +128,15 @@ g = fd.gather_padded(t, dst=0)
 lens = torch.tensor([2 + r, 1])
 pay = torch.arange(int(lens.sum()) * 4, dtype=torch.float32).view(-1, 4) + 1000 * r
 al, ap = fd.gather_varlen(lens, pay, dst=0)
+# split="dynamic": the ranks draw from one shared counter - together every batch exactly once, dearest first
+from f5e_tts_b200 import evaluate as ev
+prompts = [(None, None, None, None, [100 + 37 * (i % 5)] * (1 + i % 3), None) for i in range(23)]
+mine = list(ev.split_batches(prompts, r, 2, "dynamic"))
+got = [None, None]
+dist.all_gather_object(got, mine)
+assert sorted(got[0] + got[1]) == list(range(23)), got
+cost = [sum(fd.utterance_cost(d) for d in p[4]) for p in prompts]
+assert all(cost[a] >= cost[b] for a, b in zip(mine, mine[1:])), mine
 if r == 0:
     assert g.shape == (4, 9), g.shape
     assert torch.equal(g[:2, :6], torch.arange(6.).repeat(2, 1)) and g[:2, 6:].abs().sum() == 0
