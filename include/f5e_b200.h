@@ -324,7 +324,10 @@ int f5e_dit_forward(const f5e_dit_model* model, const f5e_dit_buffers* buf, cons
  * float [steps].  traj: optional fp32 [steps, batch*n_pad, mel_dim] (state after each step).  klen: int32
  * [2*batch] (both halves) or NULL.  use_graph != 0 runs the loop as ONE CUDA graph launch: the instantiated graph is
  * cached (8 entries, LRU) on every argument it bakes in - pointers, sizes, dt values, the model / layer / buffer structs -
- * so a caller that keeps its buffers pays capture + instantiation once per shape; no host synchronisation either way. */
+ * so a caller that keeps its buffers pays capture + instantiation once per shape; no host synchronisation either way.
+ * Solves below 6144 rows (branches * batch * n_pad) launch every kernel of the loop with programmatic dependent launch (each
+ * kernel's prologue runs under the tail of its predecessor; results are bit-identical); the environment variable F5E_PDL,
+ * read once per process, forces it off (0) or on (1) for every size.  f5e_launch_count() counts a replayed graph's kernels. */
 int f5e_ode_solve(const f5e_dit_model* model, const f5e_dit_buffers* buf, float* y, const float* mod, int32_t mod_size,
                   const float* dt_host, int32_t steps, float cfg_strength, const int32_t* klen, int32_t batch,
                   int32_t n_pad, float* traj, int32_t round_bf16, int32_t use_graph, const f5e_dit_packing* pack,
