@@ -207,3 +207,30 @@ def test_library_stamp_matches_sources():
     lib = _lib.load()
     lib.f5e_build_stamp.restype = C.c_char_p
     assert lib.f5e_build_stamp().decode() == build.source_stamp()
+
+
+def test_row_packing_index_plumbing():
+    """make_packing (include/f5e_b200.h: f5e_dit_packing): integer plumbing in torch, device independent.  Dropping form: the
+    valid rows of every sample back to back.  Split form (the exact default): the same prefix, then the padded rows, i.e. a
+    permutation of all samples * n_pad rows; every guidance branch contributes the same number of valid and of padded rows."""
+    import torch
+    from f5e_tts_b200.model import make_packing
+    n_pad, klen1 = 9, torch.tensor([9, 4, 7])
+    klen = klen1.repeat(2)                                   # two guidance branches
+    S = klen.numel()
+    drop, keep_d = make_packing(klen, n_pad)
+    split, keep_s = make_packing(klen, n_pad, keep_padded=True)
+    valid = int(klen.sum())
+    assert drop.rows_packed == split.rows_packed == valid and drop.rows_total == 0 and split.rows_total == S * n_pad
+    row_map_d, row_info_d, row_start_d = keep_d
+    row_map_s, row_info_s, row_start_s = keep_s
+    assert torch.equal(row_map_s[:valid], row_map_d) and torch.equal(row_info_s[:valid], row_info_d)
+    assert torch.equal(row_start_s, row_start_d) and row_start_d.tolist() == [0, 9, 13, 20, 29, 33]
+    assert sorted(row_map_s.tolist()) == list(range(S * n_pad))                      # a permutation of all rows
+    sample, frame = row_info_s >> 16, row_info_s & 0xFFFF
+    assert torch.equal(sample * n_pad + frame, row_map_s)                            # row_info agrees with row_map
+    assert bool((frame[:valid] < klen[sample[:valid].long()]).all()) and bool((frame[valid:] >= klen[sample[valid:].long()]).all())
+    # f5e_ode_solve addresses the STATE rows with the first 1 / branches of each part: those must be branch 0's rows
+    half_v, half_p = valid // 2, (S * n_pad - valid) // 2
+    assert bool((sample[:half_v] < S // 2).all()) and bool((sample[valid: valid + half_p] < S // 2).all())
+    assert bool((sample[half_v:valid] >= S // 2).all()) and bool((sample[valid + half_p:] >= S // 2).all())
