@@ -17,6 +17,9 @@
 //     reference, so O / l is exact).
 //   * The last key block of a sample is narrowed to the 32-key chunks that hold real keys (QK with N = nc, PV with
 //     K = nc, nc exponentials per row): 0.261 -> 0.243 ms at 1030 frames.
+//   * Ragged batches: the work items are enumerated densely over the samples sorted by descending key length (AttSched,
+//     built in shared memory by every CTA), so the static round-robin shares of the CTAs differ by one cheap item at most:
+//     0.144 -> 0.128 ms for lengths in [343, 1030], 17.35 -> 17.10 ms per NFE step at config 2 (same box, same bits).
 //   * (Evaluating part of the exponentials as a polynomial on the FMA pipe costs MORE time and more joules here -
 //     0.270 / 0.288 ms sustained for 1/4 / 1/2 of them against 0.261 - although a MUFU.EX2 is ~64 pJ:
 //     profiles/r02_attention.md.)
@@ -44,7 +47,8 @@ constexpr int ATT_TILE_BYTES = 128 * 64 * 2;  // 16 KB
 constexpr int ATT_SMEM_Q = 0;
 constexpr int ATT_SMEM_KV = ATT_TILE_BYTES;
 constexpr int ATT_SMEM_BAR = ATT_SMEM_KV + ATT_KV_SLOTS * ATT_TILE_BYTES;
-constexpr int ATT_SMEM_TOTAL = ATT_SMEM_BAR + 128 + 1024;
+constexpr int ATT_SMEM_SCHED = ATT_SMEM_BAR + 128;  // int [3 * 256 + 1]: clipped key lengths, sorted order, tile prefix
+constexpr int ATT_SMEM_TOTAL = ATT_SMEM_SCHED + 3 * 1024 + 16 + 1024;
 constexpr uint32_t ATT_TMEM_COLS = 256;
 constexpr uint32_t ATT_TMEM_O = 128;   // S [0,128) fp32 | O [128,192) fp32 | P [192,256) bf16 pairs (128 keys)
 constexpr uint32_t ATT_TMEM_P = 192;
@@ -77,12 +81,36 @@ __device__ __forceinline__ void att_trace(int role, int blk, int slot) {
 struct AttItem {
   int sample, head, q0, klen, nb, row_base, q_limit;
 };
+// Item schedule of a ragged batch (built in shared memory by every CTA, see the kernel prologue): the samples sorted by
+// descending key length and, over that order, the running count of their 128-query tiles.  Items are enumerated DENSELY
+// (no slots for the all-padding query tiles of the shorter samples) and longest first, so the CTAs' static round-robin
+// shares differ by at most one item of the cheapest kind; the plain (sample, head, tile) enumeration left the busiest CTA
+// ~25 % above the mean at config 2's lengths (850 - 1030 frames), a tail during which most SMs idle.
+constexpr int ATT_SCHED_MAX = 256;  // samples; larger batches (or klen == NULL: nothing is ragged) use the plain enumeration
+struct AttSched {
+  const int* tab;  // shared memory: [ATT_SCHED_MAX] clipped key lengths | [ATT_SCHED_MAX] sample of rank r | [n + 1] tiles before rank r
+  int n;           // 0 = plain enumeration
+};
 // Work item w -> (sample, head, query tile); false when the tile holds padded queries only (skipped by every role).
 __device__ __forceinline__ bool att_decode(int w, int qtiles, int heads, const int* __restrict__ klen_ptr,
-                                           const int* __restrict__ row_start, int n_pad, AttItem& it) {
-  const int qt = w % qtiles, sh = w / qtiles;
-  it.head = sh % heads;
-  it.sample = sh / heads;
+                                           const int* __restrict__ row_start, int n_pad, const AttSched& sc, AttItem& it) {
+  int qt;
+  if (sc.n > 0) {
+    const int th = w / heads;  // running tile index over the sorted samples; heads of one tile are neighbours
+    int lo = 0, hi = sc.n;     // largest r with prefix[r] <= th (ranks with zero tiles are stepped over)
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (sc.tab[2 * ATT_SCHED_MAX + mid] <= th) lo = mid; else hi = mid;
+    }
+    it.sample = sc.tab[ATT_SCHED_MAX + lo];
+    it.head = w - th * heads;
+    qt = th - sc.tab[2 * ATT_SCHED_MAX + lo];
+  } else {
+    qt = w % qtiles;
+    const int sh = w / qtiles;
+    it.head = sh % heads;
+    it.sample = sh / heads;
+  }
   it.klen = klen_ptr ? min(__ldg(klen_ptr + it.sample), n_pad) : n_pad;
   it.q0 = qt * ATT_BM;
   it.nb = (it.klen + ATT_BN - 1) / ATT_BN;
@@ -107,7 +135,8 @@ template <bool KEY_BIAS>
 __global__ void __launch_bounds__(ATT_THREADS, 2)
 attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __restrict__ out, int ldo,
                  const int* __restrict__ klen_ptr, const int* __restrict__ row_start, int n_pad, int inner, int heads,
-                 int qtiles, int total_items, float scale_log2, const float* __restrict__ key_bias, int ld_bias) {
+                 int qtiles, int total_items, float scale_log2, const float* __restrict__ key_bias, int ld_bias,
+                 int samples) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + ATT_SMEM_BAR);
@@ -141,13 +170,41 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __res
   pdl_wait();     // programmatic dependent launch: the prologue above may overlap the tail of the QKV GEMM
   pdl_trigger();
 
+  // Item schedule (AttSched): rank every sample by (key length descending, index) and count the tiles before it.
+  AttSched sched{reinterpret_cast<const int*>(smem + ATT_SMEM_SCHED), 0};
+#ifndef ATT_PLAIN_ORDER
+  if (klen_ptr != nullptr && samples > 1 && samples <= ATT_SCHED_MAX) {  // CTA-uniform
+    int* sk = reinterpret_cast<int*>(smem + ATT_SMEM_SCHED);
+    int* so = sk + ATT_SCHED_MAX;
+    int* sp = so + ATT_SCHED_MAX;
+    for (int t = threadIdx.x; t < samples; t += ATT_THREADS) sk[t] = min(__ldg(klen_ptr + t), n_pad);
+    __syncthreads();
+    for (int t = threadIdx.x; t < samples; t += ATT_THREADS) {
+      const int kt = sk[t];
+      int rank = 0, pre = 0;
+      for (int u = 0; u < samples; ++u) {
+        const int ku = sk[u];
+        const bool before = ku > kt || (ku == kt && u < t);
+        rank += before ? 1 : 0;
+        pre += before ? (ku + ATT_BM - 1) / ATT_BM : 0;
+      }
+      so[rank] = t;
+      sp[rank] = pre;
+      if (rank == samples - 1) sp[samples] = pre + (kt + ATT_BM - 1) / ATT_BM;
+    }
+    __syncthreads();
+    sched.n = samples;
+    total_items = sp[samples] * heads;
+  }
+#endif
+
   if (warp == ATT_WARP_TMA) {
     if (elect_one()) {
       int slot = 0, item = 0;
       uint32_t phase = 0;
       for (int w = blockIdx.x; w < total_items; w += gridDim.x) {
         AttItem it;
-        if (!att_decode(w, qtiles, heads, klen_ptr, row_start, n_pad, it)) continue;
+        if (!att_decode(w, qtiles, heads, klen_ptr, row_start, n_pad, sched, it)) continue;
         const int row_base = it.row_base;
         if (item > 0) mbar_wait(q_empty, (item - 1) & 1);  // every QK of the previous item has read Q
         mbar_expect_tx(q_full, ATT_TILE_BYTES);
@@ -210,7 +267,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __res
       int item = 0, blk = 0;
       for (int w = blockIdx.x; w < total_items; w += gridDim.x) {
         AttItem it;
-        if (!att_decode(w, qtiles, heads, klen_ptr, row_start, n_pad, it)) continue;
+        if (!att_decode(w, qtiles, heads, klen_ptr, row_start, n_pad, sched, it)) continue;
         auto ncols = [&](int j) { return att_ncols(it.klen - j * ATT_BN); };
         mbar_wait(q_full, item & 1);
         if (blk > 0) {  // the softmax warps hold the previous item's last S block in registers
@@ -246,7 +303,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __res
     int blk = 0;
     for (int w = blockIdx.x; w < total_items; w += gridDim.x) {
       AttItem it;
-      if (!att_decode(w, qtiles, heads, klen_ptr, row_start, n_pad, it)) continue;
+      if (!att_decode(w, qtiles, heads, klen_ptr, row_start, n_pad, sched, it)) continue;
       float m_ref = -INFINITY;  // exponent reference (scaled log2 units); lags the true row maximum by at most 8
       float l = 0.f;
       // One key block of NC computed columns (NC = 128 except in the last block of a sample, see `ncols` above).
@@ -425,10 +482,10 @@ int attention(cudaStream_t st, const __nv_bfloat16* qkv, int ld_qkv, __nv_bfloat
   const float sl2 = scale * 1.4426950408889634f;
   if (key_bias)
     F5E_CUDA_CHECK(launch_pdl(attention_kernel<true>, dim3(grid), dim3(ATT_THREADS), ATT_SMEM_TOTAL, st, tm, out, ldo, klen,
-                              row_start, n_pad, inner, heads, qtiles, (int)total, sl2, key_bias, ld_bias));
+                              row_start, n_pad, inner, heads, qtiles, (int)total, sl2, key_bias, ld_bias, samples));
   else
     F5E_CUDA_CHECK(launch_pdl(attention_kernel<false>, dim3(grid), dim3(ATT_THREADS), ATT_SMEM_TOTAL, st, tm, out, ldo, klen,
-                              row_start, n_pad, inner, heads, qtiles, (int)total, sl2, (const float*)nullptr, 0));
+                              row_start, n_pad, inner, heads, qtiles, (int)total, sl2, (const float*)nullptr, 0, samples));
   F5E_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
