@@ -1,3 +1,8 @@
+"""Developer tool: mean / median cycles per phase from an attention trace (tools/attn_lab.py --trace out.npy, library built
+with -DATT_TRACE): softmax warp of lane quarter 0 (slots 0 start, 2 S in registers, 5 exponent reference fixed, 6 exponentials
+done, 7 P stored) and the MMA issuer (role 4: 0 QK issued, 1 p_full seen, 2 PV issued).
+    python tools/attn_trace_summary.py gpurun_out/trace.npy
+"""
 import numpy as np, sys
 t = np.load(sys.argv[1]).astype(np.int64)   # [cta, role, blk, slot]
 ncta, nrole, nblk, nslot = t.shape
